@@ -1,0 +1,829 @@
+"""The fused executor behind ``AudioSlowFast.forward`` / ``ResNet.forward`` and their backward.
+
+What the reference does with 110 nn.Conv2d + 110 nn.BatchNorm2d + ReLU / add / cat / pool modules
+(/root/reference/audio_slowfast/models/audio_model_builder.py:311-325 and the helpers it calls) is laid
+out here ONCE per batch size as a static plan over pre-allocated channels-last buffers and executed as
+a flat sequence of C-ABI kernel launches on the current CUDA stream:
+
+  * every residual-stage / lateral conv  -> asf_tapgemm (tcgen05 + TMEM + TMA implicit GEMM, bf16 in,
+    fp32 accumulate) with BN scale/shift, ReLU, residual add and the lateral's concat-slice write fused
+    into the epilogue (frozen / eval BN), or per-channel batch statistics emitted by the epilogue followed
+    by one fused normalise(+residual)(+ReLU) pass (training BN);
+  * stems (C_in = 1)                     -> CUDA-core direct conv + fused BN/ReLU/max-pool;
+  * head                                 -> warp-reduction average pool + CUDA-core GEMMs;
+  * backward                             -> the same tap-GEMM kernel for dgrad (flipped taps, transposed
+    weights, ReLU mask / gradient accumulation fused in the epilogue) and its MN-major mode for wgrad.
+
+``Engine.run`` registers one autograd node for the whole network; its backward writes parameter gradients
+straight into ``p.grad`` (views of one flat fp32 buffer that the data-parallel wrapper all-reduces in
+buckets while the remaining backward is still running).
+
+With compute dtype float32 (cfg.B200.COMPUTE_DTYPE) every conv runs on the CUDA-core direct kernels
+instead: that is the fp32 parity mode (1e-3 logits criterion), not a fallback -- it needs the GPU too.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+
+BN_UNFROZEN = ("s1.pathway0_stem.bn", "s1.pathway1_stem.bn", "s1_fuse.bn")
+
+
+class Act:
+    """Channels-last activation: logical (B, T, F, C) living in ``buf`` (B, T, F, Ctot) at channel offset."""
+
+    def __init__(self, B, T, F, C, dtype, device, parent=None, c_off=0, name=""):
+        self.B, self.T, self.F, self.C = B, T, F, C
+        self.name = name
+        if parent is None:
+            self.buf = torch.empty((B, T, F, C), dtype=dtype, device=device)
+            self.c_off = 0
+        else:
+            assert (parent.B, parent.T, parent.F) == (B, T, F) and c_off + C <= parent.buf.shape[3]
+            self.buf = parent.buf
+            self.c_off = parent.c_off + c_off
+        self.parent = parent
+        self.ld = self.buf.shape[3]
+        self.rows = B * T * F
+        self.dtype = dtype
+        self.code = L.dtype_code(dtype)
+        self.esize = self.buf.element_size()
+        self._grad = None
+        self.grad_state = 0  # backward bookkeeping: 0 = nothing written yet this pass
+
+    @property
+    def ptr(self):
+        return self.buf.data_ptr() + self.c_off * self.esize
+
+    def row_ptr(self, row):
+        return self.ptr + row * self.ld * self.esize
+
+    def view(self):
+        return self.buf[..., self.c_off:self.c_off + self.C]
+
+    def slice(self, c_off, C, name=""):
+        return Act(self.B, self.T, self.F, C, self.dtype, self.buf.device, parent=self, c_off=c_off, name=name)
+
+    @property
+    def grad(self):
+        """Gradient buffer with the same geometry (slices share their parent's gradient buffer)."""
+        if self._grad is None:
+            if self.parent is not None:
+                pg = self.parent.grad
+                self._grad = Act(self.B, self.T, self.F, self.C, self.dtype, self.buf.device, parent=pg,
+                                 c_off=self.c_off - self.parent.c_off, name=self.name + ".grad")
+            else:
+                self._grad = Act(self.B, self.T, self.F, self.C, self.dtype, self.buf.device, name=self.name + ".grad")
+        return self._grad
+
+
+class ConvUnit:
+    """conv (+BN) (+residual) (+ReLU) with its static geometry and buffers."""
+
+    def __init__(self, name, conv, bn, x, y, relu, res=None):
+        self.name, self.conv, self.bn, self.x, self.y, self.relu, self.res = name, conv, bn, x, y, relu, res
+        self.kt, self.kf = conv.kernel_size
+        self.st, self.sf = conv.stride
+        self.pt, self.pf = conv.padding
+        self.Cin, self.Cout = conv.in_channels, conv.out_channels
+        self.taps = self.kt * self.kf
+        assert x.C == self.Cin and y.C == self.Cout, (name, x.C, self.Cin, y.C, self.Cout)
+        To = (x.T + 2 * self.pt - self.kt) // self.st + 1
+        Fo = (x.F + 2 * self.pf - self.kf) // self.sf + 1
+        assert (To, Fo) == (y.T, y.F), (name, To, Fo, y.T, y.F)
+        self.raw = None          # raw conv output (training-BN mode only)
+        self.scale = self.shift = self.mean = self.invstd = self.stats = self.red = None
+        self.w_pack = self.w_pack_t = None
+        self.w_key = None
+        self.batch_mode = False
+        # conv class for the tap-GEMM path
+        if self.kt == 1 and self.kf == 1 and self.st == 1 and self.sf == 1:
+            self.axis, self.k, self.s, self.p = "flat", 1, 1, 0
+        elif self.kf == 1 and self.sf == 1 and self.pf == 0:
+            self.axis, self.k, self.s, self.p = "T", self.kt, self.st, self.pt
+        elif self.kt == 1 and self.st == 1 and self.pt == 0:
+            self.axis, self.k, self.s, self.p = "F", self.kf, self.sf, self.pf
+        else:
+            self.axis = None
+
+    def geom(self):
+        g = L.ConvGeom()
+        g.B, g.Tin, g.Fin, g.Cin = self.x.B, self.x.T, self.x.F, self.Cin
+        g.Tout, g.Fout, g.Cout = self.y.T, self.y.F, self.Cout
+        g.kt, g.kf, g.st, g.sf, g.pt, g.pf = self.kt, self.kf, self.st, self.sf, self.pt, self.pf
+        g.ld_in, g.ld_out = self.x.ld, self.y.ld
+        return g
+
+
+def _epilogue(scale=None, shift=None, res=None, mask=None, stats=None, stats_stride=0, relu=False, accumulate=False,
+              row_off=0):
+    e = L.Epilogue()
+    e.scale = scale.data_ptr() if scale is not None else None
+    e.shift = shift.data_ptr() if shift is not None else None
+    if res is not None:
+        e.res, e.ld_res = res.row_ptr(row_off), res.ld
+    if mask is not None:
+        e.mask, e.ld_mask = mask.row_ptr(row_off), mask.ld
+    if stats is not None:
+        e.stats, e.stats_stride = stats.data_ptr(), stats_stride
+    e.relu, e.accumulate = int(relu), int(accumulate)
+    return e
+
+
+def _pow2_box(first):
+    assert first <= 128 and (first & (first - 1)) == 0, "frequency extent %d must be a power of two <= 128" % first
+    return (first, 128 // first, 1)
+
+
+def _set_m(tg, ext, box, m_to_a):
+    for j in range(3):
+        tg.m_ext[j], tg.m_box[j], tg.m_to_a[j] = ext[j], box[j], m_to_a[j]
+
+
+def _set_a(tg, act, dims, strides):
+    tg.a = act.ptr
+    tg.nd = len(dims)
+    for i, (d, s) in enumerate(zip(dims, strides)):
+        tg.a_dim[i], tg.a_stride[i] = d, s
+
+
+def tg_forward_geometry(u, tg, x):
+    """Fills the A-side (tensor map, M-space, taps) of a TapGemm for unit ``u`` reading activation ``x``
+    over the OUTPUT position space.  Returns the o_stride triple (in output rows)."""
+    B, T, F, ld = x.B, x.T, x.F, x.ld
+    k, s, p = u.k, u.s, u.p
+    tg.K = u.Cin
+    tg.ntaps = k
+    tg.ntaps_w = k
+    for i in range(k):
+        tg.b_tap[i] = i
+    if u.axis == "flat":
+        _set_a(tg, x, [B * T * F], [ld])
+        _set_m(tg, (B * T * F, 1, 1), (128, 1, 1), (1, 0, 0))
+        return (1, 0, 0)
+    if u.axis == "T" and s == 1:
+        _set_a(tg, x, [F, T, B], [ld, F * ld, T * F * ld])
+        _set_m(tg, (F, T, B), _pow2_box(F), (1, 2, 3))
+        for i in range(k):
+            tg.a_off[i][1] = i - p
+        return (1, F, T * F)
+    if u.axis == "T":
+        assert T % s == 0 and u.y.T == T // s, "time-strided conv needs T divisible by the stride"
+        To = T // s
+        _set_a(tg, x, [F, s, To, B], [ld, F * ld, s * F * ld, T * F * ld])
+        _set_m(tg, (F, To, B), _pow2_box(F), (1, 3, 4))
+        for i in range(k):
+            q = i - p
+            tg.a_off[i][1] = q % s
+            tg.a_off[i][2] = (q - q % s) // s
+        return (1, F, To * F)
+    if u.axis == "F" and s == 1:
+        _set_a(tg, x, [F, B * T], [ld, F * ld])
+        _set_m(tg, (F, B * T, 1), _pow2_box(F), (1, 2, 0))
+        for i in range(k):
+            tg.a_off[i][0] = i - p
+        return (1, F, 0)
+    if u.axis == "F":
+        assert F % s == 0 and u.y.F == F // s, "frequency-strided conv needs F divisible by the stride"
+        Fo = F // s
+        _set_a(tg, x, [s, Fo, B * T], [ld, s * ld, F * ld])
+        _set_m(tg, (Fo, B * T, 1), _pow2_box(Fo), (2, 3, 0))
+        for i in range(k):
+            q = i - p
+            tg.a_off[i][0] = q % s
+            tg.a_off[i][1] = (q - q % s) // s
+        return (1, Fo, 0)
+    raise NotImplementedError("conv %s is not a tap-GEMM shape" % u.name)
+
+
+def tg_output_space(u, y):
+    """(dims, strides, m_to_a) of a tensor map over an OUTPUT-shaped activation ``y`` matching the M-space
+    that tg_forward_geometry defines for ``u``."""
+    B, T, F, ld = y.B, y.T, y.F, y.ld
+    if u.axis == "flat":
+        return [B * T * F], [ld], (1, 0, 0)
+    if u.axis == "T":
+        return [F, T, B], [ld, F * ld, T * F * ld], (1, 2, 3)
+    return [F, B * T], [ld, F * ld], (1, 2, 0)
+
+
+class Engine:
+    def __init__(self, model):
+        L.require_cuda_sm100()
+        self.model = model
+        self.dtype = model.compute_dtype
+        self.code = L.dtype_code(self.dtype)
+        self.use_tc = self.dtype == torch.bfloat16
+        self.device = next(model.parameters()).device
+        if self.device.type != "cuda":
+            raise RuntimeError("asf_b200 models must live on a CUDA device (call .cuda()); there is no CPU path")
+        self.plan = None
+        self.grad_hook = None        # callable(engine, names_done) used by the data-parallel wrapper
+        self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
+        self._flat_grad = None
+        self._grad_views = {}
+        self._dwp = None
+
+    # ------------------------------------------------------------------------------------------ plan
+    def invalidate_weights(self):
+        if self.plan is not None:
+            for u in self.plan.units:
+                u.w_key = None
+
+    def _build_plan(self, B, in_shapes):
+        m = self.model
+        dev, dt = self.device, self.dtype
+        npath = m.num_pathways
+        plan = type("Plan", (), {})()
+        plan.B, plan.in_shapes = B, in_shapes
+        plan.units, plan.stems, plan.blocks, plan.fuses = [], [], [], []
+        named = dict(m.named_modules())
+
+        # ---- stems: conv (SIMT) -> raw ; BN+ReLU+maxpool -> pooled
+        x = []
+        stem_out_c = []
+        for p in range(npath):
+            st = getattr(m.s1, "pathway%d_stem" % p)
+            stem_out_c.append(st.conv.out_channels)
+        # slow pathway buffers carry the lateral channels in the same allocation (no torch.cat)
+        def lateral_c(stage_idx):
+            if npath == 1:
+                return 0
+            f = getattr(m, "s%d_fuse" % stage_idx)
+            return f.conv_f2s.out_channels
+
+        for p in range(npath):
+            st = getattr(m.s1, "pathway%d_stem" % p)
+            _, _, T, F = in_shapes[p]
+            conv = st.conv
+            To = (T + 2 * conv.padding[0] - conv.kernel_size[0]) // conv.stride[0] + 1
+            Fo = (F + 2 * conv.padding[1] - conv.kernel_size[1]) // conv.stride[1] + 1
+            xin = Act(B, T, F, 1, torch.float32, dev, name="in%d" % p)
+            raw = Act(B, To, Fo, conv.out_channels, dt, dev, name="stem%d.raw" % p)
+            Tp, Fp = (To + 2 - 3) // 2 + 1, (Fo + 2 - 3) // 2 + 1
+            if p == 0 and npath == 2:
+                full = Act(B, Tp, Fp, conv.out_channels + lateral_c(1), dt, dev, name="s1.cat")
+                pooled = full.slice(0, conv.out_channels, name="s1.p0")
+                pooled.full = full
+            else:
+                pooled = Act(B, Tp, Fp, conv.out_channels, dt, dev, name="s1.p%d" % p)
+                pooled.full = pooled
+            u = ConvUnit("s1.pathway%d_stem" % p, conv, st.bn, xin, raw, relu=False)
+            u.bn_name = "s1.pathway%d_stem.bn" % p
+            u.pooled = pooled
+            u.is_stem = True
+            plan.stems.append(u)
+            x.append(pooled)
+
+        def add_unit(name, conv, bn, xa, ya, relu, res=None, bn_name=None):
+            u = ConvUnit(name, conv, bn, xa, ya, relu, res)
+            u.bn_name = bn_name
+            u.is_stem = False
+            plan.units.append(u)
+            return u
+
+        depths = [len([1 for n in named if n.startswith("s%d.pathway0_res" % s) and n.count(".") == 1]) for s in (2, 3, 4, 5)]
+        order = []  # execution order entries: ("fuse", unit) | ("block", dict)
+        for si, sname in enumerate(("s2", "s3", "s4", "s5")):
+            stage = getattr(m, sname)
+            if npath == 2:
+                f = getattr(m, "s%d_fuse" % (si + 1))
+                xs_full = x[0].full
+                fuse_out = xs_full.slice(x[0].C, f.conv_f2s.out_channels, name="s%d_fuse.out" % (si + 1))
+                fu = add_unit("s%d_fuse" % (si + 1), f.conv_f2s, f.bn, x[1], fuse_out, relu=True,
+                              bn_name="s%d_fuse.bn" % (si + 1))
+                order.append(("fuse", fu))
+                x[0] = xs_full  # the stage reads slow + lateral channels
+            for p in range(npath):
+                h = x[p]
+                for i in range(depths[si]):
+                    blk = getattr(stage, "pathway%d_res%d" % (p, i))
+                    pre = "%s.pathway%d_res%d" % (sname, p, i)
+                    b2 = blk.branch2
+                    sf = b2.b.stride[1]
+                    cout = b2.c.out_channels
+                    T, F = h.T, h.F
+                    Fo = (F + 2 * b2.b.padding[1] - 3) // sf + 1
+                    last = i == depths[si] - 1
+                    # the last slow block of s2..s4 writes into the next concat buffer
+                    if last and p == 0 and npath == 2 and si < 3:
+                        full = Act(B, T, Fo, cout + lateral_c(si + 2), dt, dev, name=pre + ".cat")
+                        out = full.slice(0, cout, name=pre + ".out")
+                        out.full = full
+                    else:
+                        out = Act(B, T, Fo, cout, dt, dev, name=pre + ".out")
+                        out.full = out
+                    entry = {"name": pre, "x": h, "out": out}
+                    if hasattr(blk, "branch1"):
+                        sc = Act(B, T, Fo, cout, dt, dev, name=pre + ".sc")
+                        entry["b1"] = add_unit(pre + ".branch1", blk.branch1, blk.branch1_bn, h, sc, relu=False,
+                                               bn_name=pre + ".branch1_bn")
+                        res = sc
+                    else:
+                        res = h
+                    ha = Act(B, T, F, b2.a.out_channels, dt, dev, name=pre + ".a")
+                    hb = Act(B, T, Fo, b2.b.out_channels, dt, dev, name=pre + ".b")
+                    entry["a"] = add_unit(pre + ".branch2.a", b2.a, b2.a_bn, h, ha, relu=True, bn_name=pre + ".branch2.a_bn")
+                    entry["b"] = add_unit(pre + ".branch2.b", b2.b, b2.b_bn, ha, hb, relu=True, bn_name=pre + ".branch2.b_bn")
+                    entry["c"] = add_unit(pre + ".branch2.c", b2.c, b2.c_bn, hb, out, relu=True, res=res,
+                                          bn_name=pre + ".branch2.c_bn")
+                    order.append(("block", entry))
+                    h = out
+                x[p] = h
+        plan.order = order
+        plan.final = x
+        # head
+        head = m.head
+        feat_dim = sum(head.dim_in)
+        plan.feat = torch.empty((B, feat_dim), dtype=torch.float32, device=dev)
+        plan.feat_drop = torch.empty_like(plan.feat)
+        plan.dfeat = torch.empty_like(plan.feat)
+        for p in range(npath):
+            ps = head.pool_size[p]
+            assert (x[p].T, x[p].F) == (ps[0], ps[1]), (
+                "head pooling %s needs a %dx%d map, got %dx%d: the clip length does not match "
+                "AUDIO_DATA.NUM_FRAMES" % (ps, ps[0], ps[1], x[p].T, x[p].F))
+        plan.projs = head.projections()
+        plan.logits = [torch.empty((B, pr.out_features), dtype=torch.float32, device=dev) for pr in plan.projs]
+        # per-unit BN scratch
+        for u in plan.stems + plan.units:
+            Cn = u.Cout
+            u.scale = torch.empty(Cn, dtype=torch.float32, device=dev)
+            u.shift = torch.empty(Cn, dtype=torch.float32, device=dev)
+            u.mean = torch.empty(Cn, dtype=torch.float32, device=dev)
+            u.invstd = torch.empty(Cn, dtype=torch.float32, device=dev)
+            u.stats = torch.zeros(2 * Cn, dtype=torch.float32, device=dev)
+            u.red = torch.zeros(2 * Cn, dtype=torch.float32, device=dev)
+        return plan
+
+    # ------------------------------------------------------------------------------------------ weights
+    def _prepare_unit(self, u, training):
+        """Refreshes (when stale) the folded BN affine and the packed weight copies of a unit."""
+        bn, conv = u.bn, u.conv
+        u.batch_mode = bool(training and bn.training)
+        key = (conv.weight._version, conv.weight.data_ptr(), bn.weight._version, bn.bias._version,
+               bn.running_mean._version, bn.running_var._version, u.batch_mode, self.force_simt)
+        if key == u.w_key:
+            return
+        st = L.stream_ptr()
+        w32 = conv.weight.detach()
+        if w32.dtype != torch.float32 or not w32.is_contiguous():
+            raise RuntimeError("asf_b200 keeps fp32 contiguous master weights (got %s)" % w32.dtype)
+        wcode = self.code if not u.is_stem else L.F32
+        wdt = self.dtype if not u.is_stem else torch.float32
+        if u.w_pack is None:
+            u.w_pack = torch.empty((u.Cout, u.taps, u.Cin), dtype=wdt, device=self.device)
+            if not u.is_stem:
+                u.w_pack_t = torch.empty((u.Cin, u.taps, u.Cout), dtype=wdt, device=self.device)
+        rs = None
+        if not u.batch_mode:
+            L.call("asf_bn_fold", L.ptr(bn.weight), L.ptr(bn.bias), L.ptr(bn.running_mean), L.ptr(bn.running_var),
+                   C.c_float(bn.eps), u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+            if not u.is_stem:
+                rs = u.scale  # fold the BN scale into the packed weights; the epilogue only adds the shift
+        L.call("asf_pack_weight", L.ptr(w32), L.ptr(u.w_pack), wcode, u.Cout, u.Cin, u.taps, L.ptr(rs), st)
+        if not u.is_stem:
+            L.call("asf_pack_weight_t", L.ptr(w32), L.ptr(u.w_pack_t), wcode, u.Cout, u.Cin, u.taps, L.ptr(rs), st)
+        u.w_key = key
+
+    # ------------------------------------------------------------------------------------------ conv launches
+    def _tc_ok(self, u):
+        return self.use_tc and not self.force_simt and u.axis is not None and u.Cin % 8 == 0
+
+    def _conv_fwd(self, u, out, epi_kwargs):
+        st = L.stream_ptr()
+        if self._tc_ok(u):
+            tg = L.TapGemm()
+            o_stride = tg_forward_geometry(u, tg, u.x)
+            tg.bw, tg.N = u.w_pack.data_ptr(), u.Cout
+            tg.out, tg.out_dtype, tg.ld_out = out.ptr, out.code, out.ld
+            for j in range(3):
+                tg.o_stride[j] = o_stride[j]
+            tg.epi = _epilogue(**epi_kwargs)
+            L.call("asf_tapgemm", C.byref(tg), 0, st)
+        else:
+            g = u.geom()
+            g.ld_out = out.ld
+            e = _epilogue(**epi_kwargs)
+            L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), u.x.code, L.ptr(u.w_pack), L.dtype_code(u.w_pack.dtype),
+                   C.c_void_p(out.ptr), out.code, C.byref(g), C.byref(e), st)
+
+    def _conv_dgrad(self, u, dy, dx, accumulate, res=None, mask=None):
+        """dx (+)= conv^T(dy) [+ res] then masked by (mask > 0).  Handles strided convs as one launch per
+        input phase; the caller guarantees dx was zeroed if some phase has no tap and accumulate is False."""
+        st = L.stream_ptr()
+        if not self._tc_ok(u):
+            g = u.geom()
+            g.ld_in, g.ld_out = dx.ld, dy.ld
+            e = _epilogue(res=res, mask=mask, accumulate=accumulate)
+            L.call("asf_conv_dgrad_simt", C.c_void_p(dy.ptr), dy.code, L.ptr(u.w_pack), L.dtype_code(u.w_pack.dtype),
+                   C.c_void_p(dx.ptr), dx.code, C.byref(g), C.byref(e), st)
+            return
+        B, k, s, p = dy.B, u.k, u.s, u.p
+        for rho in range(s):
+            taps = [(j, (rho + p - j) // s) for j in range(k) if (rho + p - j) % s == 0]
+            if not taps:
+                assert accumulate or getattr(dx, "zeroed", False), "uncovered phase without zero fill: " + u.name
+                continue
+            tg = L.TapGemm()
+            tg.K, tg.N = u.Cout, u.Cin
+            tg.ntaps, tg.ntaps_w = len(taps), k
+            T, F, ld = dy.T, dy.F, dy.ld
+            row_off = 0
+            if u.axis == "flat":
+                _set_a(tg, dy, [B * T * F], [ld])
+                _set_m(tg, (B * T * F, 1, 1), (128, 1, 1), (1, 0, 0))
+                o_stride = (1, 0, 0)
+            elif u.axis == "T":
+                _set_a(tg, dy, [F, T, B], [ld, F * ld, T * F * ld])
+                Ti = dx.T
+                _set_m(tg, (F, Ti // s, B), _pow2_box(F), (1, 2, 3))
+                for i, (j, off) in enumerate(taps):
+                    tg.a_off[i][1] = off
+                o_stride = (1, s * F, Ti * F)
+                row_off = rho * F
+            else:
+                _set_a(tg, dy, [F, B * T], [ld, F * ld])
+                Fi = dx.F
+                _set_m(tg, (Fi // s, B * T, 1), _pow2_box(Fi // s), (1, 2, 0))
+                for i, (j, off) in enumerate(taps):
+                    tg.a_off[i][0] = off
+                o_stride = (s, Fi, 0)
+                row_off = rho
+            for i, (j, off) in enumerate(taps):
+                tg.b_tap[i] = j
+            tg.bw = u.w_pack_t.data_ptr()
+            tg.out, tg.out_dtype, tg.ld_out = dx.row_ptr(row_off), dx.code, dx.ld
+            for j in range(3):
+                tg.o_stride[j] = o_stride[j]
+            tg.epi = _epilogue(res=res, mask=mask, accumulate=accumulate, row_off=row_off)
+            L.call("asf_tapgemm", C.byref(tg), 0, st)
+
+    def _conv_wgrad(self, u, dy, rscale, gview, accumulate):
+        st = L.stream_ptr()
+        if u.is_stem:
+            g = u.geom()
+            g.ld_out = dy.ld
+            if rscale is not None:
+                raise RuntimeError("stem BN is never folded in training")
+            L.call("asf_stem_wgrad", C.c_void_p(u.x.ptr), C.c_void_p(dy.ptr), dy.code, L.ptr(gview), C.byref(g),
+                   int(accumulate), st)
+            return
+        if not self._tc_ok(u):
+            g = u.geom()
+            g.ld_out = dy.ld
+            L.call("asf_conv_wgrad_simt", C.c_void_p(u.x.ptr), u.x.code, C.c_void_p(dy.ptr), dy.code, L.ptr(gview),
+                   C.byref(g), L.ptr(rscale), int(accumulate), st)
+            return
+        tg = L.TapGemm()
+        tg_forward_geometry(u, tg, u.x)
+        tg.N = u.Cout
+        dims, strides, m2a = tg_output_space(u, dy)
+        tg.y, tg.y_nd = dy.ptr, len(dims)
+        for i, (d, s_) in enumerate(zip(dims, strides)):
+            tg.y_dim[i], tg.y_stride[i] = d, s_
+        for j in range(3):
+            tg.y_m_to_a[j] = m2a[j]
+        dwp = self._dwp_view(u)
+        tg.dwp = dwp.data_ptr()
+        L.call("asf_tapgemm", C.byref(tg), 1, st)
+        L.call("asf_unpack_wgrad", L.ptr(dwp), L.ptr(gview), u.Cout, u.Cin, u.taps, L.ptr(rscale), int(accumulate), st)
+
+    # ------------------------------------------------------------------------------------------ grads
+    def _ensure_grad_buffers(self):
+        if self._flat_grad is not None:
+            return
+        params = [(n, p) for n, p in self.model.named_parameters()]
+        # reverse registration order ~ order in which backward produces them: head, s5, s4, ... stems
+        params = params[::-1]
+        total = sum(p.numel() for _, p in params)
+        self._flat_grad = torch.zeros(total, dtype=torch.float32, device=self.device)
+        off = 0
+        self._grad_offsets = {}
+        for n, p in params:
+            self._grad_views[n] = self._flat_grad[off:off + p.numel()].view_as(p)
+            self._grad_offsets[n] = (off, p.numel())
+            off += p.numel()
+        self._param_by_name = dict(params)
+        self._name_of = {id(p): n for n, p in params}
+        # packed wgrad workspace (fp32 [Cout][taps][Cin] per conv, accumulated with atomics, zeroed per pass)
+        tot = sum(u.Cout * u.taps * u.Cin for u in self.plan.units)
+        self._dwp = torch.zeros(tot, dtype=torch.float32, device=self.device)
+        o = 0
+        self._dwp_off = {}
+        for u in self.plan.units:
+            n = u.Cout * u.taps * u.Cin
+            self._dwp_off[u.name] = (o, n)
+            o += n
+
+    def _dwp_view(self, u):
+        o, n = self._dwp_off[u.name]
+        return self._dwp[o:o + n]
+
+    def _grad_target(self, p):
+        """Returns (grad_view, accumulate) for a parameter following autograd semantics: a missing .grad is
+        (re)attached as a view of the flat buffer and overwritten; an existing one is accumulated into."""
+        if not p.requires_grad:
+            return None, False
+        n = self._name_of[id(p)]
+        view = self._grad_views[n]
+        if p.grad is None:
+            p.grad = view
+            return view, False
+        if p.grad.data_ptr() != view.data_ptr():
+            # user-owned grad tensor: accumulate there
+            return p.grad, True
+        return view, True
+
+    # ------------------------------------------------------------------------------------------ forward
+    def run(self, xs):
+        m = self.model
+        B = xs[0].shape[0]
+        shapes = tuple(tuple(t.shape) for t in xs)
+        for t in xs:
+            if t.dim() != 4 or t.shape[1] != 1:
+                raise ValueError("expected inputs of shape (B, 1, T, F), got %s" % (tuple(t.shape),))
+            if t.device != self.device:
+                raise RuntimeError("input on %s but the model is on %s" % (t.device, self.device))
+        if self.plan is None or self.plan.B != B or self.plan.in_shapes != shapes:
+            self.plan = self._build_plan(B, shapes)
+            self._flat_grad = None
+            self._grad_views = {}
+        training = m.training
+        needs_grad = torch.is_grad_enabled() and training and any(p.requires_grad for p in m.parameters())
+        if needs_grad:
+            self._ensure_grad_buffers()
+            params = [p for p in m.parameters() if p.requires_grad]
+            outs = _NetFn.apply(self, len(xs), *xs, *params)
+        else:
+            outs = self._forward(xs, training, None)
+        outs = tuple(outs)
+        return outs if len(outs) > 1 else outs[0]
+
+    def _bn_forward(self, u, raw, out, res, relu, training, st):
+        """Training-mode BN on a raw conv output whose per-channel stats are already in u.stats."""
+        bn = u.bn
+        rows = raw.rows
+        mom = bn.momentum if bn.momentum is not None else 0.1
+        track = bn.track_running_stats
+        L.call("asf_bn_finalize", L.ptr(u.stats), u.Cout, C.c_double(rows), L.ptr(bn.weight), L.ptr(bn.bias),
+               C.c_float(bn.eps), C.c_float(mom), L.ptr(bn.running_mean) if track else None,
+               L.ptr(bn.running_var) if track else None, L.ptr(bn.num_batches_tracked) if track else None,
+               L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.mean), L.ptr(u.invstd), st)
+        if out is not None:
+            L.call("asf_bn_apply", C.c_void_p(raw.ptr), raw.ld, C.c_void_p(res.ptr) if res is not None else None,
+                   res.ld if res is not None else 0, C.c_void_p(out.ptr), out.ld, out.code, rows, u.Cout,
+                   L.ptr(u.scale), L.ptr(u.shift), int(relu), st)
+
+    def _unit_forward(self, u, training):
+        st = L.stream_ptr()
+        self._prepare_unit(u, training)
+        if u.batch_mode:
+            if u.raw is None:
+                u.raw = Act(u.y.B, u.y.T, u.y.F, u.Cout, self.dtype, self.device, name=u.name + ".raw")
+            u.stats.zero_()
+            if self._tc_ok(u):
+                self._conv_fwd(u, u.raw, dict(stats=u.stats, stats_stride=u.Cout))
+            else:
+                self._conv_fwd(u, u.raw, dict())
+                L.call("asf_channel_stats", C.c_void_p(u.raw.ptr), u.raw.code, u.raw.rows, u.Cout, u.raw.ld,
+                       L.ptr(u.stats), st)
+            self._bn_forward(u, u.raw, u.y, u.res, u.relu, training, st)
+        else:
+            self._conv_fwd(u, u.y, dict(shift=u.shift, res=u.res, relu=u.relu))
+
+    def _forward(self, xs, training, ctx):
+        plan, m = self.plan, self.model
+        st = L.stream_ptr()
+        # stems
+        for p, u in enumerate(plan.stems):
+            xin = xs[p]
+            if xin.dtype != torch.float32:
+                xin = xin.float()
+            u.x.buf.copy_(xin.reshape(u.x.buf.shape))  # (B,1,T,F) fp32 is already channels-last for C = 1
+            self._prepare_unit(u, training)
+            g = u.geom()
+            e = _epilogue()
+            L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), L.F32, L.ptr(u.w_pack), L.F32, C.c_void_p(u.y.ptr),
+                   u.y.code, C.byref(g), C.byref(e), st)
+            if u.batch_mode:
+                u.stats.zero_()
+                L.call("asf_channel_stats", C.c_void_p(u.y.ptr), u.y.code, u.y.rows, u.Cout, u.y.ld, L.ptr(u.stats), st)
+                self._bn_forward(u, u.y, None, None, False, training, st)
+            L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld, u.y.code,
+                   u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+        # stages
+        for kind, item in plan.order:
+            if kind == "fuse":
+                self._unit_forward(item, training)
+            else:
+                if "b1" in item:
+                    self._unit_forward(item["b1"], training)
+                self._unit_forward(item["a"], training)
+                self._unit_forward(item["b"], training)
+                self._unit_forward(item["c"], training)
+        # head
+        head = m.head
+        c_off = 0
+        for p, xa in enumerate(plan.final):
+            L.call("asf_avgpool_fwd", C.c_void_p(xa.ptr), xa.code, xa.B, xa.T * xa.F, xa.C, L.ptr(plan.feat),
+                   plan.feat.shape[1], c_off, st)
+            c_off += xa.C
+        feat = plan.feat
+        plan.drop_mask = None
+        if training and head.dropout_rate > 0.0:
+            keep = 1.0 - head.dropout_rate
+            plan.drop_mask = (torch.rand_like(plan.feat) < keep).float()
+            L.call("asf_scale_mask", L.ptr(plan.feat), L.ptr(plan.drop_mask), L.ptr(plan.feat_drop), plan.feat.numel(),
+                   C.c_float(1.0 / keep), st)
+            feat = plan.feat_drop
+        plan.feat_used = feat
+        outs = []
+        for pr, lg in zip(plan.projs, plan.logits):
+            L.call("asf_sgemm", L.ptr(feat), L.ptr(pr.weight), L.ptr(lg), plan.B, pr.out_features, pr.in_features, 0, 1,
+                   feat.shape[1], pr.in_features, pr.out_features, C.c_float(1.0), C.c_float(0.0), L.ptr(pr.bias), st)
+            if not training:
+                L.call("asf_softmax_rows", L.ptr(lg), plan.B, pr.out_features, pr.out_features, st)
+            outs.append(lg.clone())
+        return outs
+
+    # ------------------------------------------------------------------------------------------ backward
+    def _unit_backward(self, u, dz, need_dx, dx_accumulate, dx_res=None, dx_mask=None):
+        """dz: Act holding dL/d(BN output [+res]) of unit u (already ReLU-masked).  Produces the parameter
+        gradients of u and, when need_dx, u.x.grad (+)= dgrad."""
+        st = L.stream_ptr()
+        bn, conv = u.bn, u.conv
+        if u.batch_mode:
+            rows = dz.rows
+            u.red.zero_()
+            L.call("asf_bn_bwd_reduce", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld, dz.code, rows,
+                   u.Cout, L.ptr(u.mean), L.ptr(u.invstd), L.ptr(u.red), st)
+            gw, acc_w = self._grad_target(bn.weight)
+            gb, acc_b = self._grad_target(bn.bias)
+            if acc_w or acc_b:
+                tmp_w = torch.empty_like(bn.weight) if gw is not None else None
+                tmp_b = torch.empty_like(bn.bias) if gb is not None else None
+            else:
+                tmp_w, tmp_b = gw, gb
+            dconv = u.raw.grad
+            L.call("asf_bn_bwd_apply", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld,
+                   C.c_void_p(dconv.ptr), dconv.ld, dz.code, rows, u.Cout, L.ptr(bn.weight), L.ptr(u.mean),
+                   L.ptr(u.invstd), L.ptr(u.red), C.c_double(rows), L.ptr(tmp_w), L.ptr(tmp_b), st)
+            if acc_w and gw is not None:
+                gw.add_(tmp_w)
+            if acc_b and gb is not None:
+                gb.add_(tmp_b)
+            rscale = None
+        else:
+            dconv = dz
+            rscale = None if u.is_stem else u.scale
+            if bn.weight.requires_grad or bn.bias.requires_grad:
+                raise RuntimeError(
+                    "%s: BN in eval mode with trainable gamma/beta is not supported by the fused backward "
+                    "(use freeze_fn('bn_parameters') together with freeze_fn('bn_statistics'))" % u.name)
+        gview, acc = self._grad_target(conv.weight)
+        if gview is not None:
+            self._conv_wgrad(u, dconv, rscale, gview, acc)
+        if need_dx:
+            self._conv_dgrad(u, dconv, u.x.grad, dx_accumulate, res=dx_res, mask=dx_mask)
+
+    def _backward(self, dlogits):
+        plan, m = self.plan, self.model
+        st = L.stream_ptr()
+        B = plan.B
+        self._dwp.zero_()
+        done = []
+        # ---- head
+        plan.dfeat.zero_()
+        feat = plan.feat_used
+        for pr, dl in zip(plan.projs, dlogits):
+            if dl is None:
+                continue
+            dl = dl.contiguous().float()
+            gw, acc = self._grad_target(pr.weight)
+            if gw is not None:  # dW[j][c] = sum_b dl[b][j] feat[b][c]
+                L.call("asf_sgemm", L.ptr(dl), L.ptr(feat), L.ptr(gw), pr.out_features, pr.in_features, B, 1, 0,
+                       pr.out_features, feat.shape[1], pr.in_features, C.c_float(1.0), C.c_float(1.0 if acc else 0.0),
+                       None, st)
+            gb, accb = self._grad_target(pr.bias)
+            if gb is not None:
+                if accb:
+                    gb.add_(dl.sum(0))
+                else:
+                    gb.copy_(dl.sum(0))
+            # dfeat[b][c] += sum_j dl[b][j] W[j][c]
+            L.call("asf_sgemm", L.ptr(dl), L.ptr(pr.weight), L.ptr(plan.dfeat), B, pr.in_features, pr.out_features, 0, 0,
+                   pr.out_features, pr.in_features, pr.in_features, C.c_float(1.0), C.c_float(1.0), None, st)
+        if plan.drop_mask is not None:
+            keep = 1.0 - m.head.dropout_rate
+            L.call("asf_scale_mask", L.ptr(plan.dfeat), L.ptr(plan.drop_mask), L.ptr(plan.dfeat), plan.dfeat.numel(),
+                   C.c_float(1.0 / keep), st)
+        self._notify(["head"])
+        c_off = 0
+        for xa in plan.final:
+            # gradient w.r.t. the pre-ReLU block output: avg-pool backward masked by (out > 0)
+            L.call("asf_avgpool_bwd", L.ptr(plan.dfeat), plan.dfeat.shape[1], c_off, C.c_void_p(xa.ptr),
+                   C.c_void_p(xa.grad.ptr), xa.code, xa.B, xa.T * xa.F, xa.C, st)
+            c_off += xa.C
+        # which activations already hold a (partial) gradient in this pass
+        written = set(id(xa.full.grad.buf) for xa in plan.final)
+
+        def first_write(act):
+            key = id(act.grad.buf)
+            fresh = key not in written
+            written.add(key)
+            return fresh
+
+        for kind, item in reversed(plan.order):
+            if kind == "fuse":
+                u = item
+                # dz of the lateral = its channel slice of the slow concat gradient (already masked by the
+                # consumer block's last dgrad); dx accumulates into the fast activation's gradient.
+                fresh = first_write(u.x)
+                u.x.grad.zeroed = False
+                # the lateral is always the LAST writer of its (fast) input's gradient: it applies the ReLU mask
+                self._unit_backward(u, u.y.grad, True, not fresh, dx_mask=u.x)
+                self._notify([u.name])
+            else:
+                blk = item
+                xin, out = blk["x"], blk["out"]
+                dz_out = out.grad
+                c, b_, a = blk["c"], blk["b"], blk["a"]
+                # c: dgrad -> d(h_b), masked by h_b > 0
+                self._unit_backward(c, dz_out, True, False, dx_mask=c.x)
+                self._unit_backward(b_, b_.y.grad, True, False, dx_mask=b_.x)
+                fresh = first_write(xin)
+                xg = xin.grad
+                # is this block input also consumed elsewhere later in the backward (lateral of the fast path)?
+                # the mask is applied by the LAST writer; a stage's first fast block is followed (in backward
+                # order) by the lateral conv that reads the same activation, so the mask must wait for it.
+                later = blk.get("mask_later", False)
+                if "b1" in blk:
+                    b1 = blk["b1"]
+                    if fresh and b1.s > 1:
+                        xg.buf.zero_() if xg.parent is None else xg.view().zero_()
+                        xg.zeroed = True
+                        fresh = False
+                    self._unit_backward(b1, dz_out, True, not fresh)
+                    self._unit_backward(a, a.y.grad, True, True, dx_mask=None if later else xin)
+                else:
+                    self._unit_backward(a, a.y.grad, True, not fresh, dx_res=dz_out, dx_mask=None if later else xin)
+                self._notify([blk["name"]])
+        # ---- stems
+        for u in plan.stems:
+            pooled = u.pooled
+            dz = u.y.grad
+            L.call("asf_bn_relu_maxpool_bwd", C.c_void_p(u.y.ptr), C.c_void_p(pooled.grad.ptr), pooled.grad.ld,
+                   C.c_void_p(dz.ptr), dz.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+            if u.batch_mode:
+                u.raw = u.y  # the stem keeps its raw conv output in u.y
+            self._unit_backward(u, dz, False, False)
+        self._notify(["stems"])
+
+    def _notify(self, names):
+        if self.grad_hook is not None:
+            self.grad_hook(self, names)
+
+
+class _NetFn(torch.autograd.Function):
+    """One autograd node for the whole network.  Parameter gradients are written straight into p.grad
+    (views of the engine's flat buffer), so the node returns None for them."""
+
+    @staticmethod
+    def forward(ctx, engine, n_in, *tensors):
+        xs = tensors[:n_in]
+        ctx.engine = engine
+        ctx.n_in = n_in
+        ctx.n_params = len(tensors) - n_in
+        outs = engine._forward(xs, True, ctx)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *dlogits):
+        eng = ctx.engine
+        # lateral-aware mask ordering (computed once per plan)
+        eng._mark_mask_later()
+        eng._backward(list(dlogits))
+        return (None, None) + (None,) * (ctx.n_in + ctx.n_params)
+
+
+def _mark_mask_later(self):
+    plan = self.plan
+    if getattr(plan, "_marked", False):
+        return
+    fuse_inputs = set(id(u.x.buf) for kind, u in plan.order if kind == "fuse")
+    # a block whose input is also read by a lateral conv that runs EARLIER in forward order (i.e. LATER in
+    # backward order) must leave the ReLU mask to that lateral's dgrad... but the lateral's dgrad is strided
+    # in 4 phases that together cover every row, so it can apply the mask.
+    for kind, item in plan.order:
+        if kind == "block" and id(item["x"].buf) in fuse_inputs and item["x"].parent is None:
+            item["mask_later"] = True
+    plan._marked = True
+
+
+Engine._mark_mask_later = _mark_mask_later

@@ -1,0 +1,689 @@
+// BatchNorm statistics / apply / backward, pools, head helpers, weight (re)packing.
+// All kernels are HBM-bound streaming passes: channel index is the fastest-varying thread index so every
+// warp touches contiguous addresses; reductions go warp/block-level first and finish with a few fp32 atomics.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace asf {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// ----------------------------------------------------------------------------------------------- stats
+// block = 256 threads = RP row-lanes x CB channels (CB = min(C,256)); grid.x over row chunks, grid.y over
+// channel blocks.  Each thread streams rows with stride RP, then the block folds its row-lanes in smem.
+template <typename T, bool kBwd>
+__global__ void __launch_bounds__(256) channel_reduce_kernel(const T* __restrict__ a, int64_t ld_a,
+                                                             const T* __restrict__ x, int64_t ld_x, int64_t rows,
+                                                             int C, int CB, int64_t rows_per_block,
+                                                             const float* __restrict__ mean,
+                                                             const float* __restrict__ invstd, float* out) {
+  __shared__ float s0[256], s1[256];
+  const int RP = 256 / CB;
+  const int cl = threadIdx.x % CB, rl = threadIdx.x / CB;
+  const int c = blockIdx.y * CB + cl;
+  float acc0 = 0.f, acc1 = 0.f;
+  if (rl < RP && c < C) {
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    int64_t r1 = r0 + rows_per_block;
+    if (r1 > rows) r1 = rows;
+    float mu = 0.f, is = 1.f;
+    if (kBwd) {
+      mu = mean[c];
+      is = invstd[c];
+    }
+    for (int64_t r = r0 + rl; r < r1; r += RP) {
+      float v = ldf(a + r * ld_a + c);
+      if (kBwd) {
+        float xh = (ldf(x + r * ld_x + c) - mu) * is;
+        acc0 += v;
+        acc1 += v * xh;
+      } else {
+        acc0 += v;
+        acc1 += v * v;
+      }
+    }
+  }
+  s0[threadIdx.x] = acc0;
+  s1[threadIdx.x] = acc1;
+  __syncthreads();
+  if (threadIdx.x < CB && c < C) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int k = 0; k < RP; ++k) {
+      t0 += s0[threadIdx.x + k * CB];
+      t1 += s1[threadIdx.x + k * CB];
+    }
+    atomicAdd(out + c, t0);
+    atomicAdd(out + C + c, t1);
+  }
+}
+
+template <typename T, bool kBwd>
+static int launch_channel_reduce(const T* a, int64_t ld_a, const T* x, int64_t ld_x, int64_t rows, int C,
+                                 const float* mean, const float* invstd, float* out, cudaStream_t st) {
+  int CB = C < 256 ? C : 256;
+  // CB must divide 256 for the row-lane layout; otherwise fall back to one row-lane of 256 channels
+  if (256 % CB != 0) CB = 256;
+  int cblocks = (int)cdiv(C, CB);
+  int64_t target_blocks = 148 * 8 / cblocks;
+  if (target_blocks < 1) target_blocks = 1;
+  int64_t rpb = cdiv(rows, target_blocks);
+  int RP = 256 / CB;
+  if (rpb < RP * 4) rpb = RP * 4;
+  dim3 grid((unsigned)cdiv(rows, rpb), cblocks);
+  channel_reduce_kernel<T, kBwd><<<grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, CB, rpb, mean, invstd, out);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                   float momentum, float* running_mean, float* running_var,
+                                   int64_t* num_batches_tracked, float* scale, float* shift, float* save_mean,
+                                   float* save_invstd) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && num_batches_tracked) *num_batches_tracked += 1;
+  if (c >= C) return;
+  double mean = (double)stats[c] / count;
+  double var = (double)stats[C + c] / count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+  float sc = g * invstd;
+  scale[c] = sc;
+  shift[c] = b - (float)mean * sc;
+  if (save_mean) save_mean[c] = (float)mean;
+  if (save_invstd) save_invstd[c] = invstd;
+  if (running_mean) {
+    double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+  }
+}
+
+__global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                               const float* __restrict__ rm, const float* __restrict__ rv, float eps, int C,
+                               float* scale, float* shift) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float sc = gamma[c] * rsqrtf(rv[c] + eps);
+  // rsqrtf is 2 ulp; use the exact form to match torch's 1/sqrt(var+eps)
+  sc = gamma[c] / sqrtf(rv[c] + eps);
+  scale[c] = sc;
+  shift[c] = beta[c] - rm[c] * sc;
+}
+
+template <typename T>
+__global__ void bn_apply_kernel(const T* __restrict__ x, int64_t ld_x, const T* __restrict__ res, int64_t ld_res,
+                                T* __restrict__ y, int64_t ld_y, int64_t rows, int C,
+                                const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+  int64_t total = rows * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / C;
+    int c = (int)(i - r * C);
+    float v = ldf(x + r * ld_x + c) * scale[c] + shift[c];
+    if (res) v += ldf(res + r * ld_res + c);
+    if (relu) v = fmaxf(v, 0.f);
+    stf(y + r * ld_y + c, v);
+  }
+}
+
+template <typename T>
+__global__ void bn_bwd_apply_kernel(const T* __restrict__ dz, int64_t ld_dz, const T* __restrict__ x, int64_t ld_x,
+                                    T* __restrict__ dx, int64_t ld_dx, int64_t rows, int C,
+                                    const float* __restrict__ gamma, const float* __restrict__ mean,
+                                    const float* __restrict__ invstd, const float* __restrict__ red, float inv_count) {
+  int64_t total = rows * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / C;
+    int c = (int)(i - r * C);
+    float is = invstd[c];
+    float xh = (ldf(x + r * ld_x + c) - mean[c]) * is;
+    float g = gamma ? gamma[c] : 1.f;
+    float v = g * is * (ldf(dz + r * ld_dz + c) - red[c] * inv_count - xh * red[C + c] * inv_count);
+    stf(dx + r * ld_dx + c, v);
+  }
+}
+
+__global__ void copy_dgamma_dbeta_kernel(const float* __restrict__ red, int C, float* dgamma, float* dbeta) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (dbeta) dbeta[c] = red[c];
+  if (dgamma) dgamma[c] = red[C + c];
+}
+
+template <typename T>
+__global__ void relu_bwd_kernel(const T* __restrict__ a, int64_t ld_a, const T* __restrict__ b, int64_t ld_b,
+                                const T* __restrict__ mask, int64_t ld_mask, T* __restrict__ y, int64_t ld_y,
+                                int64_t rows, int C) {
+  int64_t total = rows * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / C;
+    int c = (int)(i - r * C);
+    float v = ldf(a + r * ld_a + c);
+    if (b) v += ldf(b + r * ld_b + c);
+    if (mask && !(ldf(mask + r * ld_mask + c) > 0.f)) v = 0.f;
+    stf(y + r * ld_y + c, v);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------- pools
+template <typename T>
+__global__ void bn_relu_maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t ld_y, int B, int Tn,
+                                           int F, int C, int To, int Fo, const float* __restrict__ scale,
+                                           const float* __restrict__ shift) {
+  int64_t total = (int64_t)B * To * Fo * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int c = (int)(i % C);
+    int64_t r = i / C;
+    int fo = (int)(r % Fo);
+    r /= Fo;
+    int to = (int)(r % To);
+    int b = (int)(r / To);
+    float sc = scale[c], sh = shift[c];
+    float m = -INFINITY;
+    for (int dt = -1; dt <= 1; ++dt) {
+      int t = 2 * to + dt;
+      if (t < 0 || t >= Tn) continue;
+      for (int df = -1; df <= 1; ++df) {
+        int f = 2 * fo + df;
+        if (f < 0 || f >= F) continue;
+        float v = fmaxf(ldf(x + (((int64_t)b * Tn + t) * F + f) * C + c) * sc + sh, 0.f);
+        // the pooled activation is what the stored dtype can hold
+        m = fmaxf(m, v);
+      }
+    }
+    stf(y + (i / C) * ld_y + c, m);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ bool window_argmax_is(const T* __restrict__ x, int b, int Tn, int F, int C, int c, int to,
+                                                 int fo, float sc, float sh, int t_self, int f_self) {
+  float m = -INFINITY;
+  int at = -1, af = -1;
+  for (int dt = -1; dt <= 1; ++dt) {
+    int t = 2 * to + dt;
+    if (t < 0 || t >= Tn) continue;
+    for (int df = -1; df <= 1; ++df) {
+      int f = 2 * fo + df;
+      if (f < 0 || f >= F) continue;
+      float v = fmaxf(ldf(x + (((int64_t)b * Tn + t) * F + f) * C + c) * sc + sh, 0.f);
+      if (v > m) {  // strict: first occurrence in (t, f) scan order wins, as in torch
+        m = v;
+        at = t;
+        af = f;
+      }
+    }
+  }
+  return at == t_self && af == f_self;
+}
+
+template <typename T>
+__global__ void bn_relu_maxpool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, int64_t ld_dy,
+                                           T* __restrict__ dz, int B, int Tn, int F, int C, int To, int Fo,
+                                           const float* __restrict__ scale, const float* __restrict__ shift) {
+  int64_t total = (int64_t)B * Tn * F * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int c = (int)(i % C);
+    int64_t r = i / C;
+    int f = (int)(r % F);
+    r /= F;
+    int t = (int)(r % Tn);
+    int b = (int)(r / Tn);
+    float sc = scale[c], sh = shift[c];
+    float a = ldf(x + i) * sc + sh;
+    float g = 0.f;
+    if (a > 0.f) {
+      int to0 = t >> 1, to1 = (t + 1) >> 1;  // windows containing t: ceil((t-1)/2) .. floor((t+1)/2)
+      int fo0 = f >> 1, fo1 = (f + 1) >> 1;
+      if (t & 1) to0 = (t - 1) >> 1; else to1 = to0;
+      if (f & 1) fo0 = (f - 1) >> 1; else fo1 = fo0;
+      for (int to = to0; to <= to1; ++to) {
+        if (to >= To) continue;
+        for (int fo = fo0; fo <= fo1; ++fo) {
+          if (fo >= Fo) continue;
+          if (window_argmax_is(x, b, Tn, F, C, c, to, fo, sc, sh, t, f))
+            g += ldf(dy + (((int64_t)b * To + to) * Fo + fo) * ld_dy + c);
+        }
+      }
+    }
+    stf(dz + i, g);
+  }
+}
+
+template <typename T>
+__global__ void avgpool_fwd_kernel(const T* __restrict__ x, int B, int P, int C, float* __restrict__ feat,
+                                   int64_t ld_feat, int c_off) {
+  // block (32 channels x 8 position-lanes): coalesced along channels, position-lanes folded in smem
+  __shared__ float s[8][33];
+  int c = blockIdx.x * 32 + threadIdx.x;
+  int b = blockIdx.y;
+  float acc = 0.f;
+  if (c < C)
+    for (int p = threadIdx.y; p < P; p += 8) acc += ldf(x + ((int64_t)b * P + p) * C + c);
+  s[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    float t = 0.f;
+    for (int k = 0; k < 8; ++k) t += s[k][threadIdx.x];
+    feat[(int64_t)b * ld_feat + c_off + c] = t / (float)P;
+  }
+}
+
+template <typename T>
+__global__ void avgpool_bwd_kernel(const float* __restrict__ dfeat, int64_t ld_feat, int c_off,
+                                   const T* __restrict__ mask, T* __restrict__ dx, int B, int P, int C) {
+  int64_t total = (int64_t)B * P * C;
+  float inv = 1.f / (float)P;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int c = (int)(i % C);
+    int b = (int)(i / ((int64_t)P * C));
+    float v = dfeat[(int64_t)b * ld_feat + c_off + c] * inv;
+    if (mask && !(ldf(mask + i) > 0.f)) v = 0.f;
+    stf(dx + i, v);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------- head
+// tb = 1: both operands contiguous along K -> one warp per output, lanes stride K (coalesced).
+__global__ void sgemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ Bm, float* __restrict__ C,
+                                int M, int N, int K, int ta, int64_t lda, int64_t ldb, int64_t ldc, float alpha,
+                                float beta, const float* __restrict__ bias) {
+  int warp = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (warp >= M * N) return;
+  int m = warp / N, n = warp - m * N;
+  float acc = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    float a = ta ? A[(int64_t)k * lda + m] : A[(int64_t)m * lda + k];
+    acc += a * Bm[(int64_t)n * ldb + k];
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    float v = alpha * acc + (bias ? bias[n] : 0.f);
+    if (beta != 0.f) v += beta * C[(int64_t)m * ldc + n];
+    C[(int64_t)m * ldc + n] = v;
+  }
+}
+// tb = 0: B row-major [K][N] -> one thread per output, n fastest (coalesced on B and C, A broadcast).
+__global__ void sgemm_nn_kernel(const float* __restrict__ A, const float* __restrict__ Bm, float* __restrict__ C,
+                                int M, int N, int K, int ta, int64_t lda, int64_t ldb, int64_t ldc, float alpha,
+                                float beta, const float* __restrict__ bias) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)M * N) return;
+  int m = (int)(i / N), n = (int)(i - (int64_t)m * N);
+  float acc = 0.f;
+  for (int k = 0; k < K; ++k) {
+    float a = ta ? A[(int64_t)k * lda + m] : A[(int64_t)m * lda + k];
+    acc += a * Bm[(int64_t)k * ldb + n];
+  }
+  float v = alpha * acc + (bias ? bias[n] : 0.f);
+  if (beta != 0.f) v += beta * C[(int64_t)m * ldc + n];
+  C[(int64_t)m * ldc + n] = v;
+}
+
+__global__ void softmax_rows_kernel(float* x, int rows, int n, int64_t ld) {
+  int warp = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  float* p = x + (int64_t)warp * ld;
+  float m = -INFINITY;
+  for (int i = lane; i < n; i += 32) m = fmaxf(m, p[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  float s = 0.f;
+  for (int i = lane; i < n; i += 32) s += expf(p[i] - m);
+  s = warp_sum(s);
+  float inv = 1.f / s;
+  for (int i = lane; i < n; i += 32) p[i] = expf(p[i] - m) * inv;
+}
+
+__global__ void scale_mask_kernel(const float* __restrict__ x, const float* __restrict__ mask, float* y, int64_t n,
+                                  float inv_keep) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = x[i] * mask[i] * inv_keep;
+}
+
+__global__ void gather_rows_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                   const int32_t* __restrict__ idx, int B, int T_src, int n_idx, int F) {
+  int64_t total = (int64_t)B * n_idx * F;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int f = (int)(i % F);
+    int64_t r = i / F;
+    int j = (int)(r % n_idx);
+    int b = (int)(r / n_idx);
+    dst[i] = src[((int64_t)b * T_src + idx[j]) * F + f];
+  }
+}
+
+// ----------------------------------------------------------------------------------------------- weights
+template <typename T>
+__global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ p, int O, int I, int taps,
+                                   const float* __restrict__ rscale, int transpose) {
+  int64_t total = (int64_t)O * I * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    // i indexes the DESTINATION so writes are coalesced
+    int o, c, tp;
+    if (!transpose) {  // [O][taps][I]
+      c = (int)(i % I);
+      int64_t r = i / I;
+      tp = (int)(r % taps);
+      o = (int)(r / taps);
+    } else {  // [I][taps][O]
+      o = (int)(i % O);
+      int64_t r = i / O;
+      tp = (int)(r % taps);
+      c = (int)(r / taps);
+    }
+    float v = w[((int64_t)o * I + c) * taps + tp];
+    if (rscale) v *= rscale[o];
+    stf(p + i, v);
+  }
+}
+
+__global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int I, int taps,
+                                    const float* __restrict__ rscale, int accumulate) {
+  int64_t total = (int64_t)O * I * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int tp = (int)(i % taps);
+    int64_t r = i / taps;
+    int c = (int)(r % I);
+    int o = (int)(r / I);
+    float v = dwp[((int64_t)o * taps + tp) * I + c];
+    if (rscale) v *= rscale[o];
+    if (accumulate) v += dw[i];
+    dw[i] = v;
+  }
+}
+
+// Stem weight gradient (C_in = 1): dw[n][tap] = sum_rows dout[row][n] * in[row shifted by tap].
+// block = 256 threads = RL row-lanes x Cout channels; each thread keeps all taps (<= 35) in registers while it
+// streams its rows (dout coalesced along n, the input sample is a warp broadcast); row-lanes are folded in smem
+// and one atomic per (n, tap) per block finishes the reduction.
+constexpr int STEM_MAX_TAPS = 35;
+template <typename TD>
+__global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ in, const TD* __restrict__ dout,
+                                                         float* __restrict__ dw, asf_conv_geom_t g,
+                                                         int64_t rows_per_block) {
+  __shared__ float red[256];
+  const int taps = g.kt * g.kf;
+  const int n = threadIdx.x % g.Cout, rl = threadIdx.x / g.Cout, RL = 256 / g.Cout;
+  const int64_t rows = (int64_t)g.B * g.Tout * g.Fout;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < rows) ? r0 + rows_per_block : rows;
+  float acc[STEM_MAX_TAPS];
+#pragma unroll
+  for (int i = 0; i < STEM_MAX_TAPS; ++i) acc[i] = 0.f;
+  if (rl < RL) {
+    for (int64_t row = r0 + rl; row < r1; row += RL) {
+      const int fo = (int)(row % g.Fout);
+      const int64_t r2 = row / g.Fout;
+      const int to = (int)(r2 % g.Tout);
+      const int b = (int)(r2 / g.Tout);
+      const float d = ldf(dout + row * g.ld_out + n);
+      const float* ib = in + (int64_t)b * g.Tin * g.Fin;
+#pragma unroll
+      for (int tp = 0; tp < STEM_MAX_TAPS; ++tp) {
+        if (tp < taps) {
+          const int it = tp / g.kf, jf = tp - it * g.kf;
+          const int t = to * g.st + it - g.pt, f = fo * g.sf + jf - g.pf;
+          if (t >= 0 && t < g.Tin && f >= 0 && f < g.Fin) acc[tp] = fmaf(d, ib[(int64_t)t * g.Fin + f], acc[tp]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int tp = 0; tp < STEM_MAX_TAPS; ++tp) {
+    if (tp < taps) {
+      __syncthreads();
+      red[threadIdx.x] = acc[tp];
+      __syncthreads();
+      if (threadIdx.x < g.Cout) {
+        float t = 0.f;
+        for (int k = 0; k < RL; ++k) t += red[threadIdx.x + k * g.Cout];
+        atomicAdd(dw + (int64_t)threadIdx.x * taps + tp, t);
+      }
+    }
+  }
+}
+
+static inline unsigned ew_grid(int64_t total) {
+  int64_t g = cdiv(total, 256);
+  int64_t cap = 148 * 16;
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace asf
+
+using namespace asf;
+
+extern "C" {
+
+const char* asf_last_error(void) { return asf::g_err; }
+int asf_version(void) { return 100; }
+
+int asf_device_is_sm100(void) {
+  int dev = 0;
+  cudaDeviceProp prop;
+  ASF_CUDA(cudaGetDevice(&dev));
+  ASF_CUDA(cudaGetDeviceProperties(&prop, dev));
+  return prop.major == 10 ? 1 : 0;
+}
+
+int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream) {
+  ASF_CHECK_ARG(x && stats && rows > 0 && C > 0 && ld >= C, "asf_channel_stats: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, false>((const T*)x, ld, (const T*)nullptr, 0, rows, C,
+                                                                      nullptr, nullptr, stats, (cudaStream_t)stream)));
+}
+
+int asf_bn_finalize(const float* stats, int C, double count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                    float* scale, float* shift, float* save_mean, float* save_invstd, void* stream) {
+  ASF_CHECK_ARG(stats && scale && shift && C > 0 && count > 0, "asf_bn_finalize: bad arguments");
+  bn_finalize_kernel<<<(unsigned)cdiv(C, 128), 128, 0, (cudaStream_t)stream>>>(
+      stats, C, count, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked, scale, shift,
+      save_mean, save_invstd);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                float eps, int C, float* scale, float* shift, void* stream) {
+  ASF_CHECK_ARG(gamma && beta && running_mean && running_var && scale && shift && C > 0, "asf_bn_fold: bad arguments");
+  bn_fold_kernel<<<(unsigned)cdiv(C, 128), 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps,
+                                                                          C, scale, shift);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
+                 int64_t rows, int C, const float* scale, const float* shift, int relu, void* stream) {
+  ASF_CHECK_ARG(x && y && scale && shift && rows > 0 && C > 0, "asf_bn_apply: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    bn_apply_kernel<T><<<ew_grid(rows * C), 256, 0, (cudaStream_t)stream>>>((const T*)x, ld_x, (const T*)res, ld_res,
+                                                                          (T*)y, ld_y, rows, C, scale, shift, relu);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
+                      const float* mean, const float* invstd, float* red, void* stream) {
+  ASF_CHECK_ARG(dz && x && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_reduce: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, true>((const T*)dz, ld_dz, (const T*)x, ld_x, rows, C,
+                                                                     mean, invstd, red, (cudaStream_t)stream)));
+}
+
+int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
+                     int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
+                     const float* red, double count, float* dgamma, float* dbeta, void* stream) {
+  ASF_CHECK_ARG(dz && x && dx && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_apply: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dgamma || dbeta) {
+    copy_dgamma_dbeta_kernel<<<(unsigned)cdiv(C, 128), 128, 0, st>>>(red, C, dgamma, dbeta);
+    ASF_LAUNCH_CHECK();
+  }
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    bn_bwd_apply_kernel<T><<<ew_grid(rows * C), 256, 0, st>>>((const T*)dz, ld_dz, (const T*)x, ld_x, (T*)dx, ld_dx,
+                                                            rows, C, gamma, mean, invstd, red, (float)(1.0 / count));
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const void* mask, int64_t ld_mask,
+                 void* y, int64_t ld_y, int dtype, int64_t rows, int C, void* stream) {
+  ASF_CHECK_ARG(a && y && rows > 0 && C > 0, "asf_relu_bwd: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    relu_bwd_kernel<T><<<ew_grid(rows * C), 256, 0, (cudaStream_t)stream>>>(
+        (const T*)a, ld_a, (const T*)b, ld_b, (const T*)mask, ld_mask, (T*)y, ld_y, rows, C);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int B, int T, int F, int C,
+                            const float* scale, const float* shift, void* stream) {
+  ASF_CHECK_ARG(x && y && scale && shift && B > 0 && T > 0 && F > 0 && C > 0, "asf_bn_relu_maxpool_fwd: bad arguments");
+  int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  ASF_DISPATCH_DTYPE(dtype, Tt, {
+    bn_relu_maxpool_fwd_kernel<Tt><<<ew_grid((int64_t)B * To * Fo * C), 256, 0, (cudaStream_t)stream>>>(
+        (const Tt*)x, (Tt*)y, ld_y, B, T, F, C, To, Fo, scale, shift);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_bn_relu_maxpool_bwd(const void* x, const void* dy, int64_t ld_dy, void* dz, int dtype, int B, int T, int F,
+                            int C, const float* scale, const float* shift, void* stream) {
+  ASF_CHECK_ARG(x && dy && dz && scale && shift && B > 0 && T > 0 && F > 0 && C > 0,
+                "asf_bn_relu_maxpool_bwd: bad arguments");
+  int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  ASF_DISPATCH_DTYPE(dtype, Tt, {
+    bn_relu_maxpool_bwd_kernel<Tt><<<ew_grid((int64_t)B * T * F * C), 256, 0, (cudaStream_t)stream>>>(
+        (const Tt*)x, (const Tt*)dy, ld_dy, (Tt*)dz, B, T, F, C, To, Fo, scale, shift);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_avgpool_fwd(const void* x, int dtype, int B, int P, int C, float* feat, int64_t ld_feat, int c_off,
+                    void* stream) {
+  ASF_CHECK_ARG(x && feat && B > 0 && P > 0 && C > 0, "asf_avgpool_fwd: bad arguments");
+  dim3 grid((unsigned)cdiv(C, 32), B), block(32, 8);
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    avgpool_fwd_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>((const T*)x, B, P, C, feat, ld_feat, c_off);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_avgpool_bwd(const float* dfeat, int64_t ld_feat, int c_off, const void* mask, void* dx, int dtype, int B,
+                    int P, int C, void* stream) {
+  ASF_CHECK_ARG(dfeat && dx && B > 0 && P > 0 && C > 0, "asf_avgpool_bwd: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    avgpool_bwd_kernel<T><<<ew_grid((int64_t)B * P * C), 256, 0, (cudaStream_t)stream>>>(dfeat, ld_feat, c_off,
+                                                                                       (const T*)mask, (T*)dx, B, P, C);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_sgemm(const float* A, const float* Bm, float* C, int M, int N, int K, int ta, int tb, int64_t lda,
+              int64_t ldb, int64_t ldc, float alpha, float beta, const float* bias, void* stream) {
+  ASF_CHECK_ARG(A && Bm && C && M > 0 && N > 0 && K > 0, "asf_sgemm: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (tb) {
+    int64_t threads = (int64_t)M * N * 32;
+    sgemm_nt_kernel<<<(unsigned)cdiv(threads, 256), 256, 0, st>>>(A, Bm, C, M, N, K, ta, lda, ldb, ldc, alpha, beta,
+                                                                  bias);
+  } else {
+    sgemm_nn_kernel<<<(unsigned)cdiv((int64_t)M * N, 256), 256, 0, st>>>(A, Bm, C, M, N, K, ta, lda, ldb, ldc, alpha,
+                                                                         beta, bias);
+  }
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_softmax_rows(float* x, int rows, int n, int64_t ld, void* stream) {
+  ASF_CHECK_ARG(x && rows > 0 && n > 0, "asf_softmax_rows: bad arguments");
+  softmax_rows_kernel<<<(unsigned)cdiv((int64_t)rows * 32, 256), 256, 0, (cudaStream_t)stream>>>(x, rows, n, ld);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_scale_mask(const float* x, const float* mask, float* y, int64_t n, float inv_keep, void* stream) {
+  ASF_CHECK_ARG(x && mask && y && n > 0, "asf_scale_mask: bad arguments");
+  scale_mask_kernel<<<(unsigned)cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(x, mask, y, n, inv_keep);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_gather_rows(const float* src, float* dst, const int32_t* idx, int B, int T_src, int n_idx, int F,
+                    void* stream) {
+  ASF_CHECK_ARG(src && dst && idx && B > 0 && n_idx > 0 && F > 0, "asf_gather_rows: bad arguments");
+  gather_rows_kernel<<<ew_grid((int64_t)B * n_idx * F), 256, 0, (cudaStream_t)stream>>>(src, dst, idx, B, T_src,
+                                                                                      n_idx, F);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_pack_weight(const float* w_oihw, void* packed, int dtype, int O, int I, int taps, const float* rscale,
+                    void* stream) {
+  ASF_CHECK_ARG(w_oihw && packed && O > 0 && I > 0 && taps > 0, "asf_pack_weight: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    pack_weight_kernel<T><<<ew_grid((int64_t)O * I * taps), 256, 0, (cudaStream_t)stream>>>(w_oihw, (T*)packed, O, I,
+                                                                                         taps, rscale, 0);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_pack_weight_t(const float* w_oihw, void* packed, int dtype, int O, int I, int taps, const float* rscale,
+                      void* stream) {
+  ASF_CHECK_ARG(w_oihw && packed && O > 0 && I > 0 && taps > 0, "asf_pack_weight_t: bad arguments");
+  ASF_DISPATCH_DTYPE(dtype, T, {
+    pack_weight_kernel<T><<<ew_grid((int64_t)O * I * taps), 256, 0, (cudaStream_t)stream>>>(w_oihw, (T*)packed, O, I,
+                                                                                         taps, rscale, 1);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_oihw, const asf_conv_geom_t* g,
+                   int accumulate, void* stream) {
+  ASF_CHECK_ARG(in && dout && dw_oihw && g, "asf_stem_wgrad: null pointer");
+  ASF_CHECK_ARG(g->Cin == 1 && g->kt * g->kf <= STEM_MAX_TAPS && g->Cout <= 256 && 256 % g->Cout == 0,
+                "asf_stem_wgrad: needs Cin == 1, <= %d taps, Cout dividing 256", STEM_MAX_TAPS);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int taps = g->kt * g->kf;
+  if (!accumulate) ASF_CUDA(cudaMemsetAsync(dw_oihw, 0, sizeof(float) * (size_t)g->Cout * taps, st));
+  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
+  int64_t blocks = 148 * 4;
+  int64_t rpb = cdiv(rows, blocks);
+  const int RL = 256 / g->Cout;
+  if (rpb < RL) rpb = RL;
+  blocks = cdiv(rows, rpb);
+  ASF_DISPATCH_DTYPE(dout_dtype, TD, {
+    stem_wgrad_kernel<TD><<<(unsigned)blocks, 256, 0, st>>>(in, (const TD*)dout, dw_oihw, *g, rpb);
+    ASF_LAUNCH_CHECK();
+    return 0;
+  });
+}
+
+int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
+                     int accumulate, void* stream) {
+  ASF_CHECK_ARG(dwp && dw_oihw && O > 0 && I > 0 && taps > 0, "asf_unpack_wgrad: bad arguments");
+  unpack_wgrad_kernel<<<ew_grid((int64_t)O * I * taps), 256, 0, (cudaStream_t)stream>>>(dwp, dw_oihw, O, I, taps,
+                                                                                      rscale, accumulate);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,773 @@
+// tap-GEMM: the implicit-GEMM convolution engine of the hot path, written directly against the Blackwell
+// (sm_100a) execution model -- TMA (cp.async.bulk.tensor) stages bf16 operand tiles into 128B-swizzled shared
+// memory, ONE elected thread issues tcgen05.mma (UMMA 128xNx16, kind::f16) with fp32 accumulators in TMEM, and
+// four epilogue warps drain TMEM with tcgen05.ld and apply the fused BN/ReLU/residual/mask/stats epilogue.
+//
+//   mode 0 (forward conv, dgrad):  D[m][n] = sum_tap sum_c A[coord(m)+off(tap)][c] * W[n][tap][c]
+//        persistent CTAs (one per SM), 128 x BLOCK_N output tiles, double-buffered TMEM accumulators so the
+//        epilogue of tile i overlaps the MMAs of tile i+1, S-stage smem ring (full/empty mbarriers).
+//        Convolution padding = TMA out-of-bounds zero fill; taps = coordinate offsets on the tensor map;
+//        stride-2 / stride-4 convs = a parity / phase dimension in the tensor map.  No im2col, no halo copies.
+//   mode 1 (wgrad): dW[n][tap][c] += sum_rows Y[row][n] * X[row+off(tap)][c]; both operands are read straight from
+//        the channels-last activations as MN-major UMMA operands (rows are the GEMM K), split over row tiles
+//        across CTAs and finished with fp32 atomics.
+//
+// Replaces cuDNN conv fwd/dgrad/wgrad + the separate BN / ReLU / add / cat kernels behind
+//   /root/reference/audio_slowfast/models/resnet_helper.py:170-225, :310-341 and audio_model_builder.py:90-111.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace asf {
+
+// ------------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.b32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a lost arrival turns into a trap (reported as a launch failure) instead of a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("asf tapgemm: mbarrier wait timeout tag=%d block=%d thread=%d parity=%u\n", tag, (int)blockIdx.x,
+             (int)threadIdx.x, parity);
+      __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void tma_load(const CUtensorMap* tm, uint64_t* bar, void* dst, int rank, int c0, int c1,
+                                         int c2, int c3, int c4) {
+  const uint32_t d = smem_u32(dst), b = smem_u32(bar);
+  const uint64_t t = (uint64_t)tm;
+  switch (rank) {
+    case 2:
+      asm volatile(
+          "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1) : "memory");
+      break;
+    case 3:
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2) : "memory");
+      break;
+    case 4:
+      asm volatile(
+          "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+      break;
+    default:
+      asm volatile(
+          "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
+      break;
+  }
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)tm) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on `bar` once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// shared-memory matrix descriptor, 128B swizzle (layout_type 2), descriptor version 1 (Blackwell)
+__device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// instruction descriptor: D fp32, A/B bf16, M x N, majors (0 = K-major, 1 = MN-major)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------ parameters
+constexpr int TG_MAX_STAGES = 8;
+constexpr int TG_BLOCK_M = 128;
+constexpr int TG_KC = 64;                 // bf16 elements per 128B swizzle row
+constexpr int TG_A_BYTES = TG_BLOCK_M * 128;
+constexpr int TG_THREADS = 192;           // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2..5 epilogue
+constexpr int TG_SMEM_BUDGET = 200 * 1024;
+
+struct TgParams {
+  CUtensorMap tm_a;  // mode 0: activations (A operand).   mode 1: X (activations, UMMA B operand)
+  CUtensorMap tm_b;  // mode 0: weights [K][taps_w][N].     mode 1: Y (output grads, UMMA A operand)
+  int rank_a, rank_b;
+  int m_ext[3], m_log2[3], m_to_a[3], m_tiles[3], y_m_to_a[3];
+  int m_tiles_total;
+  int ntaps;
+  int a_off[ASF_MAX_TAPS][4];
+  int b_tap[ASF_MAX_TAPS];
+  int K, N, kchunks, block_n, n_tiles, stages;
+  // mode 0 output
+  void* out;
+  int out_bf16;
+  int vec_ok;
+  long long ld_out;
+  long long o_stride[3];
+  asf_epilogue_t epi;
+  // mode 1
+  float* dwp;
+  int ntaps_w, ksplit, c_tiles, r_tiles;
+};
+
+struct TgShared {
+  uint64_t full[TG_MAX_STAGES];
+  uint64_t empty[TG_MAX_STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void tile_coords(const TgParams& p, int m_tile, int start[3]) {
+  int i0 = m_tile % p.m_tiles[0];
+  int r = m_tile / p.m_tiles[0];
+  int i1 = r % p.m_tiles[1];
+  int i2 = r / p.m_tiles[1];
+  start[0] = i0 << p.m_log2[0];
+  start[1] = i1 << p.m_log2[1];
+  start[2] = i2 << p.m_log2[2];
+}
+
+// ------------------------------------------------------------------------------------------------ mode 0
+__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid_constant__ TgParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int b_bytes = p.block_n * 128;
+  const int stage_bytes = TG_A_BYTES + b_bytes;
+  TgShared* sh = (TgShared*)(smem + (size_t)p.stages * stage_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.m_tiles_total * p.n_tiles;
+  const int kiters = p.ntaps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_a);
+    tma_prefetch_desc(&p.tm_b);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&sh->full[s], 1);
+      mbar_init(&sh->empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sh->tmem_full[i], 1);
+      mbar_init(&sh->tmem_empty[i], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sh->tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh->tmem_base;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+        int st[3];
+        tile_coords(p, m_tile, st);
+        int base[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          if (p.m_to_a[j] > 0) base[p.m_to_a[j]] = st[j];
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int c1 = base[1] + p.a_off[tap][0], c2 = base[2] + p.a_off[tap][1], c3 = base[3] + p.a_off[tap][2],
+                    c4 = base[4] + p.a_off[tap][3];
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            mbar_wait(&sh->empty[s], ph ^ 1, 1);
+            uint8_t* sa = smem + (size_t)s * stage_bytes;
+            mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
+            tma_load(&p.tm_a, &sh->full[s], sa, p.rank_a, kc * TG_KC, c1, c2, c3, c4);
+            tma_load(&p.tm_b, &sh->full[s], sa + TG_A_BYTES, 3, kc * TG_KC, p.b_tap[tap], n_tile * p.block_n, 0, 0);
+            if (++s == p.stages) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(TG_BLOCK_M, p.block_n, 0, 0);
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&sh->tmem_empty[buf], ((it >> 1) & 1) ^ 1, 2);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 256);
+        for (int ki = 0; ki < kiters; ++ki) {
+          mbar_wait(&sh->full[s], ph, 3);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint64_t adesc = make_sdesc(sa, 16, 1024);
+          const uint64_t bdesc = make_sdesc(sa + TG_A_BYTES, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < TG_KC / 16; ++k)  // +32 bytes (2 x 16B units) per UMMA_K=16 step inside the swizzle row
+            umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (ki | k) != 0);
+          umma_commit(&sh->empty[s]);
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&sh->tmem_full[buf]);
+      }
+    }
+  } else {
+    // ===== epilogue warps (TMEM lane quarter = warp % 4) =====
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    const int r1 = r & ((1 << p.m_log2[0]) - 1);
+    const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
+    const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
+    const asf_epilogue_t& e = p.epi;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+      int st[3];
+      tile_coords(p, m_tile, st);
+      const int m1 = st[0] + r1, m2 = st[1] + r2, m3 = st[2] + r3;
+      const bool valid = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
+      const long long orow = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
+      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
+      tc_fence_after();
+      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
+      const int n0 = n_tile * p.block_n;
+      for (int ch = 0; ch < p.block_n / 16; ++ch) {
+        const int nb = n0 + ch * 16;
+        if (nb >= p.N) break;
+        float v[16];
+        tmem_ld16(taddr0 + (uint32_t)(ch * 16), v);
+        const bool full16 = p.vec_ok && (nb + 16 <= p.N);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = nb + j;
+          if (n < p.N) {
+            if (e.scale) v[j] *= e.scale[n];
+            if (e.shift) v[j] += e.shift[n];
+          } else {
+            v[j] = 0.f;
+          }
+        }
+        if (valid) {
+          if (p.out_bf16) {
+            bf16* o = (bf16*)p.out + orow * p.ld_out + nb;
+            if (full16) {
+              if (e.res) {
+                const uint4* rp = (const uint4*)((const bf16*)e.res + orow * e.ld_res + nb);
+                uint4 q0 = rp[0], q1 = rp[1];
+                const bf16* rb0 = (const bf16*)&q0;
+                const bf16* rb1 = (const bf16*)&q1;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { v[j] += __bfloat162float(rb0[j]); v[8 + j] += __bfloat162float(rb1[j]); }
+              }
+              if (e.accumulate) {
+                const uint4* rp = (const uint4*)o;
+                uint4 q0 = rp[0], q1 = rp[1];
+                const bf16* rb0 = (const bf16*)&q0;
+                const bf16* rb1 = (const bf16*)&q1;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { v[j] += __bfloat162float(rb0[j]); v[8 + j] += __bfloat162float(rb1[j]); }
+              }
+              if (e.relu) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+              }
+              if (e.mask) {
+                const uint4* rp = (const uint4*)((const bf16*)e.mask + orow * e.ld_mask + nb);
+                uint4 q0 = rp[0], q1 = rp[1];
+                const bf16* rb0 = (const bf16*)&q0;
+                const bf16* rb1 = (const bf16*)&q1;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  if (!(__bfloat162float(rb0[j]) > 0.f)) v[j] = 0.f;
+                  if (!(__bfloat162float(rb1[j]) > 0.f)) v[8 + j] = 0.f;
+                }
+              }
+              uint4 w0, w1;
+              __nv_bfloat162* wb0 = (__nv_bfloat162*)&w0;
+              __nv_bfloat162* wb1 = (__nv_bfloat162*)&w1;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                wb0[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                wb1[j] = __floats2bfloat162_rn(v[8 + 2 * j], v[8 + 2 * j + 1]);
+              }
+              ((uint4*)o)[0] = w0;
+              ((uint4*)o)[1] = w1;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const int n = nb + j;
+                if (n < p.N) {
+                  if (e.res) v[j] += __bfloat162float(((const bf16*)e.res)[orow * e.ld_res + n]);
+                  if (e.accumulate) v[j] += __bfloat162float(o[j]);
+                  if (e.relu) v[j] = fmaxf(v[j], 0.f);
+                  if (e.mask && !(__bfloat162float(((const bf16*)e.mask)[orow * e.ld_mask + n]) > 0.f)) v[j] = 0.f;
+                  o[j] = __float2bfloat16_rn(v[j]);
+                }
+              }
+            }
+          } else {
+            float* o = (float*)p.out + orow * p.ld_out + nb;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int n = nb + j;
+              if (n < p.N) {
+                if (e.res) v[j] += ((const float*)e.res)[orow * e.ld_res + n];
+                if (e.accumulate) v[j] += o[j];
+                if (e.relu) v[j] = fmaxf(v[j], 0.f);
+                if (e.mask && !(((const float*)e.mask)[orow * e.ld_mask + n] > 0.f)) v[j] = 0.f;
+                o[j] = v[j];
+              }
+            }
+          }
+        }
+        if (e.stats) {
+          // per-channel sum / sum of squares over the 32 rows of this warp: recursive-halving transpose-reduce
+          // (16 shuffles per quantity instead of 80), then one atomic per channel from the even lanes.
+          float a[16], q[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float x = valid ? v[j] : 0.f;
+            a[j] = x;
+            q[j] = x * x;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const bool up = lane & 16;
+            const float sa_ = up ? a[i] : a[i + 8], ka = up ? a[i + 8] : a[i];
+            const float sq_ = up ? q[i] : q[i + 8], kq = up ? q[i + 8] : q[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 16);
+            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 16);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const bool up = lane & 8;
+            const float sa_ = up ? a[i] : a[i + 4], ka = up ? a[i + 4] : a[i];
+            const float sq_ = up ? q[i] : q[i + 4], kq = up ? q[i + 4] : q[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 8);
+            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 8);
+          }
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const bool up = lane & 4;
+            const float sa_ = up ? a[i] : a[i + 2], ka = up ? a[i + 2] : a[i];
+            const float sq_ = up ? q[i] : q[i + 2], kq = up ? q[i + 2] : q[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 4);
+            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 4);
+          }
+          {
+            const bool up = lane & 2;
+            const float sa_ = up ? a[0] : a[1], ka = up ? a[1] : a[0];
+            const float sq_ = up ? q[0] : q[1], kq = up ? q[1] : q[0];
+            a[0] = ka + __shfl_xor_sync(0xffffffffu, sa_, 2);
+            q[0] = kq + __shfl_xor_sync(0xffffffffu, sq_, 2);
+          }
+          a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
+          q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
+          const int jch = (((lane >> 4) & 1) << 3) | (((lane >> 3) & 1) << 2) | (((lane >> 2) & 1) << 1) | ((lane >> 1) & 1);
+          const int n = nb + jch;
+          if (!(lane & 1) && n < p.N) {
+            atomicAdd(e.stats + n, a[0]);
+            atomicAdd(e.stats + e.stats_stride + n, q[0]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ mode 1 (wgrad)
+constexpr int WG_STAGE_BYTES = 4 * 16384;  // Y: 2 boxes [128 rows][64 ch], X: 2 boxes [128 rows][64 ch]
+constexpr int WG_STAGES = 3;
+
+__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_wgrad_kernel(const __grid_constant__ TgParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  TgShared* sh = (TgShared*)(smem + (size_t)WG_STAGES * WG_STAGE_BYTES);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // tile decode: blockIdx.x = ((r_tile * ntaps + tap) * c_tiles + c_tile) * ksplit + ks
+  int idx = blockIdx.x;
+  const int ks = idx % p.ksplit;
+  idx /= p.ksplit;
+  const int c_tile = idx % p.c_tiles;
+  idx /= p.c_tiles;
+  const int tap = idx % p.ntaps;
+  const int r_tile = idx / p.ntaps;
+  const int n_iters = (p.m_tiles_total - ks + p.ksplit - 1) / p.ksplit;  // row tiles ks, ks+ksplit, ...
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_a);
+    tma_prefetch_desc(&p.tm_b);
+    for (int s = 0; s < WG_STAGES; ++s) {
+      mbar_init(&sh->full[s], 1);
+      mbar_init(&sh->empty[s], 1);
+    }
+    mbar_init(&sh->tmem_full[0], 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sh->tmem_base, 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < n_iters; ++i) {
+        const int m_tile = ks + i * p.ksplit;
+        int st[3];
+        tile_coords(p, m_tile, st);
+        int xb[5] = {0, 0, 0, 0, 0}, yb[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          if (p.m_to_a[j] > 0) xb[p.m_to_a[j]] = st[j];
+          if (p.y_m_to_a[j] > 0) yb[p.y_m_to_a[j]] = st[j];
+        }
+        mbar_wait(&sh->empty[s], ph ^ 1, 11);
+        uint8_t* sy = smem + (size_t)s * WG_STAGE_BYTES;
+        uint8_t* sx = sy + 2 * 16384;
+        mbar_expect_tx(&sh->full[s], (uint32_t)WG_STAGE_BYTES);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          tma_load(&p.tm_b, &sh->full[s], sy + h * 16384, p.rank_b, r_tile * 128 + h * 64, yb[1], yb[2], yb[3], yb[4]);
+          tma_load(&p.tm_a, &sh->full[s], sx + h * 16384, p.rank_a, c_tile * 128 + h * 64, xb[1] + p.a_off[tap][0],
+                   xb[2] + p.a_off[tap][1], xb[3] + p.a_off[tap][2], xb[4] + p.a_off[tap][3]);
+        }
+        if (++s == WG_STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, 128, 1, 1);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < n_iters; ++i) {
+        mbar_wait(&sh->full[s], ph, 12);
+        tc_fence_after();
+        const uint32_t sy = smem_u32(smem + (size_t)s * WG_STAGE_BYTES);
+        const uint32_t sx = sy + 2 * 16384;
+        // MN-major, 128B swizzle: 64-channel chunks LBO = 16384 B apart, 8-row (K) groups SBO = 1024 B apart
+        const uint64_t adesc = make_sdesc(sy, 16384, 1024);
+        const uint64_t bdesc = make_sdesc(sx, 16384, 1024);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)  // 16 rows (= 2048 B = 128 x 16B units) per UMMA_K step
+          umma_bf16(tmem_base, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc, (i | k) != 0);
+        umma_commit(&sh->empty[s]);
+        if (++s == WG_STAGES) { s = 0; ph ^= 1; }
+      }
+      umma_commit(&sh->tmem_full[0]);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int n = r_tile * 128 + quarter * 32 + lane;  // output channel (row of D)
+    mbar_wait(&sh->tmem_full[0], 0, 13);
+    tc_fence_after();
+    const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const int wt = p.b_tap[tap];
+    for (int ch = 0; ch < 8; ++ch) {
+      const int cb = c_tile * 128 + ch * 16;
+      if (cb >= p.K) break;
+      float v[16];
+      tmem_ld16(taddr0 + (uint32_t)(ch * 16), v);
+      if (n < p.N && n_iters > 0) {
+        float* o = p.dwp + ((long long)n * p.ntaps_w + wt) * p.K + cb;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (cb + j < p.K) atomicAdd(o + j, v[j]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)f;
+  }
+  return fn;
+}
+
+// bf16 tensor map: dim0 = channels (extent c_ext, box 64 = one 128B swizzle row), dims 1.. = (ext, stride) pairs
+static int encode_map(CUtensorMap* tm, const void* base, int c_ext, int nd, const int64_t* ext, const int64_t* stride,
+                      const int* box) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+    return ASF_E_DRIVER;
+  }
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bdim[5], estr[5];
+  gdim[0] = (cuuint64_t)c_ext;
+  bdim[0] = TG_KC;
+  estr[0] = 1;
+  for (int i = 0; i < nd; ++i) {
+    gdim[i + 1] = (cuuint64_t)ext[i];
+    gstr[i] = (cuuint64_t)stride[i] * 2;
+    bdim[i + 1] = (cuuint32_t)box[i];
+    estr[i + 1] = 1;
+    if ((gstr[i] & 15) != 0) {
+      set_error("tensor map: stride %lld elements is not a multiple of 16 bytes", (long long)stride[i]);
+      return ASF_E_BADARG;
+    }
+  }
+  if (((uintptr_t)base & 15) != 0) {
+    set_error("tensor map: base pointer not 16-byte aligned");
+    return ASF_E_BADARG;
+  }
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)(nd + 1), const_cast<void*>(base), gdim, gstr, bdim,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, c_ext %d)", (int)r, nd + 1, c_ext);
+    return ASF_E_DRIVER;
+  }
+  return 0;
+}
+
+static int ilog2_exact(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return ((1 << l) == v) ? l : -1;
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+static int g_debug_sync = -1;
+static int debug_sync(cudaStream_t st) {
+  if (g_debug_sync < 0) {
+    const char* e = getenv("ASF_DEBUG_SYNC");
+    g_debug_sync = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (g_debug_sync) ASF_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // namespace asf
+
+using namespace asf;
+
+extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
+  ASF_CHECK_ARG(q && (mode == 0 || mode == 1), "asf_tapgemm: bad mode");
+  ASF_CHECK_ARG(q->a && q->nd >= 1 && q->nd <= 4 && q->K > 0 && q->K % 8 == 0 && q->N > 0,
+                "asf_tapgemm: bad A description (nd %d, K %d, N %d)", q->nd, q->K, q->N);
+  ASF_CHECK_ARG(q->ntaps >= 1 && q->ntaps <= ASF_MAX_TAPS && q->ntaps_w >= 1, "asf_tapgemm: bad tap count");
+  static TgParams p;  // large POD; filled per call (the launch copies it)
+  memset(&p, 0, sizeof(p));
+  int box_a[4] = {1, 1, 1, 1}, box_y[4] = {1, 1, 1, 1};
+  int prod = 1, last = 0;
+  p.m_tiles_total = 1;
+  for (int j = 0; j < 3; ++j) {
+    int l = ilog2_exact(q->m_box[j]);
+    ASF_CHECK_ARG(l >= 0 && q->m_ext[j] >= 1, "asf_tapgemm: m_box[%d]=%d must be a power of two", j, q->m_box[j]);
+    p.m_ext[j] = q->m_ext[j];
+    p.m_log2[j] = l;
+    p.m_to_a[j] = q->m_to_a[j];
+    p.m_tiles[j] = (int)cdiv(q->m_ext[j], q->m_box[j]);
+    p.m_tiles_total *= p.m_tiles[j];
+    prod *= q->m_box[j];
+    if (q->m_to_a[j] > 0) {
+      ASF_CHECK_ARG(q->m_to_a[j] <= q->nd && q->m_to_a[j] > last, "asf_tapgemm: m_to_a must be increasing and <= nd");
+      last = q->m_to_a[j];
+      box_a[q->m_to_a[j] - 1] = q->m_box[j];
+    } else {
+      ASF_CHECK_ARG(q->m_box[j] == 1 && q->m_ext[j] == 1, "asf_tapgemm: unmapped M dim %d must have extent/box 1", j);
+    }
+  }
+  ASF_CHECK_ARG(prod == TG_BLOCK_M, "asf_tapgemm: product of m_box must be %d (got %d)", TG_BLOCK_M, prod);
+  p.ntaps = q->ntaps;
+  for (int t = 0; t < q->ntaps; ++t) {
+    for (int d = 0; d < 4; ++d) p.a_off[t][d] = q->a_off[t][d];
+    p.b_tap[t] = q->b_tap[t];
+    ASF_CHECK_ARG(q->b_tap[t] >= 0 && q->b_tap[t] < q->ntaps_w, "asf_tapgemm: b_tap out of range");
+  }
+  p.K = q->K;
+  p.N = q->N;
+  p.kchunks = (int)cdiv(q->K, TG_KC);
+  p.rank_a = q->nd + 1;
+  p.ntaps_w = q->ntaps_w;
+  int rc = encode_map(&p.tm_a, q->a, q->K, q->nd, q->a_dim, q->a_stride, box_a);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  if (mode == 0) {
+    ASF_CHECK_ARG(q->bw && q->out && q->ld_out >= q->N, "asf_tapgemm: mode 0 needs bw/out");
+    int bn = q->block_n;
+    if (bn <= 0) {
+      int n16 = (int)cdiv(q->N, 16) * 16;
+      bn = n16 <= 256 ? n16 : 256;
+      if (n16 > 256 && n16 % 256 != 0 && n16 % 128 == 0) bn = 128;
+      // keep at least ~1 wave of tiles on the chip when M is small
+      while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < num_sms() && bn % 32 == 0) bn /= 2;
+    }
+    ASF_CHECK_ARG(bn >= 16 && bn <= 256 && bn % 16 == 0, "asf_tapgemm: block_n %d must be a multiple of 16 in [16,256]", bn);
+    p.block_n = bn;
+    p.n_tiles = (int)cdiv(q->N, bn);
+    // weights [N][taps_w][K] viewed as a rank-3 map (K, taps_w, N), box (64, 1, block_n)
+    int64_t wext[2] = {q->ntaps_w, q->N}, wstr[2] = {q->K, (int64_t)q->ntaps_w * q->K};
+    int wbox[2] = {1, bn};
+    rc = encode_map(&p.tm_b, q->bw, q->K, 2, wext, wstr, wbox);
+    if (rc) return rc;
+    p.rank_b = 3;
+    const int stage_bytes = TG_A_BYTES + bn * 128;
+    int stages = TG_SMEM_BUDGET / stage_bytes;
+    if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
+    ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: not enough shared memory for 2 stages");
+    p.stages = stages;
+    p.out = q->out;
+    p.out_bf16 = q->out_dtype == ASF_BF16;
+    ASF_CHECK_ARG(q->out_dtype == ASF_BF16 || q->out_dtype == ASF_F32, "asf_tapgemm: bad out dtype");
+    p.ld_out = q->ld_out;
+    for (int j = 0; j < 3; ++j) p.o_stride[j] = q->o_stride[j];
+    p.epi = q->epi;
+    bool vec = p.out_bf16 && (q->ld_out % 8 == 0) && (((uintptr_t)q->out & 15) == 0);
+    if (q->epi.res) vec = vec && (q->epi.ld_res % 8 == 0) && (((uintptr_t)q->epi.res & 15) == 0);
+    if (q->epi.mask) vec = vec && (q->epi.ld_mask % 8 == 0) && (((uintptr_t)q->epi.mask & 15) == 0);
+    p.vec_ok = vec ? 1 : 0;
+    const size_t smem = (size_t)stages * stage_bytes + sizeof(TgShared) + 1024;
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+      ASF_CUDA(cudaFuncSetAttribute(tapgemm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set = smem;
+    }
+    int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
+    int grid = (int)(total < num_sms() ? total : num_sms());
+    tapgemm_fwd_kernel<<<grid, TG_THREADS, smem, st>>>(p);
+    ASF_LAUNCH_CHECK();
+    return debug_sync(st);
+  }
+
+  // mode 1: wgrad
+  ASF_CHECK_ARG(q->y && q->dwp && q->y_nd >= 1 && q->y_nd <= 4, "asf_tapgemm: mode 1 needs y/dwp");
+  last = 0;
+  for (int j = 0; j < 3; ++j) {
+    p.y_m_to_a[j] = q->y_m_to_a[j];
+    if (q->y_m_to_a[j] > 0) {
+      ASF_CHECK_ARG(q->y_m_to_a[j] <= q->y_nd && q->y_m_to_a[j] > last, "asf_tapgemm: y_m_to_a must be increasing");
+      last = q->y_m_to_a[j];
+      box_y[q->y_m_to_a[j] - 1] = q->m_box[j];
+    } else {
+      ASF_CHECK_ARG(q->m_box[j] == 1, "asf_tapgemm: unmapped Y M-dim must have box 1");
+    }
+  }
+  rc = encode_map(&p.tm_b, q->y, q->N, q->y_nd, q->y_dim, q->y_stride, box_y);
+  if (rc) return rc;
+  p.rank_b = q->y_nd + 1;
+  p.dwp = q->dwp;
+  p.c_tiles = (int)cdiv(q->K, 128);
+  p.r_tiles = (int)cdiv(q->N, 128);
+  int64_t base_tiles = (int64_t)p.c_tiles * p.r_tiles * p.ntaps;
+  int ks = q->ksplit;
+  if (ks <= 0) {
+    ks = (int)cdiv(2 * num_sms(), base_tiles);
+    if (ks > p.m_tiles_total) ks = p.m_tiles_total;
+    if (ks < 1) ks = 1;
+  }
+  ASF_CHECK_ARG(ks >= 1 && ks <= p.m_tiles_total, "asf_tapgemm: ksplit %d out of range (row tiles %d)", ks, p.m_tiles_total);
+  p.ksplit = ks;
+  const size_t smem = (size_t)WG_STAGES * WG_STAGE_BYTES + sizeof(TgShared) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    ASF_CUDA(cudaFuncSetAttribute(tapgemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  int64_t grid = base_tiles * ks;
+  ASF_CHECK_ARG(grid < (1ll << 31), "asf_tapgemm: wgrad grid too large");
+  tapgemm_wgrad_kernel<<<(unsigned)grid, TG_THREADS, smem, st>>>(p);
+  ASF_LAUNCH_CHECK();
+  return debug_sync(st);
+}

@@ -1,0 +1,241 @@
+/* asf_b200.h -- C ABI of libasf_b200.so: the B200 (sm_100a) kernels behind the Auditory SlowFast hot path.
+ *
+ * The reference (ClementSicard/auditory-slow-fast) has NO native / FFI interface of its own: its hot
+ * path is Python calling librosa/numpy (CPU) and torch.nn (cuDNN/cuBLAS).  The drop-in boundary is
+ * therefore the reference's Python call signatures (mirrored 1:1 by auditory-slow-fast_b200/asf_b200),
+ * and this header is the C ABI *below* that mirror: one entry point per library kernel the reference
+ * dispatches to today.  Each declaration cites the reference call site it replaces
+ * (paths relative to /root/reference).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no torch types.  Every pointer is a DEVICE pointer unless named h_*.
+ *  - the caller owns every buffer (including workspaces); kernels never allocate or free device memory.
+ *  - every launch is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy default).
+ *  - return value: 0 on success, otherwise a cudaError_t / negative ASF_E_* code; asf_last_error()
+ *    gives a thread-local message.  There is no CPU fallback anywhere.
+ *  - activations are channels-last "rows x channels": row = (b*T + t)*F + f, channel stride 1,
+ *    row pitch `ld` elements (>= C, so a tensor can be a channel slice of a wider buffer).
+ *  - dtype codes: ASF_F32 = 0, ASF_BF16 = 1.
+ */
+#ifndef ASF_B200_H_
+#define ASF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASF_F32 0
+#define ASF_BF16 1
+
+#define ASF_E_BADARG (-1)
+#define ASF_E_UNSUPPORTED (-2)
+#define ASF_E_DRIVER (-3)
+
+#define ASF_MAX_TAPS 8
+
+const char* asf_last_error(void);
+int asf_version(void);
+/* 1 if the current device is sm_100 (tcgen05/TMA kernels can run), 0 otherwise, <0 on error. */
+int asf_device_is_sm100(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Feature extraction.  Replaces librosa.stft + filters.mel + np.dot + np.log in
+ *   audio_slowfast/datasets/audio_loader_epic.py:66-97  (_log_specgram; VGG twin audio_loader_vggsound.py:57-69)
+ * the edge padding of _extract_sound_feature (audio_loader_epic.py:151-154) and the slow-pathway
+ * gather of pack_pathway_output (audio_slowfast/datasets/utils.py:59-63), batched.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Builds the constant tables once per configuration, on the host in float64 rounded once to float32,
+ * and uploads them (device buffers owned by the caller; synchronises `stream`):
+ *   basisT    float [win][n_bins_pad][2]  (w[j] cos(2 pi k (lpad+j)/n_fft), -w[j] sin(..)), w = periodic Hann,
+ *                                          lpad = (n_fft - win)/2  (librosa util.pad_center of the window)
+ *   melT      float [n_bins_pad][n_mels]  librosa.filters.mel(sr, n_fft, n_mels, htk=True, norm=None) transposed
+ *   mel_range int32 [n_mels][2]           [first, last+1) non-zero bin of every filter
+ * n_bins = n_fft/2 + 1 <= n_bins_pad. */
+int asf_logmel_tables(float* basisT, float* melT, int32_t* mel_range, int sr, int n_fft, int win, int n_mels,
+                      int n_bins_pad, void* stream);
+
+/* wave [B][n_samples] fp32 (row pitch wave_ld) -> fast [B][1][T_out][n_mels] fp32 where the
+ * T = 1 + n_samples/hop frames of librosa.stft(center=True, pad_mode="constant") are computed and rows
+ * T..T_out-1 replicate frame T-1 (np.pad "edge", audio_loader_epic.py:151-154).  T_out <= 0 means T.
+ * T_out < T is an error (the reference never truncates). */
+int asf_logmel_fwd(const float* wave, int64_t wave_ld, int B, int n_samples, int n_fft, int win, int hop,
+                   int n_mels, float eps, const float* basisT, const float* melT, const int32_t* mel_range,
+                   int n_bins_pad, float* fast, int T_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Convolution family.  Replaces every nn.Conv2d (+ the BatchNorm2d / ReLU / residual add / torch.cat
+ * that follow it) of
+ *   audio_slowfast/models/stem_helper.py:150-168, resnet_helper.py:170-225 and :310-341,
+ *   audio_model_builder.py:90-111 (FuseFastToSlow)
+ * and their autograd backward (cuDNN dgrad / wgrad).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Fused epilogue applied to the fp32 accumulator `acc` of output element (row, n):
+ *   v = acc * (scale ? scale[n] : 1) + (shift ? shift[n] : 0)
+ *   if (res)        v += res[row*ld_res + n]
+ *   if (accumulate) v += out[row*ld_out + n]
+ *   if (relu)       v = max(v, 0)
+ *   if (mask)       v = mask[row*ld_mask + n] > 0 ? v : 0
+ *   if (stats)      stats[n] += v ; stats[n_total + n] += v*v      (fp32 atomics, valid rows only)
+ *   out[row*ld_out + n] = (out dtype) v
+ * res / mask have the out dtype. */
+typedef struct {
+  const float* scale;
+  const float* shift;
+  const void* res;
+  int64_t ld_res;
+  const void* mask;
+  int64_t ld_mask;
+  float* stats;
+  int32_t stats_stride; /* offset of the sum-of-squares half (= channels of the stats buffer) */
+  int32_t relu;
+  int32_t accumulate;
+} asf_epilogue_t;
+
+/* Dense direct convolution geometry, channels-last. */
+typedef struct {
+  int32_t B, Tin, Fin, Cin;
+  int32_t Tout, Fout, Cout;
+  int32_t kt, kf, st, sf, pt, pf;
+  int64_t ld_in, ld_out;
+} asf_conv_geom_t;
+
+/* CUDA-core reference/stem path (any geometry incl. Cin = 1; dtype codes per tensor).
+ *   w   : packed weights [Cout][kt*kf][Cin] in dtype w_dtype
+ *   fwd : out[b,to,fo,n] = epi( sum in[b,to*st+it-pt,fo*sf+if-pf,c] * w[n][it*kf+if][c] )
+ *   dgrad: din[b,ti,fi,c] = epi( sum dout[b,to,fo,n] * w[n][tap][c] )  (epilogue indexed by (in-row, c))
+ *   wgrad: dw[n][c][it][if] (OIHW fp32) = (accumulate ? dw : 0) + rscale[n] * sum dout[row,n] * in[row_tap,c] */
+int asf_conv_fwd_simt(const void* in, int in_dtype, const void* w, int w_dtype, void* out, int out_dtype,
+                      const asf_conv_geom_t* g, const asf_epilogue_t* epi, void* stream);
+int asf_conv_dgrad_simt(const void* dout, int dout_dtype, const void* w, int w_dtype, void* din, int din_dtype,
+                        const asf_conv_geom_t* g, const asf_epilogue_t* epi, void* stream);
+int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout_dtype, float* dw_oihw,
+                        const asf_conv_geom_t* g, const float* rscale, int accumulate, void* stream);
+
+/* tcgen05 / TMEM / TMA implicit-GEMM ("tap-GEMM"), bf16 operands, fp32 accumulation in TMEM.
+ *
+ *   D[m][n] = sum_{tap < ntaps} sum_{c < K}  A[ coord(m) + a_off[tap] ][c] * Bw[n][ b_tap[tap] ][c]
+ *
+ * A is addressed through a rank-(1+nd) TMA tensor map over a bf16 tensor: dim 0 = channels (extent K,
+ * contiguous), dims 1..nd described by (a_dim, a_stride) in elements.  The GEMM M-space is a 3-D grid
+ * (m1 fastest) of extents m_ext tiled by boxes m_box (powers of two, product 128); M-dim j lives on tensor-map
+ * dim m_to_a[j] (1..nd) or is absent (0: extent 1).  Coordinates outside the tensor are zero-filled by TMA,
+ * which is how every conv padding is realised.  Bw is a bf16 tensor [N][ntaps_w][K] (K contiguous).
+ * Output row of M-coordinate (m1,m2,m3) is  m1*o_stride[0] + m2*o_stride[1] + m3*o_stride[2]  (in rows).
+ *
+ * mode 0 (forward / dgrad): as above, out dtype out_dtype with the fused epilogue.
+ * mode 1 (wgrad): D[n][c] = sum_rows Y[row][n] * A[row + a_off[tap]][c]; Y uses the same M-space through its
+ *         own tensor map (y_*), result atomically added (fp32) into dwp[N][ntaps_w][K] at tap b_tap[tap].
+ */
+typedef struct {
+  const void* a;      /* bf16 */
+  int32_t nd;         /* number of non-channel tensor-map dims (1..4) */
+  int64_t a_dim[4];   /* extents of tensor-map dims 1..nd */
+  int64_t a_stride[4];/* strides of tensor-map dims 1..nd, elements (multiple of 8) */
+  int32_t K;          /* channels (extent of dim 0) */
+  int32_t m_ext[3], m_box[3], m_to_a[3];
+  int32_t ntaps;
+  int32_t a_off[ASF_MAX_TAPS][4]; /* per-tap coordinate offset on tensor-map dims 1..nd */
+  int32_t b_tap[ASF_MAX_TAPS];    /* per-tap index into the tap dimension of Bw / dwp */
+  const void* bw;     /* mode 0: bf16 [N][ntaps_w][K] */
+  int32_t N, ntaps_w;
+  /* mode 0 output */
+  void* out;
+  int32_t out_dtype;
+  int64_t ld_out;
+  int64_t o_stride[3];
+  int32_t zero_invalid; /* rows outside m_ext are skipped (0) -- reserved */
+  asf_epilogue_t epi;
+  /* mode 1 */
+  const void* y;      /* bf16 [rows][N] viewed through the same M-space */
+  int64_t y_dim[4];
+  int64_t y_stride[4];
+  int32_t y_nd, y_m_to_a[3];
+  float* dwp;         /* fp32 [N][ntaps_w][K], accumulated */
+  int32_t ksplit;
+  int32_t block_n;    /* 0 = choose */
+} asf_tapgemm_t;
+
+int asf_tapgemm(const asf_tapgemm_t* p, int mode, void* stream);
+
+/* Stem weight gradient (Cin = 1, <= 35 taps): in fp32 [B][Tin][Fin], dout [rows][Cout] -> dw OIHW fp32.
+ * Replaces cuDNN wgrad of the stem convs (stem_helper.py:150-157). */
+int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_oihw, const asf_conv_geom_t* g,
+                   int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Weight (re)packing between the reference's state_dict layout (OIHW fp32) and kernel layouts.
+ * ---------------------------------------------------------------------------------------------- */
+/* w_oihw [O][I][kt][kf] fp32 -> packed [O][kt*kf][I] (dtype), each output row scaled by rscale[o] if given */
+int asf_pack_weight(const float* w_oihw, void* packed, int dtype, int O, int I, int taps, const float* rscale,
+                    void* stream);
+/* -> transposed packed [I][kt*kf][O] (dtype), scaled by rscale[o] */
+int asf_pack_weight_t(const float* w_oihw, void* packed, int dtype, int O, int I, int taps, const float* rscale,
+                      void* stream);
+/* dwp [O][taps][I] fp32 -> dw_oihw [O][I][taps] = (accumulate ? dw : 0) + rscale[o] * dwp */
+int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
+                     int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * BatchNorm2d (audio_slowfast/models/batchnorm_helper.py:16-31 -> nn.BatchNorm2d; train / eval / frozen,
+ * audio_model_builder.py:327-344) as per-channel statistics + fused elementwise passes.
+ * ---------------------------------------------------------------------------------------------- */
+/* stats[c] += sum_rows x, stats[C + c] += sum_rows x^2 (fp32 atomics; caller zeroes stats) */
+int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream);
+/* train-mode finalize: mean/var from stats over `count` rows; scale = gamma*invstd, shift = beta - mean*scale;
+ * running_mean/var momentum update (unbiased var) and num_batches_tracked += 1 when running_mean != NULL. */
+int asf_bn_finalize(const float* stats, int C, double count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                    float* scale, float* shift, float* save_mean, float* save_invstd, void* stream);
+/* eval/frozen: scale = gamma / sqrt(running_var + eps), shift = beta - running_mean*scale */
+int asf_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                float eps, int C, float* scale, float* shift, void* stream);
+/* y = [relu]( x*scale[c] + shift[c] (+ res) ) */
+int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
+                 int64_t rows, int C, const float* scale, const float* shift, int relu, void* stream);
+/* backward reductions: red[c] += sum dz, red[C + c] += sum dz * (x - mean[c]) * invstd[c] */
+int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
+                      const float* mean, const float* invstd, float* red, void* stream);
+/* dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count);  dgamma = red[C+c], dbeta = red[c] */
+int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
+                     int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
+                     const float* red, double count, float* dgamma, float* dbeta, void* stream);
+/* elementwise helper: y = (mask > 0) ? (a (+ b)) : 0  -- ReLU backward / gradient accumulation */
+int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const void* mask, int64_t ld_mask,
+                 void* y, int64_t ld_y, int dtype, int64_t rows, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Pools and head.  nn.MaxPool2d([3,3],[2,2],[1,1]) of stem_helper.py:161; nn.AvgPool2d + cat + Dropout +
+ * Linear (+ Softmax + mean) of audio_slowfast/models/head_helper.py:70-109.
+ * ---------------------------------------------------------------------------------------------- */
+/* y[b,tp,fp,c] = max over the 3x3/s2/p1 window of relu(x*scale+shift);  x [B][T][F][C], y [B][To][Fo][C] */
+int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int B, int T, int F, int C,
+                            const float* scale, const float* shift, void* stream);
+/* dz[b,t,f,c] = (a>0) * sum over windows whose (first) argmax is (t,f) of dy;  a = relu(x*scale+shift) */
+int asf_bn_relu_maxpool_bwd(const void* x, const void* dy, int64_t ld_dy, void* dz, int dtype, int B, int T, int F,
+                            int C, const float* scale, const float* shift, void* stream);
+/* feat[b][c_off + c] = mean over P positions of x[b][p][c]   (fp32 out, row pitch ld_feat) */
+int asf_avgpool_fwd(const void* x, int dtype, int B, int P, int C, float* feat, int64_t ld_feat, int c_off,
+                    void* stream);
+/* dx[b][p][c] = dfeat[b][c_off + c] / P, masked by (mask > 0) when mask != NULL */
+int asf_avgpool_bwd(const float* dfeat, int64_t ld_feat, int c_off, const void* mask, void* dx, int dtype, int B,
+                    int P, int C, void* stream);
+/* small fp32 GEMM on CUDA cores: C[M][N] = alpha * op(A) op(B) + beta*C (+ bias[n]); row-major, ta/tb transpose */
+int asf_sgemm(const float* A, const float* Bm, float* C, int M, int N, int K, int ta, int tb, int64_t lda,
+              int64_t ldb, int64_t ldc, float alpha, float beta, const float* bias, void* stream);
+/* in-place row softmax over [rows][n] fp32 */
+int asf_softmax_rows(float* x, int rows, int n, int64_t ld, void* stream);
+/* y = x * mask * inv_keep (dropout with a caller-provided {0,1} mask); in place allowed */
+int asf_scale_mask(const float* x, const float* mask, float* y, int64_t n, float inv_keep, void* stream);
+
+/* gather rows: dst[b][i][:] = src[b][idx[i]][:]  (fp32; pack_pathway_output index_select) */
+int asf_gather_rows(const float* src, float* dst, const int32_t* idx, int B, int T_src, int n_idx, int F,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASF_B200_H_ */
