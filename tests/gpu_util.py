@@ -1,0 +1,88 @@
+"""Helpers shared by the -m gpu tests: run single convs through the engine's launch code."""
+import ctypes as C
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from asf_b200 import _lib as L
+from asf_b200.engine import Act, ConvUnit, Engine
+
+
+def nhwc(t):
+    """NCHW tensor -> contiguous channels-last (B, T, F, C) copy."""
+    return t.permute(0, 2, 3, 1).contiguous()
+
+
+def nchw(t):
+    return t.permute(0, 3, 1, 2).contiguous()
+
+
+class Harness(Engine):
+    """Engine without a model: enough state to launch single conv units."""
+
+    def __init__(self, dtype, force_simt=False):
+        L.require_cuda_sm100()
+        self.dtype = dtype
+        self.code = L.dtype_code(dtype)
+        self.use_tc = dtype == torch.bfloat16
+        self.force_simt = force_simt
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._dwp_buf = None
+        self.grad_hook = None
+
+    def _dwp_view(self, u):
+        n = u.Cout * u.taps * u.Cin
+        if self._dwp_buf is None or self._dwp_buf.numel() < n:
+            self._dwp_buf = torch.zeros(n, dtype=torch.float32, device=self.device)
+        v = self._dwp_buf[:n]
+        v.zero_()
+        return v
+
+
+def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, in_scale=1.0):
+    """Random conv unit on random input; returns (unit, x_nchw_fp32, w_oihw_fp32)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    conv = nn.Conv2d(cin, cout, k, stride=s, padding=p, bias=False).cuda()
+    with torch.no_grad():
+        conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) / (cin * k[0] * k[1]) ** 0.5)
+    bn = nn.BatchNorm2d(cout).cuda()
+    with torch.no_grad():
+        bn.weight.copy_(0.5 + torch.rand(cout, generator=g))
+        bn.bias.copy_(0.2 * torch.randn(cout, generator=g))
+        bn.running_mean.copy_(0.1 * torch.randn(cout, generator=g))
+        bn.running_var.copy_(0.5 + torch.rand(cout, generator=g))
+    x = (in_scale * torch.randn(B, cin, T, Fq, generator=g)).cuda()
+    xa = Act(B, T, Fq, cin, h.dtype, h.device) if ld_in is None else Act(B, T, Fq, ld_in, h.dtype, h.device).slice(0, cin)
+    if ld_in is not None:
+        xa.buf.zero_()
+    xa.view().copy_(nhwc(x))
+    To = (T + 2 * p[0] - k[0]) // s[0] + 1
+    Fo = (Fq + 2 * p[1] - k[1]) // s[1] + 1
+    if ld_out is None:
+        ya = Act(B, To, Fo, cout, h.dtype, h.device)
+    else:
+        ya = Act(B, To, Fo, ld_out, h.dtype, h.device).slice(ld_out - cout, cout)
+        ya.buf.zero_()
+    u = ConvUnit("test", conv, bn, xa, ya, relu=True)
+    u.is_stem = False
+    u.bn_name = "bn"
+    dev = h.device
+    u.scale = torch.empty(cout, dtype=torch.float32, device=dev)
+    u.shift = torch.empty(cout, dtype=torch.float32, device=dev)
+    u.mean = torch.empty(cout, dtype=torch.float32, device=dev)
+    u.invstd = torch.empty(cout, dtype=torch.float32, device=dev)
+    u.stats = torch.zeros(2 * cout, dtype=torch.float32, device=dev)
+    u.red = torch.zeros(2 * cout, dtype=torch.float32, device=dev)
+    # what the kernels really see: the rounded input
+    x_seen = nchw(xa.view().float())
+    return u, x_seen, conv.weight.detach().clone()
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).norm() / (b.norm() + 1e-20))
+
+
+def max_err(a, b):
+    return float((a.float() - b.float()).abs().max())

@@ -1,0 +1,300 @@
+"""GPU (-m gpu): every CUDA kernel through the C ABI against a plain PyTorch fp32 reference of the same op
+on the same (rounded) inputs.  Conv classes follow SURVEY.md 8(a): 1x1, 1x1/s(1,2), 1x3, 1x3/s(1,2), 3x1,
+7x1/s(4,1) at the channel counts / spatial sizes of the real network (incl. ragged tiles and channel
+counts that are not multiples of the 64-wide K chunk or the 16-wide N chunk)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from asf_b200 import _lib as L  # noqa: E402
+from asf_b200.engine import Act  # noqa: E402
+from gpu_util import Harness, make_unit, max_err, nchw, nhwc, rel_err  # noqa: E402
+
+# (name, B, T, F, cin, cout, kernel, stride, pad)
+CONV_CASES = [
+    ("1x1_s2a_slow", 2, 25, 32, 80, 64, (1, 1), (1, 1), (0, 0)),
+    ("1x1_c_slow_s5", 3, 25, 4, 512, 2048, (1, 1), (1, 1), (0, 0)),
+    ("1x1_fast_c8", 2, 100, 32, 8, 32, (1, 1), (1, 1), (0, 0)),
+    ("1x1_fast_to8", 2, 100, 32, 32, 8, (1, 1), (1, 1), (0, 0)),
+    ("1x1s2_short_slow", 2, 25, 32, 320, 512, (1, 1), (1, 2), (0, 0)),
+    ("1x1s2_short_fast", 2, 100, 8, 128, 256, (1, 1), (1, 2), (0, 0)),
+    ("1x3_slow_s3", 2, 25, 16, 128, 128, (1, 3), (1, 1), (0, 1)),
+    ("1x3_slow_s5_F4", 3, 25, 4, 512, 512, (1, 3), (1, 1), (0, 1)),
+    ("1x3_fast_c8", 2, 100, 32, 8, 8, (1, 3), (1, 1), (0, 1)),
+    ("1x3s2_slow_s4", 2, 25, 16, 256, 256, (1, 3), (1, 2), (0, 1)),
+    ("1x3s2_fast_s5", 2, 100, 8, 64, 64, (1, 3), (1, 2), (0, 1)),
+    ("3x1_slow_s4", 2, 25, 8, 1024, 256, (3, 1), (1, 1), (1, 0)),
+    ("3x1_slow_s5", 3, 25, 4, 1280, 512, (3, 1), (1, 1), (1, 0)),
+    ("3x1_fast_s2", 2, 100, 32, 32, 8, (3, 1), (1, 1), (1, 0)),
+    ("3x1_fast_s4", 1, 100, 8, 128, 32, (3, 1), (1, 1), (1, 0)),
+    ("7x1s4_lat_s1", 2, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0)),
+    ("7x1s4_lat_s4", 2, 100, 8, 128, 256, (7, 1), (4, 1), (3, 0)),
+]
+IDS = [c[0] for c in CONV_CASES]
+
+
+def _ref_conv(x, w, s, p):
+    return F.conv2d(x, w, None, stride=s, padding=p)
+
+
+@pytest.fixture(scope="module")
+def h_tc():
+    return Harness(torch.bfloat16)
+
+
+@pytest.fixture(scope="module")
+def h_f32():
+    return Harness(torch.float32)
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+def test_tapgemm_forward_fused_affine(h_tc, case):
+    """frozen/eval BN: conv with BN scale folded into the weights, shift + residual + ReLU in the epilogue."""
+    _, B, T, Fq, cin, cout, k, s, p = case
+    u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=1)
+    u.bn.eval()
+    res = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+    res.buf.copy_(torch.randn(res.buf.shape, device="cuda"))
+    u.res = res
+    h_tc._unit_forward(u, training=False)
+    torch.cuda.synchronize()
+    scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+    shift = u.bn.bias - u.bn.running_mean * scale
+    w_seen = (w * scale.view(-1, 1, 1, 1)).to(torch.bfloat16).float()
+    ref = _ref_conv(x, w_seen, s, p) + shift.view(1, -1, 1, 1) + nchw(res.view().float())
+    ref = F.relu(ref)
+    out = nchw(u.y.view().float())
+    tol = 2e-2 * float(ref.abs().max())  # bf16 output rounding (2^-9 relative) dominates
+    assert max_err(out, ref) <= tol, (max_err(out, ref), tol)
+    assert rel_err(out, ref) < 6e-3, rel_err(out, ref)
+
+
+@pytest.mark.parametrize("case", [CONV_CASES[i] for i in (0, 4, 6, 9, 11, 13, 15, 16)], ids=[IDS[i] for i in (0, 4, 6, 9, 11, 13, 15, 16)])
+def test_tapgemm_forward_batch_stats(h_tc, case):
+    """training BN: raw conv output + per-channel sum / sum-of-squares from the epilogue, then normalise."""
+    _, B, T, Fq, cin, cout, k, s, p = case
+    u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=2)
+    u.bn.train()
+    rm0, rv0 = u.bn.running_mean.clone(), u.bn.running_var.clone()
+    h_tc._unit_forward(u, training=True)
+    torch.cuda.synchronize()
+    conv = _ref_conv(x, w.to(torch.bfloat16).float(), s, p)
+    mean = conv.mean((0, 2, 3))
+    var = conv.var((0, 2, 3), unbiased=False)
+    n = conv.numel() / cout
+    assert torch.allclose(u.mean, mean, atol=2e-3 * float(conv.abs().max()))
+    assert torch.allclose(u.invstd, 1.0 / torch.sqrt(var + u.bn.eps), rtol=5e-3)
+    ref = F.relu(F.batch_norm(conv, None, None, u.bn.weight, u.bn.bias, True, 0.1, u.bn.eps))
+    out = nchw(u.y.view().float())
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    assert torch.allclose(u.bn.running_mean, 0.9 * rm0 + 0.1 * mean, atol=1e-3)
+    assert torch.allclose(u.bn.running_var, 0.9 * rv0 + 0.1 * var * n / (n - 1), rtol=1e-2, atol=1e-4)
+    assert int(u.bn.num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+def test_tapgemm_dgrad(h_tc, case):
+    _, B, T, Fq, cin, cout, k, s, p = case
+    u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=3)
+    u.bn.eval()
+    h_tc._prepare_unit(u, training=True)  # frozen-BN training: folded weights
+    dy = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+    dy.buf.copy_(torch.randn(dy.buf.shape, device="cuda"))
+    dx = u.x.grad
+    prev = torch.randn(dx.buf.shape, device="cuda").to(h_tc.dtype)
+    dx.buf.copy_(prev)
+    # a strided 1x1 leaves odd input columns untouched, so in the network it is never the last (masking) writer
+    covered = not (k == (1, 1) and s != (1, 1))
+    h_tc._conv_dgrad(u, dy, dx, accumulate=True, mask=u.x if covered else None)
+    torch.cuda.synchronize()
+    scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+    w_seen = (w * scale.view(-1, 1, 1, 1)).to(torch.bfloat16).float()
+    xr = x.clone().requires_grad_(True)
+    _ref_conv(xr, w_seen, s, p).backward(nchw(dy.view().float()))
+    ref = xr.grad + nchw(prev.float())
+    if covered:
+        ref = ref * (x > 0)
+    out = nchw(dx.view().float())
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+def test_tapgemm_wgrad(h_tc, case):
+    _, B, T, Fq, cin, cout, k, s, p = case
+    u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=4)
+    dy = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+    dy.buf.copy_(torch.randn(dy.buf.shape, device="cuda"))
+    g = torch.zeros_like(w)
+    rscale = 0.5 + torch.rand(cout, device="cuda")
+    h_tc._conv_wgrad(u, dy, rscale, g, accumulate=False)
+    torch.cuda.synchronize()
+    wr = w.clone().requires_grad_(True)
+    _ref_conv(x, wr, s, p).backward(nchw(dy.view().float()))
+    ref = wr.grad * rscale.view(-1, 1, 1, 1)
+    assert rel_err(g, ref) < 5e-3, rel_err(g, ref)
+    # accumulate into an existing gradient
+    h_tc._conv_wgrad(u, dy, rscale, g, accumulate=True)
+    torch.cuda.synchronize()
+    assert rel_err(g, 2 * ref) < 5e-3
+
+
+def test_tapgemm_concat_slice_output(h_tc):
+    """the lateral conv writes into channels [64:80) of the slow buffer (no torch.cat)."""
+    u, x, w = make_unit(h_tc, 2, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0), seed=5, ld_out=80)
+    u.bn.eval()
+    u.y.buf.fill_(7.0)
+    h_tc._unit_forward(u, training=False)
+    torch.cuda.synchronize()
+    assert float((u.y.buf[..., :64].float() - 7.0).abs().max()) == 0.0
+    scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+    shift = u.bn.bias - u.bn.running_mean * scale
+    ref = F.relu(_ref_conv(x, (w * scale.view(-1, 1, 1, 1)).to(torch.bfloat16).float(), (4, 1), (3, 0)) + shift.view(1, -1, 1, 1))
+    assert rel_err(nchw(u.y.view().float()), ref) < 6e-3
+
+
+@pytest.mark.parametrize("case", [CONV_CASES[i] for i in (0, 4, 9, 11, 15)], ids=[IDS[i] for i in (0, 4, 9, 11, 15)])
+def test_simt_conv_fp32(h_f32, case):
+    """CUDA-core fp32 parity path: forward, dgrad, wgrad against torch to float rounding."""
+    _, B, T, Fq, cin, cout, k, s, p = case
+    u, x, w = make_unit(h_f32, B, T, Fq, cin, cout, k, s, p, seed=6)
+    u.bn.eval()
+    h_f32._unit_forward(u, training=False)
+    scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+    shift = u.bn.bias - u.bn.running_mean * scale
+    ws = w * scale.view(-1, 1, 1, 1)
+    ref = F.relu(_ref_conv(x, ws, s, p) + shift.view(1, -1, 1, 1))
+    assert rel_err(nchw(u.y.view()), ref) < 1e-5
+    dy = Act(u.y.B, u.y.T, u.y.F, cout, h_f32.dtype, h_f32.device)
+    dy.buf.copy_(torch.randn(dy.buf.shape, device="cuda"))
+    h_f32._conv_dgrad(u, dy, u.x.grad, accumulate=False)
+    g = torch.zeros_like(w)
+    h_f32._conv_wgrad(u, dy, u.scale, g, accumulate=False)
+    torch.cuda.synchronize()
+    xr, wr = x.clone().requires_grad_(True), ws.clone().requires_grad_(True)
+    _ref_conv(xr, wr, s, p).backward(nchw(dy.view()))
+    assert rel_err(nchw(u.x.grad.view()), xr.grad) < 1e-5
+    assert rel_err(g, wr.grad * scale.view(-1, 1, 1, 1)) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bn_stats_apply_backward(dtype):
+    rows, Cn = 3000, 64
+    g = torch.Generator().manual_seed(0)
+    x = (torch.randn(rows, Cn, generator=g) * 2 + 0.5).cuda().to(dtype)
+    dz = torch.randn(rows, Cn, generator=g).cuda().to(dtype)
+    gamma = (0.5 + torch.rand(Cn, generator=g)).cuda()
+    beta = torch.randn(Cn, generator=g).cuda()
+    st = L.stream_ptr()
+    code = L.dtype_code(dtype)
+    stats = torch.zeros(2 * Cn, device="cuda")
+    L.call("asf_channel_stats", L.ptr(x), code, rows, Cn, Cn, L.ptr(stats), st)
+    scale, shift, mean, invstd = (torch.empty(Cn, device="cuda") for _ in range(4))
+    rm, rv, nbt = torch.zeros(Cn, device="cuda"), torch.ones(Cn, device="cuda"), torch.zeros((), dtype=torch.int64, device="cuda")
+    L.call("asf_bn_finalize", L.ptr(stats), Cn, C.c_double(rows), L.ptr(gamma), L.ptr(beta), C.c_float(1e-5), C.c_float(0.1),
+           L.ptr(rm), L.ptr(rv), L.ptr(nbt), L.ptr(scale), L.ptr(shift), L.ptr(mean), L.ptr(invstd), st)
+    y = torch.empty_like(x)
+    L.call("asf_bn_apply", L.ptr(x), Cn, None, 0, L.ptr(y), Cn, code, rows, Cn, L.ptr(scale), L.ptr(shift), 1, st)
+    xf = x.float().requires_grad_(True)
+    ref = F.relu(F.batch_norm(xf, None, None, gamma, beta, True, 0.1, 1e-5))
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(y, ref) < tol
+    assert torch.allclose(mean, xf.mean(0), atol=1e-4) and int(nbt) == 1
+    # backward (no relu): dx
+    ref2 = F.batch_norm(xf, None, None, gamma, beta, True, 0.1, 1e-5)
+    ref2.backward(dz.float())
+    red = torch.zeros(2 * Cn, device="cuda")
+    L.call("asf_bn_bwd_reduce", L.ptr(dz), Cn, L.ptr(x), Cn, code, rows, Cn, L.ptr(mean), L.ptr(invstd), L.ptr(red), st)
+    dx, dg, db = torch.empty_like(x), torch.empty(Cn, device="cuda"), torch.empty(Cn, device="cuda")
+    L.call("asf_bn_bwd_apply", L.ptr(dz), Cn, L.ptr(x), Cn, L.ptr(dx), Cn, code, rows, Cn, L.ptr(gamma), L.ptr(mean),
+           L.ptr(invstd), L.ptr(red), C.c_double(rows), L.ptr(dg), L.ptr(db), st)
+    torch.cuda.synchronize()
+    assert rel_err(dx, xf.grad) < (1e-4 if dtype == torch.float32 else 1e-2)
+    assert torch.allclose(db, dz.float().sum(0), rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_stem_pool_forward_backward(dtype):
+    B, T, Fq, Cn = 2, 50, 64, 8
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(B, Cn, T, Fq, generator=g).cuda()
+    xa = nhwc(x).to(dtype)
+    scale = (0.5 + torch.rand(Cn, generator=g)).cuda()
+    shift = (0.3 * torch.randn(Cn, generator=g)).cuda()
+    To, Fo = 25, 32
+    y = torch.empty(B, To, Fo, Cn, dtype=dtype, device="cuda")
+    st = L.stream_ptr()
+    code = L.dtype_code(dtype)
+    L.call("asf_bn_relu_maxpool_fwd", L.ptr(xa), L.ptr(y), Cn, code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift), st)
+    xs = nchw(xa.float()).requires_grad_(True)
+    ref = F.max_pool2d(F.relu(xs * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)), 3, 2, 1)
+    assert rel_err(nchw(y.float()), ref) < (1e-6 if dtype == torch.float32 else 4e-3)
+    dy = torch.randn(B, To, Fo, Cn, generator=g).cuda().to(dtype)
+    dz = torch.empty_like(xa)
+    L.call("asf_bn_relu_maxpool_bwd", L.ptr(xa), L.ptr(dy), Cn, L.ptr(dz), code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift), st)
+    torch.cuda.synchronize()
+    ref.backward(nchw(dy.float()))
+    # dz is the gradient w.r.t. the BN output (before the scale): compare with grad_x / scale
+    refdz = xs.grad / scale.view(1, -1, 1, 1)
+    assert rel_err(nchw(dz.float()), refdz) < (1e-5 if dtype == torch.float32 else 1e-2)
+
+
+def test_head_kernels():
+    B, P, Cn = 4, 100, 256
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(B, P, Cn, generator=g).cuda().to(torch.bfloat16)
+    feat = torch.zeros(B, 300, device="cuda")
+    st = L.stream_ptr()
+    L.call("asf_avgpool_fwd", L.ptr(x), L.BF16, B, P, Cn, L.ptr(feat), 300, 20, st)
+    assert torch.allclose(feat[:, 20:276], x.float().mean(1), atol=1e-5)
+    W = torch.randn(97, 300, generator=g).cuda()
+    bias = torch.randn(97, generator=g).cuda()
+    out = torch.empty(B, 97, device="cuda")
+    L.call("asf_sgemm", L.ptr(feat), L.ptr(W), L.ptr(out), B, 97, 300, 0, 1, 300, 300, 97, C.c_float(1.0), C.c_float(0.0), L.ptr(bias), st)
+    assert torch.allclose(out, feat @ W.t() + bias, atol=1e-4)
+    dl = torch.randn(B, 97, generator=g).cuda()
+    dW = torch.ones(97, 300, device="cuda")
+    L.call("asf_sgemm", L.ptr(dl), L.ptr(feat), L.ptr(dW), 97, 300, B, 1, 0, 97, 300, 300, C.c_float(1.0), C.c_float(1.0), None, st)
+    assert torch.allclose(dW, 1 + dl.t() @ feat, atol=1e-4)
+    df = torch.zeros(B, 300, device="cuda")
+    L.call("asf_sgemm", L.ptr(dl), L.ptr(W), L.ptr(df), B, 300, 97, 0, 0, 97, 300, 300, C.c_float(1.0), C.c_float(1.0), None, st)
+    assert torch.allclose(df, dl @ W, atol=1e-4)
+    sm = out.clone()
+    L.call("asf_softmax_rows", L.ptr(sm), B, 97, 97, st)
+    assert torch.allclose(sm, torch.softmax(out, 1), atol=1e-6)
+    dx = torch.empty_like(x)
+    L.call("asf_avgpool_bwd", L.ptr(df), 300, 20, L.ptr(x), L.ptr(dx), L.BF16, B, P, Cn, st)
+    torch.cuda.synchronize()
+    ref = (df[:, None, 20:276] / P).expand(B, P, Cn) * (x.float() > 0)
+    assert rel_err(dx, ref) < 5e-3
+
+
+def test_weight_pack_roundtrip():
+    O, I, taps = 24, 40, 3
+    w = torch.randn(O, I, taps, 1, device="cuda")
+    rs = torch.rand(O, device="cuda") + 0.5
+    p = torch.empty(O, taps, I, device="cuda")
+    pt = torch.empty(I, taps, O, device="cuda")
+    st = L.stream_ptr()
+    L.call("asf_pack_weight", L.ptr(w), L.ptr(p), L.F32, O, I, taps, L.ptr(rs), st)
+    L.call("asf_pack_weight_t", L.ptr(w), L.ptr(pt), L.F32, O, I, taps, L.ptr(rs), st)
+    ws = w[..., 0] * rs.view(-1, 1, 1)
+    assert torch.equal(p, ws.permute(0, 2, 1).contiguous())
+    assert torch.equal(pt, ws.permute(1, 2, 0).contiguous())
+    back = torch.ones_like(w)
+    L.call("asf_unpack_wgrad", L.ptr(p), L.ptr(back), O, I, taps, None, 1, st)
+    torch.cuda.synchronize()
+    assert torch.allclose(back[..., 0], 1 + ws)
+
+
+def test_bad_arguments_raise():
+    with pytest.raises(RuntimeError):
+        L.call("asf_channel_stats", None, L.F32, 10, 8, 8, None, L.stream_ptr())
+    x = torch.zeros(4, 8, device="cuda")
+    with pytest.raises(RuntimeError):
+        L.call("asf_channel_stats", L.ptr(x), 7, 4, 8, 8, L.ptr(x), L.stream_ptr())
