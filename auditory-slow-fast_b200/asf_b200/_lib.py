@@ -78,6 +78,8 @@ _P, _I, _L, _F, _D = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double
 SIGNATURES = {
     "asf_version": [],
     "asf_device_is_sm100": [],
+    "asf_prof_start": [_I],
+    "asf_prof_stop": [_P, _P, _P],
     "asf_logmel_tables": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "asf_logmel_fwd": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _I, _P, _I, _P],
     "asf_conv_fwd_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
@@ -111,6 +113,8 @@ def _declare(l):
         fn = getattr(l, name)
         fn.argtypes = args
         fn.restype = C.c_int
+    l.asf_launch_count.argtypes = []
+    l.asf_launch_count.restype = C.c_longlong
 
 
 def call(name, *args):

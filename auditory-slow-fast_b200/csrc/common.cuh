@@ -10,6 +10,7 @@
 namespace asf {
 
 void set_error(const char* fmt, ...);
+void count_launch();  // every kernel launch of the library is counted (asf_launch_count)
 
 #define ASF_CHECK_ARG(cond, ...)         \
   do {                                   \
@@ -30,6 +31,7 @@ void set_error(const char* fmt, ...);
 
 #define ASF_LAUNCH_CHECK()                                                          \
   do {                                                                              \
+    asf::count_launch();                                                            \
     cudaError_t e__ = cudaGetLastError();                                           \
     if (e__ != cudaSuccess) {                                                       \
       asf::set_error("%s:%d launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \

@@ -8,6 +8,9 @@
 namespace asf {
 
 static thread_local char g_err[512] = "";
+static long long g_launches = 0;
+
+void count_launch() { __atomic_add_fetch(&g_launches, 1, __ATOMIC_RELAXED); }
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -466,7 +469,8 @@ using namespace asf;
 extern "C" {
 
 const char* asf_last_error(void) { return asf::g_err; }
-int asf_version(void) { return 100; }
+int asf_version(void) { return 101; }
+long long asf_launch_count(void) { return __atomic_load_n(&asf::g_launches, __ATOMIC_RELAXED); }
 
 int asf_device_is_sm100(void) {
   int dev = 0;

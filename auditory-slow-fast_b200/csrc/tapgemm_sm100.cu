@@ -627,6 +627,28 @@ static int num_sms() {
   return n;
 }
 
+// ---- optional per-launch timing (bench.py's roofline leg): cudaEvent pairs around every tap-GEMM launch
+struct ProfRec {
+  cudaEvent_t e0, e1;
+  double flops;
+  int mode;
+};
+static ProfRec* g_prof = nullptr;
+static int g_prof_cap = 0, g_prof_n = 0;
+static bool g_prof_on = false;
+
+static ProfRec* prof_begin(cudaStream_t st, int mode, double flops) {
+  if (!g_prof_on || g_prof_n >= g_prof_cap) return nullptr;
+  ProfRec* r = &g_prof[g_prof_n++];
+  r->mode = mode;
+  r->flops = flops;
+  cudaEventRecord(r->e0, st);
+  return r;
+}
+static void prof_end(ProfRec* r, cudaStream_t st) {
+  if (r) cudaEventRecord(r->e1, st);
+}
+
 static int g_debug_sync = -1;
 static int debug_sync(cudaStream_t st) {
   if (g_debug_sync < 0) {
@@ -726,7 +748,10 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     }
     int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
     int grid = (int)(total < num_sms() ? total : num_sms());
+    const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
+    ProfRec* pr = prof_begin(st, 0, flops);
     tapgemm_fwd_kernel<<<grid, TG_THREADS, smem, st>>>(p);
+    prof_end(pr, st);
     ASF_LAUNCH_CHECK();
     return debug_sync(st);
   }
@@ -767,7 +792,47 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   }
   int64_t grid = base_tiles * ks;
   ASF_CHECK_ARG(grid < (1ll << 31), "asf_tapgemm: wgrad grid too large");
+  const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
+  ProfRec* pr = prof_begin(st, 1, flops);
   tapgemm_wgrad_kernel<<<(unsigned)grid, TG_THREADS, smem, st>>>(p);
+  prof_end(pr, st);
   ASF_LAUNCH_CHECK();
   return debug_sync(st);
+}
+
+extern "C" int asf_prof_start(int max_records) {
+  ASF_CHECK_ARG(max_records > 0, "asf_prof_start: max_records must be positive");
+  if (g_prof_cap < max_records) {
+    ProfRec* n = (ProfRec*)realloc(g_prof, sizeof(ProfRec) * (size_t)max_records);
+    ASF_CHECK_ARG(n != nullptr, "asf_prof_start: out of host memory");
+    g_prof = n;
+    for (int i = g_prof_cap; i < max_records; ++i) {
+      ASF_CUDA(cudaEventCreate(&g_prof[i].e0));
+      ASF_CUDA(cudaEventCreate(&g_prof[i].e1));
+    }
+    g_prof_cap = max_records;
+  }
+  g_prof_n = 0;
+  g_prof_on = true;
+  return 0;
+}
+
+extern "C" int asf_prof_stop(double* ms, double* flops, long long* launches) {
+  g_prof_on = false;
+  for (int m = 0; m < 2; ++m) {
+    ms[m] = 0.0;
+    flops[m] = 0.0;
+    launches[m] = 0;
+  }
+  for (int i = 0; i < g_prof_n; ++i) {
+    ASF_CUDA(cudaEventSynchronize(g_prof[i].e1));
+    float t = 0.f;
+    ASF_CUDA(cudaEventElapsedTime(&t, g_prof[i].e0, g_prof[i].e1));
+    const int m = g_prof[i].mode ? 1 : 0;
+    ms[m] += t;
+    flops[m] += g_prof[i].flops;
+    launches[m] += 1;
+  }
+  g_prof_n = 0;
+  return 0;
 }

@@ -1,0 +1,405 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of Auditory SlowFast on B200, measured.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|infer|logmel] [--impl reference]
+
+Metric (BASELINE.json): clips/s of the SLOWFAST_R50 (EPIC-KITCHENS verb 97 + noun 300) bf16 TRAINING step on
+synthetic 2 s clips, 64 clips per GPU:  waveform [64, 47975] fp32 -> log-mel [400 x 128] -> slow/fast pathways
+-> AudioSlowFast forward -> mean(CE_verb, CE_noun) -> backward (-> gradient all-reduce over NCCL when N > 1)
+-> SGD-nesterov step.  One "step" = one such pass over one batch.
+
+  value      whole-job clips/s with the waveforms already resident in HBM (device-timed, CUDA events).
+  e2e        the same step through the reference-facing API with HOST inputs: every step copies the batch of
+             waveforms + labels from pinned host memory and reads the loss back (copies inside the timed region).
+  roofline   the dominant kernel (tap-GEMM forward/dgrad, tcgen05): algorithmic FLOPs of its launches divided by
+             their CUDA-event durations, measured live in an extra instrumented pass, against the measured bf16 peak.
+  cpu_baseline  the oracle (CPU restatement of the reference path, oracle/) timed on this box's host cores on a
+             bounded sample.
+  --impl reference   times that CPU implementation as the reference arm.
+
+Launch for N > 1:  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1
+                   --master-port P bench.py --gpus N --steps K --warmup W
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "auditory-slow-fast_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "clips/sec (2 s log-mel, SLOWFAST_R50 bf16 train)"
+UNIT = "clips/s"
+N_SAMPLES = 47975           # 2 s clip: int(round(24000 * 1.999)) - 1 samples
+GFLOP_FWD = 8.628           # 2*MAC over the 110 convs + 2 FCs, per clip
+GFLOP_TRAIN = 25.88         # 3 x forward (stem dgrad not needed)
+GFLOP_LOGMEL = 0.4986       # dense-contraction formulation of STFT + mel
+BYTES_LOGMEL = 4 * N_SAMPLES + 4 * 400 * 128
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return {"bf16_burst": d["bf16_tflops"], "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "hbm": d["hbm_gbs"], "source": "measured"}
+    return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "power_w_max": max(power) if power else None}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def _cpu_step_fn(batch, workload):
+    """The oracle's CPU implementation of one step on `batch` clips (numpy log-mel + functional torch model)."""
+    import numpy as np
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import logmel_np as OL
+    from oracle import model_torch as M
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ocfg = M.epic_cfg(dropout=0.5, bn_freeze=False)
+    sd = M.init_state_dict(ocfg, 0)
+    wav = OL.synthetic_waveforms(batch, N_SAMPLES, 1234)
+    labels = M.synthetic_labels(ocfg, batch)
+    pool = ThreadPoolExecutor(max_workers=min(cores, batch))
+    params = {k: v for k, v in sd.items() if v.dtype.is_floating_point and "running_" not in k}
+    mom = {k: torch.zeros_like(v) for k, v in params.items()}
+
+    def step():
+        spec = np.stack(list(pool.map(lambda w: OL.extract_sound_feature(w, 400), wav)))   # [B, 1, 400, 128]
+        if workload == "logmel":
+            return
+        fast = torch.from_numpy(spec)
+        slow = fast[:, :, torch.from_numpy(OL.slow_indices(400, 4)).long()]
+        if workload == "infer":
+            with torch.no_grad():
+                M.Net(ocfg, sd).forward([slow, fast], training=False)
+            return
+        g = torch.Generator().manual_seed(0)
+        mask = (torch.rand(batch, 2304, generator=g) < 0.5).float()
+        loss, _, grads, new_sd = M.loss_and_grads(ocfg, sd, [slow, fast], labels, dropout_mask=mask)
+        with torch.no_grad():  # SGD nesterov, momentum 0.9, wd 1e-4 (0 on BN) -- models/optimizer.py:31-62
+            for k, gk in grads.items():
+                wd = 0.0 if "bn" in k else 1e-4
+                d = gk + wd * params[k]
+                mom[k].mul_(0.9).add_(d)
+                params[k].sub_(0.01 * (d + 0.9 * mom[k]))
+        return float(loss)
+
+    return step, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = args.ref_batch
+    step, cores = _cpu_step_fn(sample, args.workload)
+    for _ in range(max(1, min(args.warmup, 2))):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    v = sample * args.steps / dt
+    out = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": _config(args, 0, 1),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d clips per step (same %s step: numpy log-mel + fp32 torch oracle fwd/bwd/SGD on "
+                                   "the host cores)" % (sample, args.workload)},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+def _config(args, B, n):
+    return {"workload": {"train": "SLOWFAST_R50 EPIC-KITCHENS-100 verb(97)+noun(300) bf16 training step, waveform->log-mel->"
+                                  "fwd->loss->bwd->SGD, batch %d/GPU (BASELINE configs[2])" % args.batch,
+                         "infer": "SLOWFAST_R50 EPIC-KITCHENS-100 bf16 inference waveform->probabilities, batch %d/GPU "
+                                  "(BASELINE configs[1])" % args.batch,
+                         "logmel": "log-mel extraction 2 s clips, batch %d/GPU (BASELINE configs[4])" % args.batch}[args.workload],
+            "global_batch": args.batch * n, "clip_samples": N_SAMPLES, "frames": 400, "mels": 128,
+            "bn_freeze": bool(args.bn_freeze), "parallelism": "dp%d" % n,
+            "l2": "inputs rotate over %d distinct batches; activations + weights + gradients of one step (> 2 GB) exceed "
+                  "the 126 MB L2, so nothing survives between steps" % args.rotate}
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("bench.py: --gpus %d but WORLD_SIZE=%d (launch N > 1 through torch.distributed.run)" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from asf_b200 import _lib as L
+    from asf_b200.config.defaults import epic_slowfast_cfg
+    from asf_b200.datasets.audio_loader_epic import logmel_batch
+    from asf_b200.models import build_model
+    from oracle import logmel_np as OL  # synthetic-input generator only, not on the timed path
+
+    L.require_cuda_sm100()
+    B = args.batch
+    cfg = epic_slowfast_cfg((97, 300), bool(args.bn_freeze))
+    cfg.BN.FREEZE = bool(args.bn_freeze)
+    cfg.NUM_GPUS = world
+    torch.manual_seed(0)
+    model = build_model(cfg)
+    net = model.module if hasattr(model, "module") else model
+    train = args.workload == "train"
+    if train:
+        model.train()
+        if args.bn_freeze:
+            net.freeze_fn("bn_parameters")
+            net.freeze_fn("bn_statistics")
+        bn_params = [p for n, p in net.named_parameters() if "bn" in n and p.requires_grad]
+        other = [p for n, p in net.named_parameters() if "bn" not in n and p.requires_grad]
+        opt = torch.optim.SGD([{"params": bn_params, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}],
+                              lr=0.01, momentum=0.9, nesterov=True, foreach=True)
+    else:
+        model.eval()
+
+    # synthetic inputs: args.rotate distinct batches per rank, pinned on the host and resident on the device
+    host_w, host_v, host_n = [], [], []
+    for i in range(args.rotate):
+        w = torch.from_numpy(OL.synthetic_waveforms(B, N_SAMPLES, 1234 + 1000 * rank + i))
+        g = torch.Generator().manual_seed(1235 + 1000 * rank + i)
+        host_w.append(w.pin_memory())
+        host_v.append(torch.randint(0, 97, (B,), generator=g).pin_memory())
+        host_n.append(torch.randint(0, 300, (B,), generator=g).pin_memory())
+    dev_w = [w.to(dev) for w in host_w]
+    dev_v = [v.to(dev) for v in host_v]
+    dev_n = [v.to(dev) for v in host_n]
+    ce = torch.nn.functional.cross_entropy
+
+    def step(w, yv, yn):
+        """the reference-facing calls: extraction + pack_pathway_output, model(x), compute_loss, backward, SGD"""
+        x = logmel_batch(cfg, w)
+        if args.workload == "logmel":
+            return x[-1]
+        if not train:
+            with torch.no_grad():
+                return model(x)[0]
+        opt.zero_grad(set_to_none=False)
+        verb, noun = model(x)
+        loss = 0.5 * (ce(verb, yv) + ce(noun, yn))
+        loss.backward()
+        opt.step()
+        return loss
+
+    def resident_step(i):
+        j = i % args.rotate
+        return step(dev_w[j], dev_v[j], dev_n[j])
+
+    def host_step(i):
+        j = i % args.rotate
+        w = host_w[j].to(dev, non_blocking=True)
+        yv = host_v[j].to(dev, non_blocking=True)
+        yn = host_n[j].to(dev, non_blocking=True)
+        out = step(w, yv, yn)
+        if out.dim() == 0:
+            return float(out)  # the loss, read back every step
+        return out.float().sum().item() if args.workload == "logmel" else out.cpu()
+
+    def timed(fn, steps, warmup, sample_clocks=False):
+        for i in range(warmup):
+            fn(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        n0 = L.lib().asf_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        launches = L.lib().asf_launch_count() - n0
+        clocks = sampler.stop() if sampler else None
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, launches, clocks
+
+    ms, launches, clocks = timed(resident_step, args.steps, args.warmup, sample_clocks=True)
+    clips = B * world * args.steps
+    value = clips / (ms * 1e-3)
+    ms_e2e, _, _ = timed(host_step, args.steps, max(3, args.warmup // 2))
+    e2e_value = clips / (ms_e2e * 1e-3)
+    h2d = B * N_SAMPLES * 4 + (2 * B * 8 if train else 0)
+    d2h = 4 if train else (B * 97 * 4 if args.workload == "infer" else 4)
+
+    # ---- roofline leg: per-launch CUDA-event timing of the tap-GEMM kernels over a few more steps (rank 0)
+    peaks = _peaks()
+    roof = None
+    if args.workload != "logmel":
+        psteps = min(args.steps, 5)
+        L.call("asf_prof_start", 4096 * psteps)
+        for i in range(psteps):
+            resident_step(i)
+        torch.cuda.synchronize()
+        pms, pfl, pn = (C.c_double * 2)(), (C.c_double * 2)(), (C.c_longlong * 2)()
+        L.call("asf_prof_stop", pms, pfl, pn)
+        if pn[0] > 0:
+            ach = pfl[0] / (pms[0] * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "tapgemm_fwd_kernel (tcgen05 implicit-GEMM conv forward + dgrad)",
+                    "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s", "frac": ach / peaks["bf16_sustained"],
+                    "peak_source": peaks["source"] + " sustained bf16 (kernel timed inside a long step)", "traffic": None,
+                    "launches_per_step": pn[0] / psteps, "kernel_ms_per_step": pms[0] / psteps,
+                    "wgrad_kernel": {"achieved": (pfl[1] / (pms[1] * 1e-3) / 1e12) if pn[1] else None,
+                                     "launches_per_step": pn[1] / psteps, "kernel_ms_per_step": pms[1] / psteps},
+                    "step_tensor_frac": (GFLOP_TRAIN if train else GFLOP_FWD) * B * world * 1e9 / (ms / args.steps * 1e-3) / 1e12 / world
+                    / peaks["bf16_sustained"]}
+    else:
+        ach = BYTES_LOGMEL * B / (ms / args.steps * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s",
+                "frac": ach / peaks["hbm"], "peak_source": peaks["source"], "traffic": None}
+
+    # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same step on the host cores
+    cpu = None
+    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+        cstep, cores = _cpu_step_fn(args.ref_batch, args.workload)
+        cstep()
+        t0 = time.perf_counter()
+        n = 0
+        while n < 2 or (time.perf_counter() - t0 < 10.0 and n < 50):
+            cstep()
+            n += 1
+        dt = time.perf_counter() - t0
+        cpu = {"value": args.ref_batch * n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d steps of %d clips (same %s step through oracle/: numpy log-mel + fp32 torch fwd/bwd/SGD)"
+                         % (n, args.ref_batch, args.workload)}
+
+    if rank == 0:
+        out = {
+            "metric": METRIC if train else {"infer": "clips/sec (2 s log-mel, SLOWFAST_R50 bf16 inference)",
+                                            "logmel": "clips/sec (2 s log-mel extraction)"}[args.workload],
+            "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.workload != "logmel" else "f32", "data": "synthetic",
+            "config": _config(args, B, world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="train", choices=["train", "infer", "logmel"])
+    ap.add_argument("--batch", type=int, default=None, help="clips per GPU (default 64 train, 256 infer/logmel)")
+    ap.add_argument("--bn-freeze", type=int, default=0, help="1 = the EPIC fine-tuning recipe (BN.FREEZE True); "
+                    "default 0 = every BatchNorm in training mode (the harder case, SURVEY.md 8d)")
+    ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through")
+    ap.add_argument("--ref-batch", type=int, default=8, help="clips per step of the CPU reference arm / baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.batch is None:
+        args.batch = 64 if args.workload == "train" else 256
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,15 @@ extern "C" {
 
 const char* asf_last_error(void);
 int asf_version(void);
+/* number of kernel launches the library has issued in this process (every launch, every entry point) */
+long long asf_launch_count(void);
+/* Per-launch timing of the tap-GEMM kernels (measurement aid for bench.py's roofline leg; not used by the
+ * product path).  asf_prof_start arms up to max_records cudaEvent pairs; every asf_tapgemm launch until
+ * asf_prof_stop is bracketed by one pair on its stream.  asf_prof_stop synchronises and returns, for
+ * mode 0 (forward/dgrad) in [0] and mode 1 (wgrad) in [1]: total kernel milliseconds, total algorithmic
+ * FLOPs (2 * M * N * K * taps of each launch) and the number of launches. */
+int asf_prof_start(int max_records);
+int asf_prof_stop(double* ms, double* flops, long long* launches);
 /* 1 if the current device is sm_100 (tcgen05/TMA kernels can run), 0 otherwise, <0 on error. */
 int asf_device_is_sm100(void);
 

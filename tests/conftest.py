@@ -10,6 +10,14 @@ for p in (ROOT, os.path.join(ROOT, "auditory-slow-fast_b200")):
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+try:  # torch references on the GPU must be true fp32 (TF32 conv/matmul would add ~3e-4 of their own error)
+    import torch
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+except Exception:  # pragma: no cover
+    pass
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")

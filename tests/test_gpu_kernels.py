@@ -167,6 +167,7 @@ def test_simt_conv_fp32(h_f32, case):
     h_f32._unit_forward(u, training=False)
     scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
     shift = u.bn.bias - u.bn.running_mean * scale
+    scale, shift = scale.detach(), shift.detach()
     ws = w * scale.view(-1, 1, 1, 1)
     ref = F.relu(_ref_conv(x, ws, s, p) + shift.view(1, -1, 1, 1))
     assert rel_err(nchw(u.y.view()), ref) < 1e-5
