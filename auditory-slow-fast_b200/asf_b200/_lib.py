@@ -55,6 +55,13 @@ class TapGemm(C.Structure):
     ]
 
 
+class PackDesc(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("packed", C.c_void_p), ("packed_t", C.c_void_p), ("rscale", C.c_void_p),
+                ("O", C.c_int32), ("I", C.c_int32), ("taps", C.c_int32), ("dtype", C.c_int32), ("chunk0", C.c_int64)]
+
+
+PACK_CHUNK = 2048
+
 _lib = None
 
 
@@ -80,6 +87,7 @@ SIGNATURES = {
     "asf_device_is_sm100": [],
     "asf_prof_start": [_I],
     "asf_prof_stop": [_P, _P, _P],
+    "asf_prof_record": [_I, _P],
     "asf_logmel_tables": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "asf_logmel_fwd": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _I, _P, _I, _P],
     "asf_conv_fwd_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
@@ -88,13 +96,14 @@ SIGNATURES = {
     "asf_tapgemm": [C.POINTER(TapGemm), _I, _P],
     "asf_pack_weight": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weight_t": [_P, _P, _I, _I, _I, _I, _P, _P],
+    "asf_pack_weights_multi": [_P, _I, C.c_longlong, _P],
     "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _P],
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "asf_bn_fold": [_P, _P, _P, _P, _F, _I, _P, _P, _P],
     "asf_bn_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _I, _P],
     "asf_bn_bwd_reduce": [_P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P],
-    "asf_bn_bwd_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _D, _P, _P, _P],
+    "asf_bn_bwd_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _D, _P, _P, _I, _P],
     "asf_relu_bwd": [_P, _L, _P, _L, _P, _L, _P, _L, _I, _L, _I, _P],
     "asf_bn_relu_maxpool_fwd": [_P, _P, _L, _I, _I, _I, _I, _I, _P, _P, _P],
     "asf_bn_relu_maxpool_bwd": [_P, _P, _L, _P, _I, _I, _I, _I, _I, _P, _P, _P],

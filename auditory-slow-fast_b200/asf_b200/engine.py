@@ -351,14 +351,20 @@ class Engine:
         plan.projs = head.projections()
         plan.logits = [torch.empty((B, pr.out_features), dtype=torch.float32, device=dev) for pr in plan.projs]
         # per-unit BN scratch
-        for u in plan.stems + plan.units:
+        # (one flat allocation each: the per-step zeroing of all statistics is ONE memset, not 220 fill kernels)
+        allu = plan.stems + plan.units
+        tot = sum(u.Cout for u in allu)
+        flat = torch.empty(4 * tot, dtype=torch.float32, device=dev)
+        plan.stats_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
+        plan.red_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
+        o = 0
+        for u in allu:
             Cn = u.Cout
-            u.scale = torch.empty(Cn, dtype=torch.float32, device=dev)
-            u.shift = torch.empty(Cn, dtype=torch.float32, device=dev)
-            u.mean = torch.empty(Cn, dtype=torch.float32, device=dev)
-            u.invstd = torch.empty(Cn, dtype=torch.float32, device=dev)
-            u.stats = torch.zeros(2 * Cn, dtype=torch.float32, device=dev)
-            u.red = torch.zeros(2 * Cn, dtype=torch.float32, device=dev)
+            u.scale, u.shift = flat[4 * o:4 * o + Cn], flat[4 * o + Cn:4 * o + 2 * Cn]
+            u.mean, u.invstd = flat[4 * o + 2 * Cn:4 * o + 3 * Cn], flat[4 * o + 3 * Cn:4 * o + 4 * Cn]
+            u.stats = plan.stats_flat[2 * o:2 * o + 2 * Cn]
+            u.red = plan.red_flat[2 * o:2 * o + 2 * Cn]
+            o += Cn
         return plan
 
     # ------------------------------------------------------------------------------------------ weights
@@ -390,6 +396,61 @@ class Engine:
         if not u.is_stem:
             L.call("asf_pack_weight_t", L.ptr(w32), L.ptr(u.w_pack_t), wcode, u.Cout, u.Cin, u.taps, L.ptr(rs), st)
         u.w_key = key
+
+    def _prepare_all(self, training):
+        """Refreshes every stale folded-BN affine and packed weight copy of the plan: one bn_fold launch per BN
+        whose parameters changed (frozen / eval mode only) and ONE multi-tensor pack launch for all stale convs."""
+        plan = self.plan
+        st = L.stream_ptr()
+        stale = []
+        for u in plan.stems + plan.units:
+            bn, conv = u.bn, u.conv
+            u.batch_mode = bool(training and bn.training)
+            fold_key = None
+            if not u.batch_mode:
+                fold_key = (bn.weight._version, bn.bias._version, bn.running_mean._version, bn.running_var._version,
+                            bn.weight.data_ptr())
+                if fold_key != getattr(u, "fold_key", None):
+                    L.call("asf_bn_fold", L.ptr(bn.weight), L.ptr(bn.bias), L.ptr(bn.running_mean),
+                           L.ptr(bn.running_var), C.c_float(bn.eps), u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+                    u.fold_key = fold_key
+            key = (conv.weight._version, conv.weight.data_ptr(), fold_key, u.batch_mode, self.force_simt)
+            if key != u.w_key:
+                w32 = conv.weight
+                if w32.dtype != torch.float32 or not w32.is_contiguous():
+                    raise RuntimeError("asf_b200 keeps fp32 contiguous master weights (got %s)" % w32.dtype)
+                if u.w_pack is None:
+                    wdt = self.dtype if not u.is_stem else torch.float32
+                    u.w_pack = torch.empty((u.Cout, u.taps, u.Cin), dtype=wdt, device=self.device)
+                    if not u.is_stem:
+                        u.w_pack_t = torch.empty((u.Cin, u.taps, u.Cout), dtype=wdt, device=self.device)
+                stale.append(u)
+                u.w_key = key
+        if not stale:
+            return
+        tkey = tuple((u.name, u.conv.weight.data_ptr(), u.batch_mode) for u in stale)
+        cache = getattr(plan, "_pack_tables", None)
+        if cache is None:
+            cache = plan._pack_tables = {}
+        ent = cache.get(tkey)
+        if ent is None:
+            arr = (L.PackDesc * len(stale))()
+            chunk = 0
+            for i, u in enumerate(stale):
+                d = arr[i]
+                d.w, d.packed = u.conv.weight.data_ptr(), u.w_pack.data_ptr()
+                d.packed_t = u.w_pack_t.data_ptr() if u.w_pack_t is not None else None
+                fold = (not u.batch_mode) and (not u.is_stem)  # BN scale folded into the packed weights
+                d.rscale = u.scale.data_ptr() if fold else None
+                d.O, d.I, d.taps, d.dtype = u.Cout, u.Cin, u.taps, L.dtype_code(u.w_pack.dtype)
+                d.chunk0 = chunk
+                chunk += -(-(u.Cout * u.Cin * u.taps) // L.PACK_CHUNK)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            ent = (host.to(self.device), len(stale), chunk)
+            if len(cache) > 8:
+                cache.clear()
+            cache[tkey] = ent
+        L.call("asf_pack_weights_multi", L.ptr(ent[0]), ent[1], ent[2], st)
 
     # ------------------------------------------------------------------------------------------ conv launches
     def _tc_ok(self, u):
@@ -580,13 +641,13 @@ class Engine:
                    res.ld if res is not None else 0, C.c_void_p(out.ptr), out.ld, out.code, rows, u.Cout,
                    L.ptr(u.scale), L.ptr(u.shift), int(relu), st)
 
-    def _unit_forward(self, u, training):
+    def _unit_forward(self, u, training, prepared=False):
         st = L.stream_ptr()
-        self._prepare_unit(u, training)
+        if not prepared:
+            self._prepare_unit(u, training)
         if u.batch_mode:
             if u.raw is None:
                 u.raw = Act(u.y.B, u.y.T, u.y.F, u.Cout, self.dtype, self.device, name=u.name + ".raw")
-            u.stats.zero_()
             if self._tc_ok(u):
                 self._conv_fwd(u, u.raw, dict(stats=u.stats, stats_stride=u.Cout))
             else:
@@ -600,19 +661,20 @@ class Engine:
     def _forward(self, xs, training, ctx):
         plan, m = self.plan, self.model
         st = L.stream_ptr()
+        if training:
+            plan.stats_flat.zero_()
+        self._prepare_all(training)
         # stems
         for p, u in enumerate(plan.stems):
             xin = xs[p]
             if xin.dtype != torch.float32:
                 xin = xin.float()
             u.x.buf.copy_(xin.reshape(u.x.buf.shape))  # (B,1,T,F) fp32 is already channels-last for C = 1
-            self._prepare_unit(u, training)
             g = u.geom()
             e = _epilogue()
             L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), L.F32, L.ptr(u.w_pack), L.F32, C.c_void_p(u.y.ptr),
                    u.y.code, C.byref(g), C.byref(e), st)
             if u.batch_mode:
-                u.stats.zero_()
                 L.call("asf_channel_stats", C.c_void_p(u.y.ptr), u.y.code, u.y.rows, u.Cout, u.y.ld, L.ptr(u.stats), st)
                 self._bn_forward(u, u.y, None, None, False, training, st)
             L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld, u.y.code,
@@ -620,13 +682,13 @@ class Engine:
         # stages
         for kind, item in plan.order:
             if kind == "fuse":
-                self._unit_forward(item, training)
+                self._unit_forward(item, training, True)
             else:
                 if "b1" in item:
-                    self._unit_forward(item["b1"], training)
-                self._unit_forward(item["a"], training)
-                self._unit_forward(item["b"], training)
-                self._unit_forward(item["c"], training)
+                    self._unit_forward(item["b1"], training, True)
+                self._unit_forward(item["a"], training, True)
+                self._unit_forward(item["b"], training, True)
+                self._unit_forward(item["c"], training, True)
         # head
         head = m.head
         c_off = 0
@@ -660,24 +722,16 @@ class Engine:
         bn, conv = u.bn, u.conv
         if u.batch_mode:
             rows = dz.rows
-            u.red.zero_()
             L.call("asf_bn_bwd_reduce", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld, dz.code, rows,
                    u.Cout, L.ptr(u.mean), L.ptr(u.invstd), L.ptr(u.red), st)
             gw, acc_w = self._grad_target(bn.weight)
             gb, acc_b = self._grad_target(bn.bias)
-            if acc_w or acc_b:
-                tmp_w = torch.empty_like(bn.weight) if gw is not None else None
-                tmp_b = torch.empty_like(bn.bias) if gb is not None else None
-            else:
-                tmp_w, tmp_b = gw, gb
+            if (gw is not None) and (gb is not None) and acc_w != acc_b:
+                raise RuntimeError("%s: BN weight and bias gradients must both exist or both be unset" % u.name)
             dconv = u.raw.grad
             L.call("asf_bn_bwd_apply", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld,
                    C.c_void_p(dconv.ptr), dconv.ld, dz.code, rows, u.Cout, L.ptr(bn.weight), L.ptr(u.mean),
-                   L.ptr(u.invstd), L.ptr(u.red), C.c_double(rows), L.ptr(tmp_w), L.ptr(tmp_b), st)
-            if acc_w and gw is not None:
-                gw.add_(tmp_w)
-            if acc_b and gb is not None:
-                gb.add_(tmp_b)
+                   L.ptr(u.invstd), L.ptr(u.red), C.c_double(rows), L.ptr(gw), L.ptr(gb), int(acc_w or acc_b), st)
             rscale = None
         else:
             dconv = dz
@@ -697,7 +751,7 @@ class Engine:
         st = L.stream_ptr()
         B = plan.B
         self._dwp.zero_()
-        done = []
+        plan.red_flat.zero_()
         # ---- head
         plan.dfeat.zero_()
         feat = plan.feat_used

@@ -54,6 +54,30 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// 16-byte vector path: bf16 rows of C % 8 == 0 channels whose pitch and base keep every 8-channel group aligned
+static inline bool al16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
+static inline bool ld8(int64_t ld) { return (ld & 7) == 0; }
+
+// elementwise_bf16.cu
+int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
+                int C, const float* scale, const float* shift, int relu, cudaStream_t st);
+int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
+                    int C, const float* gamma, const float* mean, const float* invstd, const float* red,
+                    float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st);
+template <bool kBwd>
+int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
+                      const float* invstd, float* out, cudaStream_t st);
+int relu_bwd_v8(const bf16* a, int64_t ld_a, const bf16* b, int64_t ld_b, const bf16* mask, int64_t ld_mask, bf16* y,
+                int64_t ld_y, int64_t rows, int C, cudaStream_t st);
+int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* mask, bf16* dx, int B, int P, int C,
+                   cudaStream_t st);
+int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, int F, int C, const float* scale,
+                           const float* shift, cudaStream_t st);
+int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* dz, int B, int T, int F, int C,
+                           const float* scale, const float* shift, cudaStream_t st);
+int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st);
+int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st);
+
 // dispatch on a dtype code
 #define ASF_DISPATCH_DTYPE(code, T, ...)                       \
   do {                                                         \

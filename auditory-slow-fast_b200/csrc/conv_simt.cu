@@ -151,6 +151,11 @@ int asf_conv_fwd_simt(const void* in, int in_dtype, const void* w, int w_dtype, 
   int rc = check_geom(g);
   if (rc) return rc;
   int64_t total = (int64_t)g->B * g->Tout * g->Fout * g->Cout;
+  // the stems: C_in = 1, fp32 samples and weights, bf16 output, no fused epilogue -> dedicated vector kernel
+  if (g->Cin == 1 && in_dtype == ASF_F32 && w_dtype == ASF_F32 && out_dtype == ASF_BF16 && g->Cout % 8 == 0 &&
+      g->ld_in == 1 && ld8(g->ld_out) && al16(out) && !epi->scale && !epi->shift && !epi->res && !epi->mask &&
+      !epi->stats && !epi->relu && !epi->accumulate && g->kt * g->kf * g->Cout * sizeof(float) <= 48 * 1024)
+    return stem_conv_fwd_bf16((const float*)in, (const float*)w, (bf16*)out, g, (cudaStream_t)stream);
   ASF_DISPATCH3(in_dtype, TI, w_dtype, TW, out_dtype, TO, {
     conv_fwd_simt_kernel<TI, TW, TO><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const TI*)in, (const TW*)w,
                                                                                      (TO*)out, *g, *epi);

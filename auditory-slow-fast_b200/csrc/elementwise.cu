@@ -155,11 +155,12 @@ __global__ void bn_bwd_apply_kernel(const T* __restrict__ dz, int64_t ld_dz, con
   }
 }
 
-__global__ void copy_dgamma_dbeta_kernel(const float* __restrict__ red, int C, float* dgamma, float* dbeta) {
+__global__ void copy_dgamma_dbeta_kernel(const float* __restrict__ red, int C, float* dgamma, float* dbeta,
+                                         int accumulate) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  if (dbeta) dbeta[c] = red[c];
-  if (dgamma) dgamma[c] = red[C + c];
+  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + red[c];
+  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + red[C + c];
 }
 
 template <typename T>
@@ -390,6 +391,41 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ 
   }
 }
 
+// All convs of the network in ONE launch: block b handles PACK_CHUNK destination indices of the unit whose chunk range
+// contains b (binary search over the descriptor table), for both the [O][taps][I] and the [I][taps][O] copy.
+constexpr int PACK_CHUNK = 2048;
+__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_desc_t* __restrict__ d, int n) {
+  int lo = 0, hi = n - 1;
+  const long long b = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (d[mid].chunk0 <= b) lo = mid; else hi = mid - 1;
+  }
+  const asf_pack_desc_t u = d[lo];
+  const long long total = (long long)u.O * u.I * u.taps;
+  const long long i0 = (b - u.chunk0) * PACK_CHUNK;
+  for (int k = threadIdx.x; k < PACK_CHUNK; k += 256) {
+    const long long i = i0 + k;
+    if (i >= total) break;
+    {  // [O][taps][I]
+      const int c = (int)(i % u.I);
+      const long long r = i / u.I;
+      const int tp = (int)(r % u.taps), o = (int)(r / u.taps);
+      float v = u.w[((long long)o * u.I + c) * u.taps + tp];
+      if (u.rscale) v *= u.rscale[o];
+      if (u.dtype == ASF_BF16) ((bf16*)u.packed)[i] = __float2bfloat16_rn(v); else ((float*)u.packed)[i] = v;
+    }
+    if (u.packed_t) {  // [I][taps][O]
+      const int o = (int)(i % u.O);
+      const long long r = i / u.O;
+      const int tp = (int)(r % u.taps), c = (int)(r / u.taps);
+      float v = u.w[((long long)o * u.I + c) * u.taps + tp];
+      if (u.rscale) v *= u.rscale[o];
+      if (u.dtype == ASF_BF16) ((bf16*)u.packed_t)[i] = __float2bfloat16_rn(v); else ((float*)u.packed_t)[i] = v;
+    }
+  }
+}
+
 __global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int I, int taps,
                                     const float* __restrict__ rscale, int accumulate) {
   int64_t total = (int64_t)O * I * taps;
@@ -482,6 +518,8 @@ int asf_device_is_sm100(void) {
 
 int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream) {
   ASF_CHECK_ARG(x && stats && rows > 0 && C > 0 && ld >= C, "asf_channel_stats: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld) && al16(x))
+    return channel_reduce_v8<false>((const bf16*)x, ld, nullptr, 0, rows, C, nullptr, nullptr, stats, (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, false>((const T*)x, ld, (const T*)nullptr, 0, rows, C,
                                                                       nullptr, nullptr, stats, (cudaStream_t)stream)));
 }
@@ -509,6 +547,9 @@ int asf_bn_fold(const float* gamma, const float* beta, const float* running_mean
 int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
                  int64_t rows, int C, const float* scale, const float* shift, int relu, void* stream) {
   ASF_CHECK_ARG(x && y && scale && shift && rows > 0 && C > 0, "asf_bn_apply: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_x) && ld8(ld_y) && al16(x) && al16(y) && (!res || (ld8(ld_res) && al16(res))))
+    return bn_apply_v8((const bf16*)x, ld_x, (const bf16*)res, ld_res, (bf16*)y, ld_y, rows, C, scale, shift, relu,
+                       (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, {
     bn_apply_kernel<T><<<ew_grid(rows * C), 256, 0, (cudaStream_t)stream>>>((const T*)x, ld_x, (const T*)res, ld_res,
                                                                           (T*)y, ld_y, rows, C, scale, shift, relu);
@@ -520,17 +561,23 @@ int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, v
 int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, float* red, void* stream) {
   ASF_CHECK_ARG(dz && x && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_reduce: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dz) && ld8(ld_x) && al16(dz) && al16(x))
+    return channel_reduce_v8<true>((const bf16*)dz, ld_dz, (const bf16*)x, ld_x, rows, C, mean, invstd, red,
+                                   (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, true>((const T*)dz, ld_dz, (const T*)x, ld_x, rows, C,
                                                                      mean, invstd, red, (cudaStream_t)stream)));
 }
 
 int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
                      int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
-                     const float* red, double count, float* dgamma, float* dbeta, void* stream) {
+                     const float* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream) {
   ASF_CHECK_ARG(dz && x && dx && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_apply: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dz) && ld8(ld_x) && ld8(ld_dx) && al16(dz) && al16(x) && al16(dx))
+    return bn_bwd_apply_v8((const bf16*)dz, ld_dz, (const bf16*)x, ld_x, (bf16*)dx, ld_dx, rows, C, gamma, mean, invstd,
+                           red, (float)(1.0 / count), dgamma, dbeta, accumulate, st);
   if (dgamma || dbeta) {
-    copy_dgamma_dbeta_kernel<<<(unsigned)cdiv(C, 128), 128, 0, st>>>(red, C, dgamma, dbeta);
+    copy_dgamma_dbeta_kernel<<<(unsigned)cdiv(C, 128), 128, 0, st>>>(red, C, dgamma, dbeta, accumulate);
     ASF_LAUNCH_CHECK();
   }
   ASF_DISPATCH_DTYPE(dtype, T, {
@@ -544,6 +591,10 @@ int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x,
 int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const void* mask, int64_t ld_mask,
                  void* y, int64_t ld_y, int dtype, int64_t rows, int C, void* stream) {
   ASF_CHECK_ARG(a && y && rows > 0 && C > 0, "asf_relu_bwd: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_a) && ld8(ld_y) && al16(a) && al16(y) && (!b || (ld8(ld_b) && al16(b))) &&
+      (!mask || (ld8(ld_mask) && al16(mask))))
+    return relu_bwd_v8((const bf16*)a, ld_a, (const bf16*)b, ld_b, (const bf16*)mask, ld_mask, (bf16*)y, ld_y, rows, C,
+                       (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, {
     relu_bwd_kernel<T><<<ew_grid(rows * C), 256, 0, (cudaStream_t)stream>>>(
         (const T*)a, ld_a, (const T*)b, ld_b, (const T*)mask, ld_mask, (T*)y, ld_y, rows, C);
@@ -556,6 +607,8 @@ int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int
                             const float* scale, const float* shift, void* stream) {
   ASF_CHECK_ARG(x && y && scale && shift && B > 0 && T > 0 && F > 0 && C > 0, "asf_bn_relu_maxpool_fwd: bad arguments");
   int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_y) && al16(x) && al16(y))
+    return bn_relu_maxpool_fwd_v8((const bf16*)x, (bf16*)y, ld_y, B, T, F, C, scale, shift, (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, Tt, {
     bn_relu_maxpool_fwd_kernel<Tt><<<ew_grid((int64_t)B * To * Fo * C), 256, 0, (cudaStream_t)stream>>>(
         (const Tt*)x, (Tt*)y, ld_y, B, T, F, C, To, Fo, scale, shift);
@@ -569,6 +622,9 @@ int asf_bn_relu_maxpool_bwd(const void* x, const void* dy, int64_t ld_dy, void* 
   ASF_CHECK_ARG(x && dy && dz && scale && shift && B > 0 && T > 0 && F > 0 && C > 0,
                 "asf_bn_relu_maxpool_bwd: bad arguments");
   int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dy) && al16(x) && al16(dy) && al16(dz))
+    return bn_relu_maxpool_bwd_v8((const bf16*)x, (const bf16*)dy, ld_dy, (bf16*)dz, B, T, F, C, scale, shift,
+                                  (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, Tt, {
     bn_relu_maxpool_bwd_kernel<Tt><<<ew_grid((int64_t)B * T * F * C), 256, 0, (cudaStream_t)stream>>>(
         (const Tt*)x, (const Tt*)dy, ld_dy, (Tt*)dz, B, T, F, C, To, Fo, scale, shift);
@@ -591,6 +647,8 @@ int asf_avgpool_fwd(const void* x, int dtype, int B, int P, int C, float* feat, 
 int asf_avgpool_bwd(const float* dfeat, int64_t ld_feat, int c_off, const void* mask, void* dx, int dtype, int B,
                     int P, int C, void* stream) {
   ASF_CHECK_ARG(dfeat && dx && B > 0 && P > 0 && C > 0, "asf_avgpool_bwd: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && al16(dx) && (!mask || al16(mask)) && al16(dfeat) && (ld_feat % 4 == 0) && (c_off % 4 == 0))
+    return avgpool_bwd_v8(dfeat, ld_feat, c_off, (const bf16*)mask, (bf16*)dx, B, P, C, (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, {
     avgpool_bwd_kernel<T><<<ew_grid((int64_t)B * P * C), 256, 0, (cudaStream_t)stream>>>(dfeat, ld_feat, c_off,
                                                                                        (const T*)mask, (T*)dx, B, P, C);
@@ -660,6 +718,13 @@ int asf_pack_weight_t(const float* w_oihw, void* packed, int dtype, int O, int I
   });
 }
 
+int asf_pack_weights_multi(const asf_pack_desc_t* descs_dev, int n, long long total_chunks, void* stream) {
+  ASF_CHECK_ARG(descs_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_pack_weights_multi: bad arguments");
+  pack_weights_multi_kernel<<<(unsigned)total_chunks, 256, 0, (cudaStream_t)stream>>>(descs_dev, n);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
 int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_oihw, const asf_conv_geom_t* g,
                    int accumulate, void* stream) {
   ASF_CHECK_ARG(in && dout && dw_oihw && g, "asf_stem_wgrad: null pointer");
@@ -668,6 +733,8 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_
   cudaStream_t st = (cudaStream_t)stream;
   const int taps = g->kt * g->kf;
   if (!accumulate) ASF_CUDA(cudaMemsetAsync(dw_oihw, 0, sizeof(float) * (size_t)g->Cout * taps, st));
+  if (dout_dtype == ASF_BF16 && g->Cout % 8 == 0 && g->kf <= 8 && (g->Cout / 8) * g->kt <= 256 && ld8(g->ld_out) && al16(dout))
+    return stem_wgrad_v8(in, (const bf16*)dout, dw_oihw, g, st);
   const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
   int64_t blocks = 148 * 4;
   int64_t rpb = cdiv(rows, blocks);

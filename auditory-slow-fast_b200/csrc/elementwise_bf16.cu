@@ -1,0 +1,511 @@
+// Vectorised bf16 streaming kernels (8 channels = one 16-byte access per thread) for the HBM-bound passes of the
+// hot path: training-mode BatchNorm apply / backward, per-channel reductions, ReLU/avg-pool/max-pool backward and
+// the C_in = 1 stems.  elementwise.cu dispatches here whenever the tensor is bf16 with C % 8 == 0 and 16-byte
+// aligned rows (every activation of the network); the scalar kernels there remain for fp32 parity mode and
+// ragged layouts.
+//
+// Replaces the separate cuDNN BatchNorm / ATen elementwise / pooling kernels behind
+//   /root/reference/audio_slowfast/models/stem_helper.py:150-168, resnet_helper.py:181-225, :335-341.
+#include "common.cuh"
+
+namespace asf {
+
+struct F8 {
+  float v[8];
+};
+
+__device__ __forceinline__ F8 unpack8(const uint4& q) {
+  F8 r;
+  const __nv_bfloat162* h = (const __nv_bfloat162*)&q;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f = __bfloat1622float2(h[j]);
+    r.v[2 * j] = f.x;
+    r.v[2 * j + 1] = f.y;
+  }
+  return r;
+}
+__device__ __forceinline__ uint4 pack8(const F8& a) {
+  uint4 q;
+  __nv_bfloat162* h = (__nv_bfloat162*)&q;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(a.v[2 * j], a.v[2 * j + 1]);
+  return q;
+}
+__device__ __forceinline__ F8 ldf8(const float* p) {
+  F8 r;
+  const float4 a = *(const float4*)p, b = *(const float4*)(p + 4);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
+static inline unsigned vgrid(int64_t nvec) {
+  int64_t g = cdiv(nvec, 256), cap = 148 * 16;
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+// ------------------------------------------------------------------------------------------- BN apply (train)
+__global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict__ x, int64_t ld_x,
+                                                          const bf16* __restrict__ res, int64_t ld_res,
+                                                          bf16* __restrict__ y, int64_t ld_y, int64_t nvec, int CV,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int relu) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / CV;
+    const int c = (int)(i - r * CV) * 8;
+    F8 a = unpack8(*(const uint4*)(x + r * ld_x + c));
+    const F8 sc = ldf8(scale + c), sh = ldf8(shift + c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a.v[j] = fmaf(a.v[j], sc.v[j], sh.v[j]);
+    if (res) {
+      const F8 q = unpack8(*(const uint4*)(res + r * ld_res + c));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a.v[j] += q.v[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a.v[j] = fmaxf(a.v[j], 0.f);
+    }
+    *(uint4*)(y + r * ld_y + c) = pack8(a);
+  }
+}
+
+int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
+                int C, const float* scale, const float* shift, int relu, cudaStream_t st) {
+  const int64_t nvec = rows * (C / 8);
+  bn_apply_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, nvec, C / 8, scale, shift, relu);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------- BN backward apply
+// dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count); block 0 also publishes dgamma / dbeta.
+__global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __restrict__ dz, int64_t ld_dz,
+                                                              const bf16* __restrict__ x, int64_t ld_x,
+                                                              bf16* __restrict__ dx, int64_t ld_dx, int64_t nvec,
+                                                              int CV, const float* __restrict__ gamma,
+                                                              const float* __restrict__ mean,
+                                                              const float* __restrict__ invstd,
+                                                              const float* __restrict__ red, float inv_count,
+                                                              float* dgamma, float* dbeta, int accumulate) {
+  const int C = CV * 8;
+  if (blockIdx.x == 0 && (dgamma || dbeta)) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + red[c];
+      if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + red[C + c];
+    }
+  }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / CV;
+    const int c = (int)(i - r * CV) * 8;
+    const F8 g = unpack8(*(const uint4*)(dz + r * ld_dz + c));
+    const F8 xv = unpack8(*(const uint4*)(x + r * ld_x + c));
+    const F8 mu = ldf8(mean + c), is = ldf8(invstd + c), r0 = ldf8(red + c), r1 = ldf8(red + C + c);
+    F8 ga;
+    if (gamma) {
+      ga = ldf8(gamma + c);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ga.v[j] = 1.f;
+    }
+    F8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xh = (xv.v[j] - mu.v[j]) * is.v[j];
+      o.v[j] = ga.v[j] * is.v[j] * (g.v[j] - r0.v[j] * inv_count - xh * r1.v[j] * inv_count);
+    }
+    *(uint4*)(dx + r * ld_dx + c) = pack8(o);
+  }
+}
+
+int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
+                    int C, const float* gamma, const float* mean, const float* invstd, const float* red,
+                    float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st) {
+  const int64_t nvec = rows * (C / 8);
+  bn_bwd_apply_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(dz, ld_dz, x, ld_x, dx, ld_dx, nvec, C / 8, gamma, mean, invstd,
+                                                      red, inv_count, dgamma, dbeta, accumulate);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------- channel reductions
+// out[c] += sum_rows a ; out[C + c] += sum_rows (kBwd ? a * (x - mean) * invstd : a * a).
+// block = 256 threads = RP row-lanes x CVB vector-columns (CVB = min(CV, 256)); every thread streams its rows with
+// 16 fp32 accumulators, the block folds them with shared-memory atomics and flushes one global atomic per channel.
+template <bool kBwd>
+__global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __restrict__ a, int64_t ld_a,
+                                                                const bf16* __restrict__ x, int64_t ld_x,
+                                                                int64_t rows, int C, int CVB, int64_t rows_per_block,
+                                                                const float* __restrict__ mean,
+                                                                const float* __restrict__ invstd, float* out) {
+  __shared__ float s0[2048], s1[2048];
+  const int RP = 256 / CVB;
+  const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
+  const int c = (blockIdx.y * CVB + cvl) * 8;
+  for (int i = threadIdx.x; i < CVB * 8; i += 256) {
+    s0[i] = 0.f;
+    s1[i] = 0.f;
+  }
+  __syncthreads();
+  if (rl < RP && c < C) {
+    float acc0[8], acc1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc0[j] = acc1[j] = 0.f;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    int64_t r1 = r0 + rows_per_block;
+    if (r1 > rows) r1 = rows;
+    F8 mu, is;
+    if (kBwd) {
+      mu = ldf8(mean + c);
+      is = ldf8(invstd + c);
+    }
+    for (int64_t r = r0 + rl; r < r1; r += RP) {
+      const F8 v = unpack8(*(const uint4*)(a + r * ld_a + c));
+      if (kBwd) {
+        const F8 xv = unpack8(*(const uint4*)(x + r * ld_x + c));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc0[j] += v.v[j];
+          acc1[j] = fmaf(v.v[j], (xv.v[j] - mu.v[j]) * is.v[j], acc1[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc0[j] += v.v[j];
+          acc1[j] = fmaf(v.v[j], v.v[j], acc1[j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s0[cvl * 8 + j], acc0[j]);
+      atomicAdd(&s1[cvl * 8 + j], acc1[j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < CVB * 8; i += 256) {
+    const int cc = blockIdx.y * CVB * 8 + i;
+    if (cc < C) {
+      atomicAdd(out + cc, s0[i]);
+      atomicAdd(out + C + cc, s1[i]);
+    }
+  }
+}
+
+template <bool kBwd>
+int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
+                      const float* invstd, float* out, cudaStream_t st) {
+  const int CV = C / 8;
+  const int CVB = CV < 256 ? CV : 256;
+  const int cblocks = (int)cdiv(CV, CVB);
+  const int RP = 256 / CVB;
+  int64_t target = 148 * 6 / cblocks;
+  if (target < 1) target = 1;
+  int64_t rpb = cdiv(rows, target);
+  if (rpb < RP * 4) rpb = RP * 4;
+  dim3 grid((unsigned)cdiv(rows, rpb), cblocks);
+  channel_reduce_v8_kernel<kBwd><<<grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, CVB, rpb, mean, invstd, out);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+template int channel_reduce_v8<false>(const bf16*, int64_t, const bf16*, int64_t, int64_t, int, const float*,
+                                      const float*, float*, cudaStream_t);
+template int channel_reduce_v8<true>(const bf16*, int64_t, const bf16*, int64_t, int64_t, int, const float*,
+                                     const float*, float*, cudaStream_t);
+
+// ------------------------------------------------------------------------------------------- ReLU backward / add
+__global__ void __launch_bounds__(256) relu_bwd_v8_kernel(const bf16* __restrict__ a, int64_t ld_a,
+                                                          const bf16* __restrict__ b, int64_t ld_b,
+                                                          const bf16* __restrict__ mask, int64_t ld_mask,
+                                                          bf16* __restrict__ y, int64_t ld_y, int64_t nvec, int CV) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / CV;
+    const int c = (int)(i - r * CV) * 8;
+    F8 v = unpack8(*(const uint4*)(a + r * ld_a + c));
+    if (b) {
+      const F8 q = unpack8(*(const uint4*)(b + r * ld_b + c));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.v[j] += q.v[j];
+    }
+    if (mask) {
+      const F8 m = unpack8(*(const uint4*)(mask + r * ld_mask + c));
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (!(m.v[j] > 0.f)) v.v[j] = 0.f;
+    }
+    *(uint4*)(y + r * ld_y + c) = pack8(v);
+  }
+}
+
+int relu_bwd_v8(const bf16* a, int64_t ld_a, const bf16* b, int64_t ld_b, const bf16* mask, int64_t ld_mask, bf16* y,
+                int64_t ld_y, int64_t rows, int C, cudaStream_t st) {
+  const int64_t nvec = rows * (C / 8);
+  relu_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(a, ld_a, b, ld_b, mask, ld_mask, y, ld_y, nvec, C / 8);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------- avg-pool backward
+__global__ void __launch_bounds__(256) avgpool_bwd_v8_kernel(const float* __restrict__ dfeat, int64_t ld_feat,
+                                                             int c_off, const bf16* __restrict__ mask,
+                                                             bf16* __restrict__ dx, int64_t nvec, int P, int CV,
+                                                             float inv) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / CV;
+    const int c = (int)(i - r * CV) * 8;
+    const int b = (int)(r / P);
+    F8 v = ldf8(dfeat + (int64_t)b * ld_feat + c_off + c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v.v[j] *= inv;
+    if (mask) {
+      const F8 m = unpack8(*(const uint4*)(mask + i * 8));
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (!(m.v[j] > 0.f)) v.v[j] = 0.f;
+    }
+    *(uint4*)(dx + i * 8) = pack8(v);
+  }
+}
+
+int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* mask, bf16* dx, int B, int P, int C,
+                   cudaStream_t st) {
+  const int64_t nvec = (int64_t)B * P * (C / 8);
+  avgpool_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(dfeat, ld_feat, c_off, mask, dx, nvec, P, C / 8, 1.f / (float)P);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------- stem max-pool
+// y[b,to,fo,c] = max over the 3x3 / stride 2 / pad 1 window of relu(x*scale + shift)
+__global__ void __launch_bounds__(256) bn_relu_maxpool_fwd_v8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
+                                                                     int64_t ld_y, int64_t nvec, int Tn, int F, int CV,
+                                                                     int To, int Fo, const float* __restrict__ scale,
+                                                                     const float* __restrict__ shift) {
+  const int C = CV * 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % CV) * 8;
+    int64_t r = i / CV;
+    const int64_t orow = r;
+    const int fo = (int)(r % Fo);
+    r /= Fo;
+    const int to = (int)(r % To);
+    const int b = (int)(r / To);
+    const F8 sc = ldf8(scale + c), sh = ldf8(shift + c);
+    F8 m;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m.v[j] = 0.f;  // relu output is >= 0 and every window holds a valid element
+    for (int dt = -1; dt <= 1; ++dt) {
+      const int t = 2 * to + dt;
+      if (t < 0 || t >= Tn) continue;
+      for (int df = -1; df <= 1; ++df) {
+        const int f = 2 * fo + df;
+        if (f < 0 || f >= F) continue;
+        const F8 v = unpack8(*(const uint4*)(x + (((int64_t)b * Tn + t) * F + f) * C + c));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m.v[j] = fmaxf(m.v[j], fmaf(v.v[j], sc.v[j], sh.v[j]));
+      }
+    }
+    *(uint4*)(y + orow * ld_y + c) = pack8(m);
+  }
+}
+
+int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, int F, int C, const float* scale,
+                           const float* shift, cudaStream_t st) {
+  const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  const int64_t nvec = (int64_t)B * To * Fo * (C / 8);
+  bn_relu_maxpool_fwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, y, ld_y, nvec, T, F, C / 8, To, Fo, scale, shift);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// dz[b,t,f,c] = (a > 0) * sum over the (<= 4) windows whose FIRST arg-max (t,f scan order, as torch) is (t,f) of dy
+__global__ void __launch_bounds__(256) bn_relu_maxpool_bwd_v8_kernel(const bf16* __restrict__ x,
+                                                                     const bf16* __restrict__ dy, int64_t ld_dy,
+                                                                     bf16* __restrict__ dz, int64_t nvec, int Tn, int F,
+                                                                     int CV, int To, int Fo,
+                                                                     const float* __restrict__ scale,
+                                                                     const float* __restrict__ shift) {
+  const int C = CV * 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % CV) * 8;
+    int64_t r = i / CV;
+    const int f = (int)(r % F);
+    r /= F;
+    const int t = (int)(r % Tn);
+    const int b = (int)(r / Tn);
+    const F8 sc = ldf8(scale + c), sh = ldf8(shift + c);
+    const F8 xs = unpack8(*(const uint4*)(x + i * 8));
+    F8 a, g;
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      a.v[j] = fmaf(xs.v[j], sc.v[j], sh.v[j]);
+      g.v[j] = 0.f;
+      any = any || (a.v[j] > 0.f);
+    }
+    if (any) {
+      // windows containing t: to in {t/2} if t even, {(t-1)/2, (t+1)/2} if odd (same along f)
+      const int to0 = (t & 1) ? (t - 1) >> 1 : t >> 1, to1 = (t & 1) ? (t + 1) >> 1 : t >> 1;
+      const int fo0 = (f & 1) ? (f - 1) >> 1 : f >> 1, fo1 = (f & 1) ? (f + 1) >> 1 : f >> 1;
+      for (int to = to0; to <= to1; ++to) {
+        if (to >= To) continue;
+        for (int fo = fo0; fo <= fo1; ++fo) {
+          if (fo >= Fo) continue;
+          // is (t, f) the first arg-max of window (to, fo)?  an element scanned earlier must be strictly smaller...
+          // torch keeps the first maximum: (t,f) wins iff every earlier element is < a and every later one is <= a
+          bool win[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) win[j] = a.v[j] > 0.f;
+          for (int dt = -1; dt <= 1; ++dt) {
+            const int tt = 2 * to + dt;
+            if (tt < 0 || tt >= Tn) continue;
+            for (int df = -1; df <= 1; ++df) {
+              const int ff = 2 * fo + df;
+              if (ff < 0 || ff >= F || (tt == t && ff == f)) continue;
+              const bool earlier = (tt < t) || (tt == t && ff < f);
+              const F8 v = unpack8(*(const uint4*)(x + (((int64_t)b * Tn + tt) * F + ff) * C + c));
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float o = fmaxf(fmaf(v.v[j], sc.v[j], sh.v[j]), 0.f);
+                if (earlier ? (o >= a.v[j]) : (o > a.v[j])) win[j] = false;
+              }
+            }
+          }
+          const F8 d = unpack8(*(const uint4*)(dy + (((int64_t)b * To + to) * Fo + fo) * ld_dy + c));
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (win[j]) g.v[j] += d.v[j];
+        }
+      }
+    }
+    *(uint4*)(dz + i * 8) = pack8(g);
+  }
+}
+
+int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* dz, int B, int T, int F, int C,
+                           const float* scale, const float* shift, cudaStream_t st) {
+  const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
+  const int64_t nvec = (int64_t)B * T * F * (C / 8);
+  bn_relu_maxpool_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, dy, ld_dy, dz, nvec, T, F, C / 8, To, Fo, scale, shift);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------- stems (C_in = 1)
+// out[b,to,fo,n] = sum_taps in[b, to*st+it-pt, fo*sf+jf-pf] * w[n][tap]   (fp32 in / weights, bf16 out)
+// one thread = one output position x 8 output channels; the weights sit transposed in shared memory.
+__global__ void __launch_bounds__(256) stem_conv_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                            bf16* __restrict__ out, asf_conv_geom_t g, int64_t nvec) {
+  extern __shared__ float sw[];  // [taps][Cout]
+  const int taps = g.kt * g.kf, CG = g.Cout / 8;
+  for (int i = threadIdx.x; i < taps * g.Cout; i += blockDim.x) {
+    const int n = i / taps, tp = i - n * taps;
+    sw[tp * g.Cout + n] = w[i];
+  }
+  __syncthreads();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CG);
+    int64_t row = i / CG;
+    const int64_t orow = row;
+    const int fo = (int)(row % g.Fout);
+    row /= g.Fout;
+    const int to = (int)(row % g.Tout);
+    const int b = (int)(row / g.Tout);
+    const float* ib = in + (int64_t)b * g.Tin * g.Fin;
+    F8 acc;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc.v[j] = 0.f;
+    for (int it = 0; it < g.kt; ++it) {
+      const int t = to * g.st + it - g.pt;
+      if (t < 0 || t >= g.Tin) continue;
+      for (int jf = 0; jf < g.kf; ++jf) {
+        const int f = fo * g.sf + jf - g.pf;
+        if (f < 0 || f >= g.Fin) continue;
+        const float xv = ib[(int64_t)t * g.Fin + f];
+        const float* wp = sw + (it * g.kf + jf) * g.Cout + cg * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc.v[j] = fmaf(xv, wp[j], acc.v[j]);
+      }
+    }
+    *(uint4*)(out + orow * g.ld_out + cg * 8) = pack8(acc);
+  }
+}
+
+int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st) {
+  const int64_t nvec = (int64_t)g->B * g->Tout * g->Fout * (g->Cout / 8);
+  const size_t smem = sizeof(float) * (size_t)g->kt * g->kf * g->Cout;
+  stem_conv_fwd_kernel<<<vgrid(nvec), 256, smem, st>>>(in, w, out, *g, nvec);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// dw[n][it*kf + jf] += sum_rows dout[row][n] * in[row shifted by tap].  One thread owns 8 output channels x one
+// kernel row (kf <= 8 taps) and streams a slice of the output rows; a block folds its threads through shared-memory
+// atomics and issues one global atomic per weight.
+constexpr int STEM_KF_MAX = 8;
+__global__ void __launch_bounds__(256) stem_wgrad_v8_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
+                                                            float* __restrict__ dw, asf_conv_geom_t g,
+                                                            int64_t rows_per_block) {
+  extern __shared__ float sacc[];  // [Cout][taps]
+  const int taps = g.kt * g.kf, CG = g.Cout / 8;
+  const int ngroups = CG * g.kt;
+  const int RL = 256 / ngroups;
+  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) sacc[i] = 0.f;
+  __syncthreads();
+  const int grp = threadIdx.x % ngroups, rl = threadIdx.x / ngroups;
+  if (rl < RL) {
+    const int cg = grp % CG, it = grp / CG;
+    float acc[8][STEM_KF_MAX];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int k = 0; k < STEM_KF_MAX; ++k) acc[j][k] = 0.f;
+    const int64_t rows = (int64_t)g.B * g.Tout * g.Fout;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = (r0 + rows_per_block < rows) ? r0 + rows_per_block : rows;
+    for (int64_t row = r0 + rl; row < r1; row += RL) {
+      const int fo = (int)(row % g.Fout);
+      const int64_t r2 = row / g.Fout;
+      const int to = (int)(r2 % g.Tout);
+      const int b = (int)(r2 / g.Tout);
+      const int t = to * g.st + it - g.pt;
+      if (t < 0 || t >= g.Tin) continue;
+      const F8 d = unpack8(*(const uint4*)(dout + row * g.ld_out + cg * 8));
+      const float* ip = in + ((int64_t)b * g.Tin + t) * g.Fin;
+      const int f0 = fo * g.sf - g.pf;
+#pragma unroll
+      for (int k = 0; k < STEM_KF_MAX; ++k) {
+        const int f = f0 + k;
+        if (k < g.kf && f >= 0 && f < g.Fin) {
+          const float xv = ip[f];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j][k] = fmaf(d.v[j], xv, acc[j][k]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int k = 0; k < STEM_KF_MAX; ++k)
+        if (k < g.kf) atomicAdd(&sacc[(cg * 8 + j) * taps + it * g.kf + k], acc[j][k]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) atomicAdd(dw + i, sacc[i]);
+}
+
+int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st) {
+  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
+  const int ngroups = (g->Cout / 8) * g->kt;
+  const int RL = 256 / ngroups;
+  int64_t blocks = 148 * 4;
+  int64_t rpb = cdiv(rows, blocks);
+  if (rpb < RL * 8) rpb = RL * 8;
+  blocks = cdiv(rows, rpb);
+  const size_t smem = sizeof(float) * (size_t)g->Cout * g->kt * g->kf;
+  stem_wgrad_v8_kernel<<<(unsigned)blocks, 256, smem, st>>>(in, dout, dw, *g, rpb);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace asf

@@ -143,7 +143,8 @@ constexpr int TG_MAX_STAGES = 8;
 constexpr int TG_BLOCK_M = 128;
 constexpr int TG_KC = 64;                 // bf16 elements per 128B swizzle row
 constexpr int TG_A_BYTES = TG_BLOCK_M * 128;
-constexpr int TG_THREADS = 192;           // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2..5 epilogue
+constexpr int TG_THREADS = 320;           // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2..5 / 6..9 two epilogue groups
+constexpr int WG_THREADS = 192;           // wgrad: warp0 TMA, warp1 MMA, warps 2..5 epilogue
 constexpr int TG_SMEM_BUDGET = 200 * 1024;
 
 struct TgParams {
@@ -184,6 +185,182 @@ __device__ __forceinline__ void tile_coords(const TgParams& p, int m_tile, int s
   start[0] = i0 << p.m_log2[0];
   start[1] = i1 << p.m_log2[1];
   start[2] = i2 << p.m_log2[2];
+}
+
+// ------------------------------------------------------------------------------------------------ epilogue helpers
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// residual / accumulate / mask operands of one 32-column chunk of one output row (four 8-column granules each),
+// fetched one chunk ahead of their use so that their latency hides behind the TMEM load + math of the previous chunk
+struct EpiOps {
+  uint4 res[4], acc[4], mask[4];
+};
+
+__device__ __forceinline__ void epi_prefetch(const TgParams& p, EpiOps& o, long long orow, int nb, bool valid) {
+  const asf_epilogue_t& e = p.epi;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const int n = nb + 8 * g;
+    if (valid && p.vec_ok && n + 8 <= p.N) {
+      if (e.res) o.res[g] = *(const uint4*)((const bf16*)e.res + orow * e.ld_res + n);
+      if (e.accumulate) o.acc[g] = *(const uint4*)((const bf16*)p.out + orow * p.ld_out + n);
+      if (e.mask) o.mask[g] = *(const uint4*)((const bf16*)e.mask + orow * e.ld_mask + n);
+    }
+  }
+}
+
+__device__ __forceinline__ void epi_chunk_bf16(const TgParams& p, const EpiOps& o, float* v, long long orow, int nb,
+                                               bool valid) {
+  const asf_epilogue_t& e = p.epi;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const int n = nb + 8 * g;
+    float* w = v + 8 * g;
+    if (n >= p.N) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = 0.f;
+      continue;
+    }
+    if (p.vec_ok && n + 8 <= p.N) {
+      if (e.scale) {
+        const float4 s0 = *(const float4*)(e.scale + n), s1 = *(const float4*)(e.scale + n + 4);
+        w[0] *= s0.x; w[1] *= s0.y; w[2] *= s0.z; w[3] *= s0.w; w[4] *= s1.x; w[5] *= s1.y; w[6] *= s1.z; w[7] *= s1.w;
+      }
+      if (e.shift) {
+        const float4 s0 = *(const float4*)(e.shift + n), s1 = *(const float4*)(e.shift + n + 4);
+        w[0] += s0.x; w[1] += s0.y; w[2] += s0.z; w[3] += s0.w; w[4] += s1.x; w[5] += s1.y; w[6] += s1.z; w[7] += s1.w;
+      }
+      if (valid) {
+        if (e.res) {
+          const bf16* q = (const bf16*)&o.res[g];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] += __bfloat162float(q[j]);
+        }
+        if (e.accumulate) {
+          const bf16* q = (const bf16*)&o.acc[g];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] += __bfloat162float(q[j]);
+        }
+        if (e.relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] = fmaxf(w[j], 0.f);
+        }
+        if (e.mask) {
+          const bf16* q = (const bf16*)&o.mask[g];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (!(__bfloat162float(q[j]) > 0.f)) w[j] = 0.f;
+        }
+        uint4 out;
+        __nv_bfloat162* ob = (__nv_bfloat162*)&out;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(w[2 * j], w[2 * j + 1]);
+        *(uint4*)((bf16*)p.out + orow * p.ld_out + n) = out;
+      }
+    } else {
+      bf16* op = (bf16*)p.out + orow * p.ld_out + n;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (n + j < p.N) {
+          if (e.scale) w[j] *= e.scale[n + j];
+          if (e.shift) w[j] += e.shift[n + j];
+          if (valid) {
+            if (e.res) w[j] += __bfloat162float(((const bf16*)e.res)[orow * e.ld_res + n + j]);
+            if (e.accumulate) w[j] += __bfloat162float(op[j]);
+            if (e.relu) w[j] = fmaxf(w[j], 0.f);
+            if (e.mask && !(__bfloat162float(((const bf16*)e.mask)[orow * e.ld_mask + n + j]) > 0.f)) w[j] = 0.f;
+            op[j] = __float2bfloat16_rn(w[j]);
+          }
+        } else {
+          w[j] = 0.f;
+        }
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void epi_chunk_f32(const TgParams& p, float* v, long long orow, int nb, bool valid) {
+  const asf_epilogue_t& e = p.epi;
+  float* op = (float*)p.out + orow * p.ld_out + nb;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int n = nb + j;
+    if (n < p.N) {
+      if (e.scale) v[j] *= e.scale[n];
+      if (e.shift) v[j] += e.shift[n];
+      if (valid) {
+        if (e.res) v[j] += ((const float*)e.res)[orow * e.ld_res + n];
+        if (e.accumulate) v[j] += op[j];
+        if (e.relu) v[j] = fmaxf(v[j], 0.f);
+        if (e.mask && !(((const float*)e.mask)[orow * e.ld_mask + n] > 0.f)) v[j] = 0.f;
+        op[j] = v[j];
+      }
+    } else {
+      v[j] = 0.f;
+    }
+  }
+}
+
+// per-channel sum / sum of squares over the 32 rows of this warp for 16 consecutive channels: recursive-halving
+// transpose-reduce (16 shuffles per quantity instead of 80), then one atomic per channel from the even lanes.
+__device__ __forceinline__ void epi_stats16(const TgParams& p, const float* v, int nb, bool valid, int lane) {
+  const asf_epilogue_t& e = p.epi;
+  float a[16], q[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float x = valid ? v[j] : 0.f;
+    a[j] = x;
+    q[j] = x * x;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const bool up = lane & 16;
+    const float sa_ = up ? a[i] : a[i + 8], ka = up ? a[i + 8] : a[i];
+    const float sq_ = up ? q[i] : q[i + 8], kq = up ? q[i + 8] : q[i];
+    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 16);
+    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const bool up = lane & 8;
+    const float sa_ = up ? a[i] : a[i + 4], ka = up ? a[i + 4] : a[i];
+    const float sq_ = up ? q[i] : q[i + 4], kq = up ? q[i + 4] : q[i];
+    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 8);
+    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const bool up = lane & 4;
+    const float sa_ = up ? a[i] : a[i + 2], ka = up ? a[i + 2] : a[i];
+    const float sq_ = up ? q[i] : q[i + 2], kq = up ? q[i + 2] : q[i];
+    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 4);
+    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 4);
+  }
+  {
+    const bool up = lane & 2;
+    const float sa_ = up ? a[0] : a[1], ka = up ? a[1] : a[0];
+    const float sq_ = up ? q[0] : q[1], kq = up ? q[1] : q[0];
+    a[0] = ka + __shfl_xor_sync(0xffffffffu, sa_, 2);
+    q[0] = kq + __shfl_xor_sync(0xffffffffu, sq_, 2);
+  }
+  a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
+  q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
+  const int jch = (((lane >> 4) & 1) << 3) | (((lane >> 3) & 1) << 2) | (((lane >> 2) & 1) << 1) | ((lane >> 1) & 1);
+  const int n = nb + jch;
+  if (!(lane & 1) && n < p.N) {
+    atomicAdd(e.stats + n, a[0]);
+    atomicAdd(e.stats + e.stats_stride + n, q[0]);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ mode 0
@@ -261,8 +438,9 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid
           const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
           const uint64_t adesc = make_sdesc(sa, 16, 1024);
           const uint64_t bdesc = make_sdesc(sa + TG_A_BYTES, 16, 1024);
-#pragma unroll
-          for (int k = 0; k < TG_KC / 16; ++k)  // +32 bytes (2 x 16B units) per UMMA_K=16 step inside the swizzle row
+          const int kc = ki % p.kchunks;
+          const int ksteps = min(TG_KC / 16, (p.K - kc * TG_KC + 15) >> 4);  // skip the zero-filled tail of a short chunk
+          for (int k = 0; k < ksteps; ++k)  // +32 bytes (2 x 16B units) per UMMA_K=16 step inside the swizzle row
             umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (ki | k) != 0);
           umma_commit(&sh->empty[s]);
           if (++s == p.stages) { s = 0; ph ^= 1; }
@@ -271,165 +449,49 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid
       }
     }
   } else {
-    // ===== epilogue warps (TMEM lane quarter = warp % 4) =====
+    // ===== epilogue: two groups of four warps (warps 2..5 own TMEM buffer 0, warps 6..9 buffer 1), so the
+    // epilogues of two consecutive tiles run concurrently.  TMEM lane quarter of a warp = warp % 4.
+    const int group = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;
     const int r1 = r & ((1 << p.m_log2[0]) - 1);
     const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
     const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
-    const asf_epilogue_t& e = p.epi;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int buf = it & 1;
+      if ((it & 1) != group) continue;
+      const int buf = group;
       const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
       int st[3];
       tile_coords(p, m_tile, st);
       const int m1 = st[0] + r1, m2 = st[1] + r2, m3 = st[2] + r3;
       const bool valid = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
       const long long orow = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
-      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
-      tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
       const int n0 = n_tile * p.block_n;
-      for (int ch = 0; ch < p.block_n / 16; ++ch) {
-        const int nb = n0 + ch * 16;
-        if (nb >= p.N) break;
-        float v[16];
-        tmem_ld16(taddr0 + (uint32_t)(ch * 16), v);
-        const bool full16 = p.vec_ok && (nb + 16 <= p.N);
+      int nch = (min(p.block_n, p.N - n0) + 31) >> 5;
+      EpiOps cur, nxt;
+      if (p.out_bf16) epi_prefetch(p, cur, orow, n0, valid);
+      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
+      tc_fence_after();
+      for (int ch = 0; ch < nch; ++ch) {
+        const int nb = n0 + ch * 32;
+        uint32_t raw[32];
+        tmem_ld32_issue(taddr0 + (uint32_t)(ch * 32), raw);
+        if (p.out_bf16 && ch + 1 < nch) epi_prefetch(p, nxt, orow, nb + 32, valid);
+        tmem_ld_wait();
+        float v[32];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = nb + j;
-          if (n < p.N) {
-            if (e.scale) v[j] *= e.scale[n];
-            if (e.shift) v[j] += e.shift[n];
-          } else {
-            v[j] = 0.f;
-          }
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        if (p.out_bf16)
+          epi_chunk_bf16(p, cur, v, orow, nb, valid);
+        else
+          epi_chunk_f32(p, v, orow, nb, valid);
+        if (p.epi.stats) {
+          epi_stats16(p, v, nb, valid, lane);
+          if (nb + 16 < p.N) epi_stats16(p, v + 16, nb + 16, valid, lane);
         }
-        if (valid) {
-          if (p.out_bf16) {
-            bf16* o = (bf16*)p.out + orow * p.ld_out + nb;
-            if (full16) {
-              if (e.res) {
-                const uint4* rp = (const uint4*)((const bf16*)e.res + orow * e.ld_res + nb);
-                uint4 q0 = rp[0], q1 = rp[1];
-                const bf16* rb0 = (const bf16*)&q0;
-                const bf16* rb1 = (const bf16*)&q1;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { v[j] += __bfloat162float(rb0[j]); v[8 + j] += __bfloat162float(rb1[j]); }
-              }
-              if (e.accumulate) {
-                const uint4* rp = (const uint4*)o;
-                uint4 q0 = rp[0], q1 = rp[1];
-                const bf16* rb0 = (const bf16*)&q0;
-                const bf16* rb1 = (const bf16*)&q1;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { v[j] += __bfloat162float(rb0[j]); v[8 + j] += __bfloat162float(rb1[j]); }
-              }
-              if (e.relu) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-              }
-              if (e.mask) {
-                const uint4* rp = (const uint4*)((const bf16*)e.mask + orow * e.ld_mask + nb);
-                uint4 q0 = rp[0], q1 = rp[1];
-                const bf16* rb0 = (const bf16*)&q0;
-                const bf16* rb1 = (const bf16*)&q1;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  if (!(__bfloat162float(rb0[j]) > 0.f)) v[j] = 0.f;
-                  if (!(__bfloat162float(rb1[j]) > 0.f)) v[8 + j] = 0.f;
-                }
-              }
-              uint4 w0, w1;
-              __nv_bfloat162* wb0 = (__nv_bfloat162*)&w0;
-              __nv_bfloat162* wb1 = (__nv_bfloat162*)&w1;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                wb0[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                wb1[j] = __floats2bfloat162_rn(v[8 + 2 * j], v[8 + 2 * j + 1]);
-              }
-              ((uint4*)o)[0] = w0;
-              ((uint4*)o)[1] = w1;
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const int n = nb + j;
-                if (n < p.N) {
-                  if (e.res) v[j] += __bfloat162float(((const bf16*)e.res)[orow * e.ld_res + n]);
-                  if (e.accumulate) v[j] += __bfloat162float(o[j]);
-                  if (e.relu) v[j] = fmaxf(v[j], 0.f);
-                  if (e.mask && !(__bfloat162float(((const bf16*)e.mask)[orow * e.ld_mask + n]) > 0.f)) v[j] = 0.f;
-                  o[j] = __float2bfloat16_rn(v[j]);
-                }
-              }
-            }
-          } else {
-            float* o = (float*)p.out + orow * p.ld_out + nb;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int n = nb + j;
-              if (n < p.N) {
-                if (e.res) v[j] += ((const float*)e.res)[orow * e.ld_res + n];
-                if (e.accumulate) v[j] += o[j];
-                if (e.relu) v[j] = fmaxf(v[j], 0.f);
-                if (e.mask && !(((const float*)e.mask)[orow * e.ld_mask + n] > 0.f)) v[j] = 0.f;
-                o[j] = v[j];
-              }
-            }
-          }
-        }
-        if (e.stats) {
-          // per-channel sum / sum of squares over the 32 rows of this warp: recursive-halving transpose-reduce
-          // (16 shuffles per quantity instead of 80), then one atomic per channel from the even lanes.
-          float a[16], q[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float x = valid ? v[j] : 0.f;
-            a[j] = x;
-            q[j] = x * x;
-          }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const bool up = lane & 16;
-            const float sa_ = up ? a[i] : a[i + 8], ka = up ? a[i + 8] : a[i];
-            const float sq_ = up ? q[i] : q[i + 8], kq = up ? q[i + 8] : q[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 16);
-            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 16);
-          }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const bool up = lane & 8;
-            const float sa_ = up ? a[i] : a[i + 4], ka = up ? a[i + 4] : a[i];
-            const float sq_ = up ? q[i] : q[i + 4], kq = up ? q[i + 4] : q[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 8);
-            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 8);
-          }
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const bool up = lane & 4;
-            const float sa_ = up ? a[i] : a[i + 2], ka = up ? a[i + 2] : a[i];
-            const float sq_ = up ? q[i] : q[i + 2], kq = up ? q[i + 2] : q[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 4);
-            q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 4);
-          }
-          {
-            const bool up = lane & 2;
-            const float sa_ = up ? a[0] : a[1], ka = up ? a[1] : a[0];
-            const float sq_ = up ? q[0] : q[1], kq = up ? q[1] : q[0];
-            a[0] = ka + __shfl_xor_sync(0xffffffffu, sa_, 2);
-            q[0] = kq + __shfl_xor_sync(0xffffffffu, sq_, 2);
-          }
-          a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
-          q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
-          const int jch = (((lane >> 4) & 1) << 3) | (((lane >> 3) & 1) << 2) | (((lane >> 2) & 1) << 1) | ((lane >> 1) & 1);
-          const int n = nb + jch;
-          if (!(lane & 1) && n < p.N) {
-            atomicAdd(e.stats + n, a[0]);
-            atomicAdd(e.stats + e.stats_stride + n, q[0]);
-          }
-        }
+        cur = nxt;
       }
       tc_fence_before();
       __syncwarp();
@@ -448,7 +510,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid
 constexpr int WG_STAGE_BYTES = 4 * 16384;  // Y: 2 boxes [128 rows][64 ch], X: 2 boxes [128 rows][64 ch]
 constexpr int WG_STAGES = 3;
 
-__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_wgrad_kernel(const __grid_constant__ TgParams p) {
+__global__ void __launch_bounds__(WG_THREADS, 1) tapgemm_wgrad_kernel(const __grid_constant__ TgParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   TgShared* sh = (TgShared*)(smem + (size_t)WG_STAGES * WG_STAGE_BYTES);
@@ -632,9 +694,11 @@ struct ProfRec {
   cudaEvent_t e0, e1;
   double flops;
   int mode;
+  int M, N, K, taps, block_n, grid;
+  float ms;
 };
 static ProfRec* g_prof = nullptr;
-static int g_prof_cap = 0, g_prof_n = 0;
+static int g_prof_cap = 0, g_prof_n = 0, g_prof_last = 0;
 static bool g_prof_on = false;
 
 static ProfRec* prof_begin(cudaStream_t st, int mode, double flops) {
@@ -750,6 +814,10 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     int grid = (int)(total < num_sms() ? total : num_sms());
     const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
     ProfRec* pr = prof_begin(st, 0, flops);
+    if (pr) {
+      pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
+      pr->block_n = bn; pr->grid = grid;
+    }
     tapgemm_fwd_kernel<<<grid, TG_THREADS, smem, st>>>(p);
     prof_end(pr, st);
     ASF_LAUNCH_CHECK();
@@ -779,7 +847,8 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   int ks = q->ksplit;
   if (ks <= 0) {
     ks = (int)cdiv(2 * num_sms(), base_tiles);
-    if (ks > p.m_tiles_total) ks = p.m_tiles_total;
+    // every CTA ends with a 128x128 fp32 atomic flush: give it at least 8 row tiles of MMA work to amortise that
+    if (ks > p.m_tiles_total / 8) ks = p.m_tiles_total / 8;
     if (ks < 1) ks = 1;
   }
   ASF_CHECK_ARG(ks >= 1 && ks <= p.m_tiles_total, "asf_tapgemm: ksplit %d out of range (row tiles %d)", ks, p.m_tiles_total);
@@ -794,7 +863,11 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   ASF_CHECK_ARG(grid < (1ll << 31), "asf_tapgemm: wgrad grid too large");
   const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
   ProfRec* pr = prof_begin(st, 1, flops);
-  tapgemm_wgrad_kernel<<<(unsigned)grid, TG_THREADS, smem, st>>>(p);
+  if (pr) {
+    pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
+    pr->block_n = ks; pr->grid = (int)grid;
+  }
+  tapgemm_wgrad_kernel<<<(unsigned)grid, WG_THREADS, smem, st>>>(p);
   prof_end(pr, st);
   ASF_LAUNCH_CHECK();
   return debug_sync(st);
@@ -829,10 +902,20 @@ extern "C" int asf_prof_stop(double* ms, double* flops, long long* launches) {
     float t = 0.f;
     ASF_CUDA(cudaEventElapsedTime(&t, g_prof[i].e0, g_prof[i].e1));
     const int m = g_prof[i].mode ? 1 : 0;
+    g_prof[i].ms = t;
     ms[m] += t;
     flops[m] += g_prof[i].flops;
     launches[m] += 1;
   }
+  g_prof_last = g_prof_n;
   g_prof_n = 0;
+  return 0;
+}
+
+extern "C" int asf_prof_record(int i, double* out) {
+  ASF_CHECK_ARG(i >= 0 && i < g_prof_last && out, "asf_prof_record: index %d out of range (%d records)", i, g_prof_last);
+  const ProfRec& r = g_prof[i];
+  out[0] = r.mode; out[1] = r.ms; out[2] = r.flops; out[3] = r.M; out[4] = r.N; out[5] = r.K; out[6] = r.taps;
+  out[7] = r.block_n; out[8] = r.grid;
   return 0;
 }

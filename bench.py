@@ -258,7 +258,7 @@ def run_ours(args):
         if not train:
             with torch.no_grad():
                 return model(x)[0]
-        opt.zero_grad(set_to_none=False)
+        opt.zero_grad()
         verb, noun = model(x)
         loss = 0.5 * (ce(verb, yv) + ce(noun, yn))
         loss.backward()

@@ -46,6 +46,8 @@ long long asf_launch_count(void);
  * FLOPs (2 * M * N * K * taps of each launch) and the number of launches. */
 int asf_prof_start(int max_records);
 int asf_prof_stop(double* ms, double* flops, long long* launches);
+/* record i of the last asf_prof_stop: out[9] = {mode, ms, flops, M, N, K, taps, block_n (mode 1: ksplit), grid} */
+int asf_prof_record(int i, double* out);
 /* 1 if the current device is sm_100 (tcgen05/TMA kernels can run), 0 otherwise, <0 on error. */
 int asf_device_is_sm100(void);
 
@@ -184,6 +186,19 @@ int asf_pack_weight(const float* w_oihw, void* packed, int dtype, int O, int I, 
 /* -> transposed packed [I][kt*kf][O] (dtype), scaled by rscale[o] */
 int asf_pack_weight_t(const float* w_oihw, void* packed, int dtype, int O, int I, int taps, const float* rscale,
                       void* stream);
+/* Every conv of the network in one launch.  descs_dev: DEVICE array of n descriptors sorted by chunk0, where unit i
+ * owns the blocks [chunk0_i, chunk0_{i+1}) of 2048 destination elements each (chunks_i = ceil(O*I*taps / 2048));
+ * total_chunks = sum of chunks_i.  packed_t may be NULL. */
+typedef struct {
+  const float* w;      /* OIHW fp32 master weights */
+  void* packed;        /* [O][taps][I] */
+  void* packed_t;      /* [I][taps][O] or NULL */
+  const float* rscale; /* per-output-channel scale (folded BN) or NULL */
+  int32_t O, I, taps, dtype;
+  int64_t chunk0;
+} asf_pack_desc_t;
+#define ASF_PACK_CHUNK 2048
+int asf_pack_weights_multi(const asf_pack_desc_t* descs_dev, int n, long long total_chunks, void* stream);
 /* dwp [O][taps][I] fp32 -> dw_oihw [O][I][taps] = (accumulate ? dw : 0) + rscale[o] * dwp */
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
                      int accumulate, void* stream);
@@ -208,10 +223,11 @@ int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, v
 /* backward reductions: red[c] += sum dz, red[C + c] += sum dz * (x - mean[c]) * invstd[c] */
 int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, float* red, void* stream);
-/* dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count);  dgamma = red[C+c], dbeta = red[c] */
+/* dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count);  dgamma (+)= red[C+c], dbeta (+)= red[c]
+ * (+= when accumulate != 0, the autograd convention for an existing .grad) */
 int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
                      int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
-                     const float* red, double count, float* dgamma, float* dbeta, void* stream);
+                     const float* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream);
 /* elementwise helper: y = (mask > 0) ? (a (+ b)) : 0  -- ReLU backward / gradient accumulation */
 int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const void* mask, int64_t ld_mask,
                  void* y, int64_t ld_y, int dtype, int64_t rows, int C, void* stream);

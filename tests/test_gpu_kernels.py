@@ -213,7 +213,7 @@ def test_bn_stats_apply_backward(dtype):
     L.call("asf_bn_bwd_reduce", L.ptr(dz), Cn, L.ptr(x), Cn, code, rows, Cn, L.ptr(mean), L.ptr(invstd), L.ptr(red), st)
     dx, dg, db = torch.empty_like(x), torch.empty(Cn, device="cuda"), torch.empty(Cn, device="cuda")
     L.call("asf_bn_bwd_apply", L.ptr(dz), Cn, L.ptr(x), Cn, L.ptr(dx), Cn, code, rows, Cn, L.ptr(gamma), L.ptr(mean),
-           L.ptr(invstd), L.ptr(red), C.c_double(rows), L.ptr(dg), L.ptr(db), st)
+           L.ptr(invstd), L.ptr(red), C.c_double(rows), L.ptr(dg), L.ptr(db), 0, st)
     torch.cuda.synchronize()
     assert rel_err(dx, xf.grad) < (1e-4 if dtype == torch.float32 else 1e-2)
     assert torch.allclose(db, dz.float().sum(0), rtol=1e-3, atol=1e-2)

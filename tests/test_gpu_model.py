@@ -132,14 +132,23 @@ def test_train_step_gradients(golden_dir, freeze, dtype, state):
     assert errs["logits0"] < tol_logit and errs["logits1"] < tol_logit and errs["loss"] < tol_logit
     if dtype == "float32":
         # one flipped ReLU-mask element out of the 2x100x4x256 of a late activation moves a per-tensor relative
-        # error by ~2e-3 (the same fp32 oracle on CPU vs. on this GPU shows exactly such quanta), so the 1e-2
-        # criterion is asserted for >= 90 % of the tensors and 3e-2 for every tensor.
-        bound = {k: 3e-2 for k in gerr}
-        within = sum(1 for v in gerr.values() if v <= 1e-2) / len(gerr)
-        print("  tensors within 1e-2: %.1f %%" % (100 * within))
-        assert within >= 0.9, within
+        # error by ~2e-3, and the SAME fp32 oracle run on this GPU (cuDNN, TF32 off) instead of the CPU shows such
+        # quanta too.  reference_init: 1e-2 for >= 90 % of the tensors, 3e-2 for all, median < 1e-3.
+        # calibrated (chaotic backward): the yardstick is that oracle-vs-oracle noise, measured here per tensor.
         if state == "reference_init":
+            bound = {k: 3e-2 for k in gerr}
+            within = sum(1 for v in gerr.values() if v <= 1e-2) / len(gerr)
+            print("  tensors within 1e-2: %.1f %%" % (100 * within))
+            assert within >= 0.9, within
             assert float(np.median(list(gerr.values()))) < 1e-3
+        else:
+            sdg = {k: v.cuda() for k, v in sd.items()}
+            _, _, gg, _ = M.loss_and_grads(ocfg, sdg, [t.cuda() for t in inputs], {k: v.cuda() for k, v in labels.items()})
+            noise = {k: _rel(gg[k], rgrads[k]) for k in gerr}
+            med_n, med_o = float(np.median(list(noise.values()))), float(np.median(list(gerr.values())))
+            print("  oracle-on-GPU vs oracle-on-CPU median grad rel err: %.2e (ours %.2e)" % (med_n, med_o))
+            bound = {k: max(1e-2, 4.0 * noise[k], 4.0 * med_n) for k in gerr}
+            assert med_o <= max(5e-3, 2.5 * med_n), (med_o, med_n)
     else:
         ag = _autocast_grads(ocfg, sd, inputs, labels)
         aerr = {k: (_rel(ag[k], rgrads[k]) if float(rgrads[k].norm()) > 0 else float(ag[k].norm())) for k in gerr}
