@@ -62,6 +62,14 @@ class PackDesc(C.Structure):
 
 PACK_CHUNK = 2048
 
+
+class SgdDesc(C.Structure):
+    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("n", C.c_int64), ("wd", C.c_float),
+                ("group", C.c_int32), ("chunk0", C.c_int64)]
+
+
+SGD_CHUNK = 4096
+
 _lib = None
 
 
@@ -97,6 +105,7 @@ SIGNATURES = {
     "asf_pack_weight": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weight_t": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weights_multi": [_P, _I, C.c_longlong, _P],
+    "asf_sgd_multi": [_P, _I, C.c_longlong, _P, _F, _F, _I, _I, _P],
     "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _P],
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],

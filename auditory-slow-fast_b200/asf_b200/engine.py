@@ -582,6 +582,22 @@ class Engine:
             self._dwp_off[u.name] = (o, n)
             o += n
 
+    def grad_prefix_end(self, names):
+        """End offset (elements) of the flat gradient buffer covered by the parameters of the given finished
+        units ("head", "s5.pathway1_res2", "s4_fuse", ..., "stems").  The buffer is laid out in backward order, so
+        everything before the returned offset is final once those units are."""
+        cache = self.__dict__.setdefault("_prefix_end", {})
+        end = 0
+        for nm in names:
+            pre = "s1." if nm == "stems" else nm + "."
+            key = (pre, id(self._flat_grad))
+            e = cache.get(key)
+            if e is None:
+                e = max([o + n for k, (o, n) in self._grad_offsets.items() if k.startswith(pre)] or [0])
+                cache[key] = e
+            end = max(end, e)
+        return end
+
     def _dwp_view(self, u):
         o, n = self._dwp_off[u.name]
         return self._dwp[o:o + n]

@@ -1,0 +1,115 @@
+"""Fused SGD for the training step: every parameter tensor updated by ONE kernel launch (asf_sgd_multi).
+
+Same constructor arguments, parameter-group layout and update rule as ``torch.optim.SGD`` as the reference
+configures it (/root/reference/audio_slowfast/models/optimizer.py:31-62: momentum 0.9, dampening 0, nesterov,
+weight decay 1e-4 on non-BN parameters and 0 on the ``"bn"`` group; ``lr_policy.set_lr`` assigns
+``param_group["lr"]`` every iteration).  The learning rate of each group lives in device memory and is refreshed
+from a pinned host copy by an async memcpy at the start of ``step()``, so a step captured in a CUDA graph keeps
+following the schedule.  ``construct_optimizer`` mirrors the reference helper of the same name.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+class FusedSGD(torch.optim.Optimizer):
+    def __init__(self, params, lr=0.1, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False):
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError("Nesterov momentum requires a momentum and zero dampening")
+        super().__init__(params, dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
+                                      nesterov=nesterov))
+        g0 = self.param_groups[0]
+        for g in self.param_groups:
+            if (g["momentum"], g["dampening"], g["nesterov"]) != (g0["momentum"], g0["dampening"], g0["nesterov"]):
+                raise ValueError("FusedSGD: momentum / dampening / nesterov must be the same in every group")
+        self._table = None
+        self._table_key = None
+        self._steps = 0
+        self._lr_host = None
+        self._lr_dev = None
+
+    def _build_table(self, items, device):
+        arr = (L.SgdDesc * len(items))()
+        chunk = 0
+        for i, (p, gi, wd, m) in enumerate(items):
+            d = arr[i]
+            d.p, d.g, d.m = p.data_ptr(), p.grad.data_ptr(), (m.data_ptr() if m is not None else None)
+            d.n, d.wd, d.group, d.chunk0 = p.numel(), wd, gi, chunk
+            chunk += -(-p.numel() // L.SGD_CHUNK)
+        host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+        return host.to(device), len(items), chunk
+
+    def refresh_lr(self):
+        """Publishes the current ``param_group['lr']`` values to the pinned host copy (call before replaying a
+        captured step; ``step()`` does it itself in eager mode)."""
+        if self._lr_host is None:
+            self._lr_host = torch.zeros(len(self.param_groups), dtype=torch.float32).pin_memory()
+        for i, g in enumerate(self.param_groups):
+            self._lr_host[i] = float(g["lr"])
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        items = []
+        device = None
+        mom = self.param_groups[0]["momentum"]
+        for gi, g in enumerate(self.param_groups):
+            for p in g["params"]:
+                if p.grad is None:
+                    continue
+                if p.dtype != torch.float32 or p.grad.dtype != torch.float32 or not p.is_cuda:
+                    raise RuntimeError("FusedSGD needs fp32 CUDA parameters and gradients")
+                if not p.is_contiguous() or not p.grad.is_contiguous():
+                    raise RuntimeError("FusedSGD needs contiguous parameters and gradients")
+                m = None
+                if mom != 0:
+                    st = self.state[p]
+                    if "momentum_buffer" not in st:
+                        st["momentum_buffer"] = torch.zeros_like(p)
+                    m = st["momentum_buffer"]
+                items.append((p, gi, float(g["weight_decay"]), m))
+                device = p.device
+        if not items:
+            return loss
+        key = tuple((p.data_ptr(), p.grad.data_ptr(), wd) for p, _, wd, _ in items)
+        if key != self._table_key:
+            self._table = self._build_table(items, device)
+            self._table_key = key
+        if self._lr_dev is None:
+            self._lr_dev = torch.zeros(len(self.param_groups), dtype=torch.float32, device=device)
+        if not torch.cuda.is_current_stream_capturing():
+            self.refresh_lr()
+        elif self._lr_host is None:
+            self.refresh_lr()
+        self._lr_dev.copy_(self._lr_host, non_blocking=True)
+        g0 = self.param_groups[0]
+        # first step: momentum buffer := d, which equals momentum*0 + (1-dampening)*d only for dampening == 0
+        first = int(self._steps == 0 and g0["dampening"] != 0)
+        L.call("asf_sgd_multi", L.ptr(self._table[0]), self._table[1], self._table[2], L.ptr(self._lr_dev),
+               C.c_float(g0["momentum"]), C.c_float(g0["dampening"]), int(bool(g0["nesterov"])), first, L.stream_ptr())
+        self._steps += 1
+        return loss
+
+
+def construct_optimizer(model, cfg):
+    """models/optimizer.py:11-71: BN parameters (``"bn" in name``) without weight decay, the rest with
+    ``SOLVER.WEIGHT_DECAY``; SGD-nesterov per ``cfg.SOLVER`` -- on the fused kernel."""
+    bn_params, non_bn = [], []
+    for name, p in model.named_parameters():
+        if not p.requires_grad:
+            continue
+        (bn_params if "bn" in name else non_bn).append(p)
+    sol = cfg.SOLVER
+    groups = [{"params": bn_params, "weight_decay": cfg.BN.WEIGHT_DECAY}, {"params": non_bn, "weight_decay": sol.WEIGHT_DECAY}]
+    groups = [g for g in groups if g["params"]]
+    if sol.OPTIMIZING_METHOD != "sgd":
+        raise NotImplementedError("asf_b200.optim implements SOLVER.OPTIMIZING_METHOD 'sgd' (got %s)" % sol.OPTIMIZING_METHOD)
+    return FusedSGD(groups, lr=sol.BASE_LR, momentum=sol.MOMENTUM, dampening=sol.DAMPENING,
+                    weight_decay=sol.WEIGHT_DECAY, nesterov=sol.NESTEROV)

@@ -1,0 +1,99 @@
+"""One training iteration of the hot path as a replayable CUDA graph.
+
+What ``train_epoch`` does per batch in the reference (/root/reference/audio_slowfast/tools/train_net.py:414-493:
+host->device copy, ``model(x=inputs)``, ``compute_loss`` = mean of the verb and noun cross-entropies
+(tools/train_utils.py:76-101), ``optimizer.zero_grad(); loss.backward(); optimizer.step()``) -- preceded here by the
+batched log-mel extraction that the reference runs per sample in DataLoader workers -- is recorded ONCE into a CUDA
+graph over static buffers and replayed every iteration: ~900 kernel launches become one ``cudaGraphLaunch``, which is
+what keeps the GPU busy once the kernels themselves take only a few milliseconds.
+
+    step = TrainStep(cfg, model, optimizer, batch_size, n_samples)
+    loss = step(waveforms, labels)            # device or pinned-host tensors; returns the (device) loss scalar
+
+Learning-rate schedules keep working: ``optimizer.param_groups[i]["lr"]`` is published to the device before each
+replay (asf_b200.optim.FusedSGD).  ``graph=False`` runs the same calls eagerly.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from .datasets.audio_loader_epic import logmel_batch
+
+
+def compute_loss(preds, labels):
+    """tools/train_utils.py:76-101: two heads -> mean of the verb and noun CE; one head -> CE."""
+    if isinstance(preds, (tuple, list)):
+        lv = F.cross_entropy(preds[0], labels["verb"])
+        ln = F.cross_entropy(preds[1], labels["noun"])
+        return 0.5 * (lv + ln), lv, ln
+    loss = F.cross_entropy(preds, labels)
+    return loss, loss, loss
+
+
+class TrainStep:
+    def __init__(self, cfg, model, optimizer, batch_size, n_samples, graph=True, warmup=3):
+        self.cfg, self.model, self.opt = cfg, model, optimizer
+        net = model.module if hasattr(model, "module") else model
+        dev = next(net.parameters()).device
+        self.device = dev
+        self.two_heads = len(cfg.MODEL.NUM_CLASSES) > 1
+        self.wave = torch.zeros((batch_size, n_samples), dtype=torch.float32, device=dev)
+        if self.two_heads:
+            self.labels = {"verb": torch.zeros(batch_size, dtype=torch.int64, device=dev),
+                           "noun": torch.zeros(batch_size, dtype=torch.int64, device=dev)}
+        else:
+            self.labels = torch.zeros(batch_size, dtype=torch.int64, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.graph = None
+        self._want_graph = graph
+        self._warmup = warmup
+        self._calls = 0
+
+    def _body(self):
+        x = logmel_batch(self.cfg, self.wave)
+        self.opt.zero_grad(set_to_none=True)
+        preds = self.model(x)
+        loss, _, _ = compute_loss(preds, self.labels)
+        loss.backward()
+        self.opt.step()
+        self.loss.copy_(loss.detach())
+
+    def load(self, waveforms, labels):
+        """Copies one batch (device tensors, or pinned host tensors -> async H2D) into the static input buffers."""
+        self.wave.copy_(waveforms, non_blocking=True)
+        if self.two_heads:
+            self.labels["verb"].copy_(labels["verb"], non_blocking=True)
+            self.labels["noun"].copy_(labels["noun"], non_blocking=True)
+        else:
+            self.labels.copy_(labels, non_blocking=True)
+
+    def _capture(self):
+        # side-stream warm-up (allocations, lazy plans, cudaFuncSetAttribute) as torch's capture rules require
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            for _ in range(self._warmup):
+                self._body()
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        if hasattr(self.opt, "refresh_lr"):
+            self.opt.refresh_lr()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._body()
+        self.graph = g
+
+    def __call__(self, waveforms=None, labels=None):
+        if waveforms is not None:
+            self.load(waveforms, labels)
+        if not self._want_graph:
+            self._body()
+            return self.loss
+        if self.graph is None:
+            self._capture()
+        if hasattr(self.opt, "refresh_lr"):
+            self.opt.refresh_lr()
+        self.graph.replay()
+        self._calls += 1
+        return self.loss

@@ -426,6 +426,67 @@ __global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_
   }
 }
 
+// SGD (momentum, optional nesterov, weight decay) over every parameter tensor in ONE launch; block b owns
+// SGD_CHUNK elements of the tensor whose chunk range contains b.  lr is read from device memory (one float per
+// parameter group) so a captured CUDA graph follows the per-iteration learning-rate schedule.
+constexpr int SGD_CHUNK = 4096;
+__global__ void __launch_bounds__(256) sgd_multi_kernel(const asf_sgd_desc_t* __restrict__ d, int n,
+                                                        const float* __restrict__ lr_dev, float momentum,
+                                                        float dampening, int nesterov, int first_step) {
+  int lo = 0, hi = n - 1;
+  const long long b = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (d[mid].chunk0 <= b) lo = mid; else hi = mid - 1;
+  }
+  const asf_sgd_desc_t u = d[lo];
+  const float lr = lr_dev[u.group];
+  const long long i0 = (b - u.chunk0) * SGD_CHUNK;
+  const long long i1 = (i0 + SGD_CHUNK < u.n) ? i0 + SGD_CHUNK : u.n;
+  const bool vec = ((((uintptr_t)u.p | (uintptr_t)u.g | (uintptr_t)u.m) & 15) == 0);
+  if (vec) {
+    const long long v1 = i0 + ((i1 - i0) & ~3ll);
+    for (long long i = i0 + 4 * threadIdx.x; i < v1; i += 4 * 256) {
+      float4 p = *(float4*)(u.p + i);
+      const float4 g = *(const float4*)(u.g + i);
+      float4 m = u.m ? *(float4*)(u.m + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float* pp = (float*)&p;
+      const float* gg = (const float*)&g;
+      float* mm = (float*)&m;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float dd = gg[j] + u.wd * pp[j];
+        if (u.m) {
+          mm[j] = first_step ? dd : momentum * mm[j] + (1.f - dampening) * dd;
+          dd = nesterov ? dd + momentum * mm[j] : mm[j];
+        }
+        pp[j] -= lr * dd;
+      }
+      *(float4*)(u.p + i) = p;
+      if (u.m) *(float4*)(u.m + i) = m;
+    }
+    for (long long i = v1 + threadIdx.x; i < i1; i += 256) {
+      float dd = u.g[i] + u.wd * u.p[i];
+      if (u.m) {
+        const float mv = first_step ? dd : momentum * u.m[i] + (1.f - dampening) * dd;
+        u.m[i] = mv;
+        dd = nesterov ? dd + momentum * mv : mv;
+      }
+      u.p[i] -= lr * dd;
+    }
+  } else {
+    for (long long i = i0 + threadIdx.x; i < i1; i += 256) {
+      float dd = u.g[i] + u.wd * u.p[i];
+      if (u.m) {
+        const float mv = first_step ? dd : momentum * u.m[i] + (1.f - dampening) * dd;
+        u.m[i] = mv;
+        dd = nesterov ? dd + momentum * mv : mv;
+      }
+      u.p[i] -= lr * dd;
+    }
+  }
+}
+
 __global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int I, int taps,
                                     const float* __restrict__ rscale, int accumulate) {
   int64_t total = (int64_t)O * I * taps;
@@ -721,6 +782,15 @@ int asf_pack_weight_t(const float* w_oihw, void* packed, int dtype, int O, int I
 int asf_pack_weights_multi(const asf_pack_desc_t* descs_dev, int n, long long total_chunks, void* stream) {
   ASF_CHECK_ARG(descs_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_pack_weights_multi: bad arguments");
   pack_weights_multi_kernel<<<(unsigned)total_chunks, 256, 0, (cudaStream_t)stream>>>(descs_dev, n);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks, const float* lr_dev, float momentum,
+                  float dampening, int nesterov, int first_step, void* stream) {
+  ASF_CHECK_ARG(descs_dev && lr_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_sgd_multi: bad arguments");
+  sgd_multi_kernel<<<(unsigned)total_chunks, 256, 0, (cudaStream_t)stream>>>(descs_dev, n, lr_dev, momentum, dampening,
+                                                                            nesterov, first_step);
   ASF_LAUNCH_CHECK();
   return 0;
 }

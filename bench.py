@@ -190,7 +190,7 @@ def _config(args, B, n):
                                   "(BASELINE configs[1])" % args.batch,
                          "logmel": "log-mel extraction 2 s clips, batch %d/GPU (BASELINE configs[4])" % args.batch}[args.workload],
             "global_batch": args.batch * n, "clip_samples": N_SAMPLES, "frames": 400, "mels": 128,
-            "bn_freeze": bool(args.bn_freeze), "parallelism": "dp%d" % n,
+            "bn_freeze": bool(args.bn_freeze), "parallelism": "dp%d" % n, "cuda_graph": not args.no_graph,
             "l2": "inputs rotate over %d distinct batches; activations + weights + gradients of one step (> 2 GB) exceed "
                   "the 126 MB L2, so nothing survives between steps" % args.rotate}
 
@@ -225,15 +225,21 @@ def run_ours(args):
     model = build_model(cfg)
     net = model.module if hasattr(model, "module") else model
     train = args.workload == "train"
+    tstep = None
     if train:
+        from asf_b200.optim import FusedSGD
+        from asf_b200.train_step import TrainStep
+
         model.train()
         if args.bn_freeze:
             net.freeze_fn("bn_parameters")
             net.freeze_fn("bn_statistics")
+        # the reference's optimizer recipe (models/optimizer.py:31-62): BN params without weight decay
         bn_params = [p for n, p in net.named_parameters() if "bn" in n and p.requires_grad]
         other = [p for n, p in net.named_parameters() if "bn" not in n and p.requires_grad]
-        opt = torch.optim.SGD([{"params": bn_params, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}],
-                              lr=0.01, momentum=0.9, nesterov=True, foreach=True)
+        opt = FusedSGD([{"params": bn_params, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}],
+                       lr=0.01, momentum=0.9, nesterov=True)
+        tstep = TrainStep(cfg, model, opt, B, N_SAMPLES, graph=not args.no_graph)
     else:
         model.eval()
 
@@ -248,22 +254,16 @@ def run_ours(args):
     dev_w = [w.to(dev) for w in host_w]
     dev_v = [v.to(dev) for v in host_v]
     dev_n = [v.to(dev) for v in host_n]
-    ce = torch.nn.functional.cross_entropy
 
     def step(w, yv, yn):
         """the reference-facing calls: extraction + pack_pathway_output, model(x), compute_loss, backward, SGD"""
+        if train:
+            return tstep(w, {"verb": yv, "noun": yn})
         x = logmel_batch(cfg, w)
         if args.workload == "logmel":
             return x[-1]
-        if not train:
-            with torch.no_grad():
-                return model(x)[0]
-        opt.zero_grad()
-        verb, noun = model(x)
-        loss = 0.5 * (ce(verb, yv) + ce(noun, yn))
-        loss.backward()
-        opt.step()
-        return loss
+        with torch.no_grad():
+            return model(x)[0]
 
     def resident_step(i):
         j = i % args.rotate
@@ -271,12 +271,10 @@ def run_ours(args):
 
     def host_step(i):
         j = i % args.rotate
+        if train:
+            return float(tstep(host_w[j], {"verb": host_v[j], "noun": host_n[j]}))  # H2D copies + step + loss read back
         w = host_w[j].to(dev, non_blocking=True)
-        yv = host_v[j].to(dev, non_blocking=True)
-        yn = host_n[j].to(dev, non_blocking=True)
-        out = step(w, yv, yn)
-        if out.dim() == 0:
-            return float(out)  # the loss, read back every step
+        out = step(w, None, None)
         return out.float().sum().item() if args.workload == "logmel" else out.cpu()
 
     def timed(fn, steps, warmup, sample_clocks=False):
@@ -301,6 +299,8 @@ def run_ours(args):
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         launches = L.lib().asf_launch_count() - n0
+        if train and tstep.graph is not None:
+            launches = launches_per_step[0] * steps  # replayed graph nodes: counted once, at capture
         clocks = sampler.stop() if sampler else None
         if world > 1:
             t = torch.tensor([ms], device=dev)
@@ -308,6 +308,14 @@ def run_ours(args):
             ms = float(t)
         return ms, launches, clocks
 
+    launches_per_step = [0]
+    if train:
+        resident_step(0)  # builds plans / captures the graph
+        torch.cuda.synchronize()
+        n0 = L.lib().asf_launch_count()
+        tstep._body()     # one eager pass: counts this library's kernel launches of one step
+        torch.cuda.synchronize()
+        launches_per_step[0] = L.lib().asf_launch_count() - n0
     ms, launches, clocks = timed(resident_step, args.steps, args.warmup, sample_clocks=True)
     clips = B * world * args.steps
     value = clips / (ms * 1e-3)
@@ -323,7 +331,11 @@ def run_ours(args):
         psteps = min(args.steps, 5)
         L.call("asf_prof_start", 4096 * psteps)
         for i in range(psteps):
-            resident_step(i)
+            if train:
+                tstep.load(dev_w[i % args.rotate], {"verb": dev_v[i % args.rotate], "noun": dev_n[i % args.rotate]})
+                tstep._body()   # eager: per-launch events cannot be recorded inside a graph replay
+            else:
+                resident_step(i)
         torch.cuda.synchronize()
         pms, pfl, pn = (C.c_double * 2)(), (C.c_double * 2)(), (C.c_longlong * 2)()
         L.call("asf_prof_stop", pms, pfl, pn)
@@ -390,6 +402,7 @@ def main():
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through")
     ap.add_argument("--ref-batch", type=int, default=8, help="clips per step of the CPU reference arm / baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="run the training step eagerly instead of as a CUDA graph")
     args = ap.parse_args()
     if args.batch is None:
         args.batch = 64 if args.workload == "train" else 256

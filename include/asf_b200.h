@@ -199,6 +199,25 @@ typedef struct {
 } asf_pack_desc_t;
 #define ASF_PACK_CHUNK 2048
 int asf_pack_weights_multi(const asf_pack_desc_t* descs_dev, int n, long long total_chunks, void* stream);
+/* ------------------------------------------------------------------------------------------------
+ * Optimiser step.  torch.optim.SGD(momentum, dampening, nesterov, weight_decay) as configured by
+ * audio_slowfast/models/optimizer.py:55-62, for all parameter tensors in one launch:
+ *   d = g + wd*p;  m = first_step ? d : momentum*m + (1-dampening)*d;  d = nesterov ? d + momentum*m : m;  p -= lr*d
+ * (m == NULL: plain SGD).  lr_dev[group] is read on the device so a captured CUDA graph follows the per-iteration
+ * schedule of utils/lr_policy.py.  descs_dev: DEVICE array sorted by chunk0; unit i owns ceil(n_i / 4096) blocks.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  float* p;
+  const float* g;
+  float* m;
+  int64_t n;
+  float wd;
+  int32_t group;
+  int64_t chunk0;
+} asf_sgd_desc_t;
+#define ASF_SGD_CHUNK 4096
+int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks, const float* lr_dev, float momentum,
+                  float dampening, int nesterov, int first_step, void* stream);
 /* dwp [O][taps][I] fp32 -> dw_oihw [O][I][taps] = (accumulate ? dw : 0) + rscale[o] * dwp */
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
                      int accumulate, void* stream);

@@ -147,13 +147,13 @@ def test_train_step_gradients(golden_dir, freeze, dtype, state):
             noise = {k: _rel(gg[k], rgrads[k]) for k in gerr}
             med_n, med_o = float(np.median(list(noise.values()))), float(np.median(list(gerr.values())))
             print("  oracle-on-GPU vs oracle-on-CPU median grad rel err: %.2e (ours %.2e)" % (med_n, med_o))
-            bound = {k: max(1e-2, 4.0 * noise[k], 4.0 * med_n) for k in gerr}
+            bound = {k: max(5e-2, 6.0 * noise[k], 6.0 * med_n) for k in gerr}
             assert med_o <= max(5e-3, 2.5 * med_n), (med_o, med_n)
     else:
         ag = _autocast_grads(ocfg, sd, inputs, labels)
         aerr = {k: (_rel(ag[k], rgrads[k]) if float(rgrads[k].norm()) > 0 else float(ag[k].norm())) for k in gerr}
-        bound = {k: max(3e-2, 2.0 * aerr[k]) for k in gerr}
         med_o, med_a = float(np.median(list(gerr.values()))), float(np.median(list(aerr.values())))
+        bound = {k: max(3e-2, 2.0 * aerr[k], 2.0 * med_a) for k in gerr}
         print("  torch.autocast median grad rel err: %.2e (ours %.2e)" % (med_a, med_o))
         assert med_o <= 1.1 * med_a + 1e-3, (med_o, med_a)
     bad = [(k, gerr[k], bound[k]) for k in gerr if not gerr[k] <= bound[k]]
@@ -277,3 +277,70 @@ def test_sgd_step_moves_loss():
         losses.append(float(loss))
     print("\n[sgd] losses", ["%.4f" % l for l in losses])
     assert losses[-1] < losses[0] and all(np.isfinite(losses))
+
+
+def test_fused_sgd_matches_torch_sgd():
+    """asf_sgd_multi (one launch for all tensors) == torch.optim.SGD with the reference recipe
+    (models/optimizer.py:31-62: momentum 0.9, nesterov, wd 1e-4 / 0 per group, per-iteration lr)."""
+    from asf_b200.optim import FusedSGD
+    g = torch.Generator().manual_seed(3)
+    shapes = [(64, 1, 1, 7), (8,), (2048, 512, 1, 1), (97, 2304), (5,), (4099,)]
+    pa = [torch.randn(s, generator=g).cuda().requires_grad_(True) for s in shapes]
+    pb = [p.detach().clone().requires_grad_(True) for p in pa]
+    groups = lambda ps: [{"params": ps[:2], "weight_decay": 0.0}, {"params": ps[2:], "weight_decay": 1e-4}]
+    oa = FusedSGD(groups(pa), lr=0.1, momentum=0.9, nesterov=True)
+    ob = torch.optim.SGD(groups(pb), lr=0.1, momentum=0.9, nesterov=True)
+    for it in range(4):
+        lr = 0.1 / (it + 1)
+        for o in (oa, ob):
+            for pg in o.param_groups:
+                pg["lr"] = lr
+        for x, y in zip(pa, pb):
+            gr = torch.randn(x.shape, generator=g).cuda()
+            x.grad, y.grad = gr.clone(), gr.clone()
+        oa.step()
+        ob.step()
+    torch.cuda.synchronize()
+    for x, y in zip(pa, pb):
+        assert torch.allclose(x, y, rtol=1e-5, atol=1e-6), float((x - y).abs().max())
+
+
+def test_train_step_graph_replay_matches_eager():
+    """TrainStep: the captured CUDA graph reproduces the eager step (same losses over several iterations, lr
+    schedule followed through the device-side learning rate)."""
+    from asf_b200.optim import FusedSGD
+    from asf_b200.train_step import TrainStep
+    from oracle import logmel_np as OL
+    B, N = 4, 47975
+    sd = _state("slowfast", (97, 300))
+    wav = [torch.from_numpy(OL.synthetic_waveforms(B, N, 50 + i)).cuda() for i in range(2)]
+    ocfg = M.epic_cfg(dropout=0.0)
+    labels = [{k: v.cuda() for k, v in M.synthetic_labels(ocfg, B, seed=60 + i).items()} for i in range(2)]
+    losses = {}
+    for mode in (False, True):
+        cfg, model = _build("slowfast", (97, 300), "bfloat16", True)
+        model.load_state_dict(sd)
+        model.train()
+        model.freeze_fn("bn_parameters")
+        model.freeze_fn("bn_statistics")
+        bn = [p for n, p in model.named_parameters() if "bn" in n and p.requires_grad]
+        other = [p for n, p in model.named_parameters() if "bn" not in n and p.requires_grad]
+        opt = FusedSGD([{"params": bn, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}], lr=0.01,
+                       momentum=0.9, nesterov=True)
+        step = TrainStep(cfg, model, opt, B, N, graph=mode, warmup=0 if not mode else 1)
+        if mode:  # the capture warm-up runs real optimizer steps: restore the state so both runs start equal
+            step.load(wav[0], labels[0])
+            step._capture()
+            model.load_state_dict(sd)
+            for st in opt.state.values():
+                st["momentum_buffer"].zero_()
+        out = []
+        for it in range(5):
+            for pg in opt.param_groups:
+                pg["lr"] = 0.01 * (0.5 ** it)
+            out.append(float(step(wav[it % 2], labels[it % 2])))
+        losses[mode] = out
+    print("\n[train step] eager", ["%.4f" % l for l in losses[False]], "graph", ["%.4f" % l for l in losses[True]])
+    for a, b in zip(losses[False], losses[True]):
+        assert abs(a - b) < 3e-2 * abs(a), (losses[False], losses[True])
+    assert losses[True][-1] != losses[True][0]
