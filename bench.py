@@ -386,7 +386,13 @@ def run_ours(args):
         }
         print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # graph-captured NCCL work keeps references into the communicator: tearing the process group down
+        # explicitly can block forever, so synchronise, rendezvous once more and leave without destructors.
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
