@@ -148,7 +148,8 @@ def test_train_step_gradients(golden_dir, freeze, dtype, state):
             med_n, med_o = float(np.median(list(noise.values()))), float(np.median(list(gerr.values())))
             print("  oracle-on-GPU vs oracle-on-CPU median grad rel err: %.2e (ours %.2e)" % (med_n, med_o))
             bound = {k: max(5e-2, 6.0 * noise[k], 6.0 * med_n) for k in gerr}
-            assert med_o <= max(5e-3, 2.5 * med_n), (med_o, med_n)
+            # north-star gradient tolerance (1e-2) or the measured oracle-vs-oracle noise, whichever is larger
+            assert med_o <= max(1e-2, 2.5 * med_n), (med_o, med_n)
     else:
         ag = _autocast_grads(ocfg, sd, inputs, labels)
         aerr = {k: (_rel(ag[k], rgrads[k]) if float(rgrads[k].norm()) > 0 else float(ag[k].norm())) for k in gerr}
