@@ -10,7 +10,11 @@ objs=()
 pids=()
 for f in elementwise elementwise_bf16 conv_simt logmel tapgemm_sm100; do
   src="$HERE/csrc/$f.cu"; obj="$HERE/build/$f.o"
-  if [[ ! -f "$obj" || "$src" -nt "$obj" || "$HERE/csrc/common.cuh" -nt "$obj" || "$HERE/../include/asf_b200.h" -nt "$obj" ]]; then
+  stale=0
+  for dep in "$src" "$HERE"/csrc/*.cuh "$HERE/../include/asf_b200.h"; do
+    [[ ! -f "$obj" || "$dep" -nt "$obj" ]] && stale=1
+  done
+  if [[ $stale == 1 ]]; then
     "$NVCC" "${FLAGS[@]}" ${ASF_PTXAS_V:+-Xptxas -v} -c "$src" -o "$obj" &
     pids+=($!)
   fi

@@ -1,0 +1,365 @@
+// tap-GEMM forward / dgrad, second generation (included by tapgemm_sm100.cu inside namespace asf).
+//
+// Same mainloop contract as tapgemm_fwd_kernel (TMA -> smem ring -> tcgen05.mma -> TMEM, persistent CTAs), with
+//   * a tight single-thread MMA issue loop (no integer division, four unrolled K=16 steps per 64-channel chunk),
+//   * an all-asynchronous epilogue: residual / accumulate / mask operands arrive by TMA into swizzled smem slabs
+//     (prefetched one slab ahead), results leave through smem + TMA store; no thread ever waits on a global load.
+//     OOB rows / channels of a ragged tile are clipped by the TMA store, so the math runs unpredicated,
+//   * training-BN statistics summed column-wise from the bf16 slab that is being stored (what BN will read).
+//
+// Slab = 128 rows x 32 channels bf16 = 8 KB, CU_TENSOR_MAP_SWIZZLE_64B: 16-byte chunk c of row r lives at
+//   r*64 + ((c ^ ((r >> 1) & 3)) << 4).
+#pragma once
+
+constexpr int EPI_SLAB_COLS = 32;
+constexpr int EPI_SLAB_BYTES = TG_BLOCK_M * EPI_SLAB_COLS * 2;  // 8192
+constexpr int EPI_SHIFT_FLOATS = 256;
+
+__device__ __forceinline__ uint32_t slab_off(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
+
+__device__ __forceinline__ void bf16x8_to_f32(const uint4& q, float* f) {
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+
+// One slab of one row: raw fp32 accumulators -> epilogue math -> bf16 into the out slab.
+template <bool SHIFT, int NADD, bool MASK, bool RELU>
+__device__ __forceinline__ void epi_slab_math(const uint32_t* raw, const float* s_shift, const uint8_t* op0,
+                                              const uint8_t* op1, uint8_t* out, int r, bool zero) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float w[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = __uint_as_float(raw[8 * c + j]);
+    const uint32_t off = slab_off(r, c);
+    if (SHIFT) {
+      const float4 s0 = *(const float4*)(s_shift + 8 * c), s1 = *(const float4*)(s_shift + 8 * c + 4);
+      w[0] += s0.x; w[1] += s0.y; w[2] += s0.z; w[3] += s0.w; w[4] += s1.x; w[5] += s1.y; w[6] += s1.z; w[7] += s1.w;
+    }
+    if (NADD) {
+      float a[8];
+      bf16x8_to_f32(*(const uint4*)(op0 + off), a);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] += a[j];
+    }
+    if (RELU) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = fmaxf(w[j], 0.f);
+    }
+    if (MASK) {
+      float m[8];
+      bf16x8_to_f32(*(const uint4*)((NADD ? op1 : op0) + off), m);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = (m[j] > 0.f) ? w[j] : 0.f;
+    }
+    if (zero) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = 0.f;
+    }
+    uint4 o;
+    __nv_bfloat162* ob = (__nv_bfloat162*)&o;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(w[2 * j], w[2 * j + 1]);
+    *(uint4*)(out + off) = o;
+  }
+}
+
+// Column sums / sums of squares of one finished bf16 slab (rows outside the tensor were written as zeros).
+// t = thread index inside the 128-thread epilogue group.  Thread t owns channel pair (2w, 2w+1), w = t & 15, of rows
+// (t >> 4) + 8 i: a warp reads two adjacent rows per step = one conflict-free 128-byte wavefront.
+__device__ __forceinline__ void red_shared_f32(float* p, float v) {
+  asm volatile("red.shared::cta.add.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+template <bool SMEM>
+__device__ __forceinline__ void epi_slab_stats(const uint8_t* slab, int t, float* gsum, float* gsq, int col0, int N) {
+  // gsum / gsq: global statistics, or the CTA's shared accumulators when one N tile covers all channels
+  const int w = t & 15, rg = t >> 4;
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int r = rg + 8 * i;
+    const uint32_t v = *(const uint32_t*)(slab + r * 64 + (((w >> 2) ^ ((r >> 1) & 3)) << 4) + ((w & 3) << 2));
+    const float a = __uint_as_float(v << 16), b = __uint_as_float(v & 0xffff0000u);
+    s0 += a; q0 = fmaf(a, a, q0);
+    s1 += b; q1 = fmaf(b, b, q1);
+  }
+  s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+  s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+  q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
+  q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+  if ((t & 16) == 0) {
+    const int n = col0 + 2 * w;
+    if (SMEM) {
+      if (n < N) {
+        red_shared_f32(gsum + n, s0);
+        red_shared_f32(gsq + n, q0);
+      }
+      if (n + 1 < N) {
+        red_shared_f32(gsum + n + 1, s1);
+        red_shared_f32(gsq + n + 1, q1);
+      }
+    } else {
+      if (n < N) {
+        atomicAdd(gsum + n, s0);
+        atomicAdd(gsq + n, q0);
+      }
+      if (n + 1 < N) {
+        atomicAdd(gsum + n + 1, s1);
+        atomicAdd(gsq + n + 1, q1);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ the kernel
+// warp 0: TMA producer (mainloop operands), warp 1: MMA issuer + TMEM owner,
+// warps 2..5 / 6..9: two epilogue groups (group g drains TMEM buffer g, i.e. every other tile of this CTA).
+template <bool STATS>
+__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __grid_constant__ TgParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;  // 1024-byte aligned (128B-swizzle atoms); checked below
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  const int b_bytes = p.block_n * 128;
+  const int stage_bytes = TG_A_BYTES + b_bytes;
+  const int n_ops = p.n_add + p.has_mask;
+  uint8_t* epi_base = smem + p.epi_smem_off;
+  const int group_bytes = (2 + 2 * n_ops) * EPI_SLAB_BYTES;
+  float* shift_base = (float*)(epi_base + 2 * group_bytes);
+  TgShared* sh = (TgShared*)(shift_base + 2 * EPI_SHIFT_FLOATS);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.m_tiles_total * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_a);
+    tma_prefetch_desc(&p.tm_b);
+    tma_prefetch_desc(&p.tm_out);
+    if (n_ops > 0) tma_prefetch_desc(&p.tm_op[0]);
+    if (n_ops > 1) tma_prefetch_desc(&p.tm_op[1]);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&sh->full[s], 1);
+      mbar_init(&sh->empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sh->tmem_full[i], 1);
+      mbar_init(&sh->tmem_empty[i], 4);
+      mbar_init(&sh->op_full[i][0], 1);
+      mbar_init(&sh->op_full[i][1], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sh->tmem_base, 512);
+  // Training-BN statistics: when one N tile covers every channel the CTA sums into shared memory (the two shift
+  // areas, unused in this mode, = [2][256] floats) and touches each global counter once, at the end; thousands of
+  // same-address L2 atomics per launch serialise at ~7 ns each otherwise.
+  const bool stats_smem = STATS && p.n_tiles == 1;
+  if (stats_smem && threadIdx.x >= 64)
+    for (int i = (int)threadIdx.x - 64; i < 2 * EPI_SHIFT_FLOATS; i += TG_THREADS - 64) shift_base[i] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh->tmem_base;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+        int st[3];
+        tile_coords(p, m_tile, st);
+        int b1 = 0, b2 = 0, b3 = 0, b4 = 0;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int d = p.m_to_a[j];
+          b1 = d == 1 ? st[j] : b1;
+          b2 = d == 2 ? st[j] : b2;
+          b3 = d == 3 ? st[j] : b3;
+          b4 = d == 4 ? st[j] : b4;
+        }
+        const int nrow = n_tile * p.block_n;
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int c1 = b1 + p.a_off[tap][0], c2 = b2 + p.a_off[tap][1], c3 = b3 + p.a_off[tap][2],
+                    c4 = b4 + p.a_off[tap][3];
+          const int wt = p.b_tap[tap];
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            mbar_wait(&sh->empty[s], ph ^ 1, 1);
+            uint8_t* sa = smem + (size_t)s * stage_bytes;
+            mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
+            tma_load(&p.tm_a, &sh->full[s], sa, p.rank_a, kc * TG_KC, c1, c2, c3, c4);
+            tma_load(&p.tm_b, &sh->full[s], sa + TG_A_BYTES, 3, kc * TG_KC, wt, nrow, 0, 0);
+            if (++s == p.stages) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(TG_BLOCK_M, p.block_n, 0, 0);
+      const int kiters = p.ntaps * p.kchunks;
+      const int ksteps_last = min(TG_KC / 16, (p.K - (p.kchunks - 1) * TG_KC + 15) >> 4);
+      const bool full4 = ksteps_last == 4;
+      const uint32_t smem0 = smem_u32(smem);
+      const uint64_t adesc0 = make_sdesc(smem0, 16, 1024);
+      const uint64_t bdesc0 = make_sdesc(smem0 + TG_A_BYTES, 16, 1024);
+      const uint64_t dstage = (uint64_t)(stage_bytes >> 4);
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&sh->tmem_empty[buf], ((it >> 1) & 1) ^ 1, 2);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 256);
+        uint32_t acc = 0;
+        int kc = 0;
+        for (int ki = 0; ki < kiters; ++ki) {
+          mbar_wait(&sh->full[s], ph, 3);
+          tc_fence_after();
+          const uint64_t adesc = adesc0 + dstage * (uint64_t)s, bdesc = bdesc0 + dstage * (uint64_t)s;
+          if (full4 || kc + 1 < p.kchunks) {
+            umma_bf16(d_tmem, adesc, bdesc, idesc, acc);
+            umma_bf16(d_tmem, adesc + 2, bdesc + 2, idesc, 1);
+            umma_bf16(d_tmem, adesc + 4, bdesc + 4, idesc, 1);
+            umma_bf16(d_tmem, adesc + 6, bdesc + 6, idesc, 1);
+          } else {  // short last chunk (K % 64 != 0): skip the zero-filled K tail
+            for (int k = 0; k < ksteps_last; ++k)
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, acc | (uint32_t)k);
+          }
+          acc = 1;
+          umma_commit(&sh->empty[s]);
+          if (++kc == p.kchunks) kc = 0;
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&sh->tmem_full[buf]);
+      }
+    }
+  } else {
+    // ===== epilogue groups =====
+    const int group = (warp - 2) >> 2;
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int r = quarter * 32 + lane;            // row of the tile = TMEM lane
+    const int t = (int)threadIdx.x - 64 - group * 128;  // 0..127 inside the group
+    const bool leader = t == 0;
+    const int bar_id = 1 + group;
+    uint8_t* gbase = epi_base + group * group_bytes;
+    uint8_t* out_buf = gbase;                             // [2] slabs
+    uint8_t* op_buf = gbase + 2 * EPI_SLAB_BYTES;         // [n_ops][2] slabs
+    float* s_shift = shift_base + group * EPI_SHIFT_FLOATS;
+    const float* g_shift = p.epi.shift;
+    const int variant = (g_shift ? 8 : 0) | (p.n_add ? 4 : 0) | (p.has_mask ? 2 : 0) | (p.epi.relu ? 1 : 0);
+    const int r1 = r & ((1 << p.m_log2[0]) - 1);
+    const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
+    const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
+    uint32_t gs = 0;  // slabs processed by this group so far (selects buffers and mbarrier parities)
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      if ((it & 1) != group) continue;
+      const int buf = group;
+      const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+      int st[3];
+      tile_coords(p, m_tile, st);
+      int o1 = 0, o2 = 0, o3 = 0;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int d = p.o_dim[j];
+        o1 = d == 1 ? st[j] : o1;
+        o2 = d == 2 ? st[j] : o2;
+        o3 = d == 3 ? st[j] : o3;
+      }
+      const bool valid = (st[0] + r1 < p.m_ext[0]) && (st[1] + r2 < p.m_ext[1]) && (st[2] + r3 < p.m_ext[2]);
+      const int n0 = n_tile * p.block_n;
+      const int nslab = (min(p.block_n, p.N - n0) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
+      if (g_shift) {
+        for (int i = t; i < p.block_n; i += 128) s_shift[i] = (n0 + i < p.N) ? g_shift[n0 + i] : 0.f;
+      }
+      if (leader && n_ops > 0) {  // operands of the first slab: in flight while the MMAs of this tile still run
+        uint64_t* bar = &sh->op_full[group][gs & 1];
+        mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
+        for (int o = 0; o < n_ops; ++o)
+          tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + (gs & 1)) * EPI_SLAB_BYTES, p.rank_o, n0, o1, o2, o3, 0);
+      }
+      named_bar(bar_id, 128);  // s_shift visible to the group
+      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
+      tc_fence_after();
+      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
+      for (int s = 0; s < nslab; ++s, ++gs) {
+        const int b = gs & 1;
+        uint32_t raw[32];
+        tmem_ld32_issue(taddr0 + (uint32_t)(s * 32), raw);
+        if (leader) {
+          if (n_ops > 0 && s + 1 < nslab) {
+            uint64_t* bar = &sh->op_full[group][b ^ 1];
+            mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
+            for (int o = 0; o < n_ops; ++o)
+              tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + (b ^ 1)) * EPI_SLAB_BYTES, p.rank_o, n0 + (s + 1) * 32, o1,
+                       o2, o3, 0);
+          }
+          bulk_wait_read<1>();  // the store that last read out_buf[b] (two slabs ago) has drained it
+        }
+        tmem_ld_wait();
+        if (s == nslab - 1) {  // accumulators are in registers: hand the TMEM buffer back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
+        }
+        if (n_ops > 0) mbar_wait(&sh->op_full[group][b], (gs >> 1) & 1, 5);
+        named_bar(bar_id, 128);  // out_buf[b] is free for everybody
+        uint8_t* ob = out_buf + b * EPI_SLAB_BYTES;
+        const uint8_t* op0 = op_buf + b * EPI_SLAB_BYTES;
+        const uint8_t* op1 = op_buf + (2 + b) * EPI_SLAB_BYTES;
+        const float* ss = s_shift + s * 32;
+        const bool zero = STATS && !valid;
+        switch (variant) {
+          case 0: epi_slab_math<false, 0, false, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 1: epi_slab_math<false, 0, false, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 2: epi_slab_math<false, 0, true, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 3: epi_slab_math<false, 0, true, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 4: epi_slab_math<false, 1, false, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 5: epi_slab_math<false, 1, false, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 6: epi_slab_math<false, 1, true, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 7: epi_slab_math<false, 1, true, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 8: epi_slab_math<true, 0, false, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 9: epi_slab_math<true, 0, false, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 10: epi_slab_math<true, 0, true, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 11: epi_slab_math<true, 0, true, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 12: epi_slab_math<true, 1, false, false>(raw, ss, op0, op1, ob, r, zero); break;
+          case 13: epi_slab_math<true, 1, false, true>(raw, ss, op0, op1, ob, r, zero); break;
+          case 14: epi_slab_math<true, 1, true, false>(raw, ss, op0, op1, ob, r, zero); break;
+          default: epi_slab_math<true, 1, true, true>(raw, ss, op0, op1, ob, r, zero); break;
+        }
+        fence_proxy_async();
+        named_bar(bar_id, 128);  // slab complete
+        if (leader) {
+          tma_store(&p.tm_out, ob, p.rank_o, n0 + s * 32, o1, o2, o3);
+          bulk_commit();
+        }
+        if (STATS) {
+          if (stats_smem)
+            epi_slab_stats<true>(ob, t, shift_base, shift_base + EPI_SHIFT_FLOATS, s * 32, p.block_n);
+          else
+            epi_slab_stats<false>(ob, t, p.epi.stats, p.epi.stats + p.epi.stats_stride, n0 + s * 32, p.N);
+        }
+        __syncwarp();
+      }
+    }
+    if (leader) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+  if (stats_smem && threadIdx.x >= 64) {
+    for (int i = (int)threadIdx.x - 64; i < p.N; i += TG_THREADS - 64) {
+      atomicAdd(p.epi.stats + i, shift_base[i]);
+      atomicAdd(p.epi.stats + p.epi.stats_stride + i, shift_base[EPI_SHIFT_FLOATS + i]);
+    }
+  }
+}

@@ -88,6 +88,38 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)tm) : "memory");
 }
 
+// TMA store of one smem box to global (bulk async-group completion); OOB parts of the box are clipped
+__device__ __forceinline__ void tma_store(const CUtensorMap* tm, const void* src, int rank, int c0, int c1, int c2,
+                                          int c3) {
+  const uint32_t s = smem_u32(src);
+  const uint64_t t = (uint64_t)tm;
+  switch (rank) {
+    case 2:
+      asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(t), "r"(s),
+                   "r"(c0), "r"(c1) : "memory");
+      break;
+    case 3:
+      asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(t), "r"(s),
+                   "r"(c0), "r"(c1), "r"(c2) : "memory");
+      break;
+    default:
+      asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(t),
+                   "r"(s), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+      break;
+  }
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// generic-proxy smem writes -> visible to the async proxy (TMA store source)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void named_bar(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
                "r"(ncols) : "memory");
@@ -164,6 +196,13 @@ struct TgParams {
   long long ld_out;
   long long o_stride[3];
   asf_epilogue_t epi;
+  // mode 0, TMA epilogue: output / operand tensor maps over the output M-space, 32-channel boxes, 64B swizzle
+  CUtensorMap tm_out;
+  CUtensorMap tm_op[2];  // op 0: additive (residual, or the output itself when accumulating) else mask; op 1: mask
+  int rank_o;            // rank of tm_out / tm_op (1 + mapped M dims)
+  int o_dim[3];          // M-dim j -> coordinate slot (1..3) of the output maps, 0 = unmapped
+  int n_add, has_mask;   // operands: n_add in {0,1} additive, has_mask in {0,1}
+  int epi_smem_off;      // byte offset of the epilogue staging region inside dynamic smem
   // mode 1
   float* dwp;
   int ntaps_w, ksplit, c_tiles, r_tiles;
@@ -174,6 +213,7 @@ struct TgShared {
   uint64_t empty[TG_MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t op_full[2][2];  // [epilogue group][operand buffer]
   uint32_t tmem_base;
 };
 
@@ -365,7 +405,7 @@ __device__ __forceinline__ void epi_stats16(const TgParams& p, const float* v, i
 
 // ------------------------------------------------------------------------------------------------ mode 0
 __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid_constant__ TgParams p) {
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int b_bytes = p.block_n * 128;
   const int stage_bytes = TG_A_BYTES + b_bytes;
@@ -506,12 +546,14 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid
   }
 }
 
+#include "tapgemm_fwd_tma.cuh"
+
 // ------------------------------------------------------------------------------------------------ mode 1 (wgrad)
 constexpr int WG_STAGE_BYTES = 4 * 16384;  // Y: 2 boxes [128 rows][64 ch], X: 2 boxes [128 rows][64 ch]
 constexpr int WG_STAGES = 3;
 
 __global__ void __launch_bounds__(WG_THREADS, 1) tapgemm_wgrad_kernel(const __grid_constant__ TgParams p) {
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   TgShared* sh = (TgShared*)(smem + (size_t)WG_STAGES * WG_STAGE_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -637,7 +679,7 @@ static PFN_encodeTiled get_encode() {
 
 // bf16 tensor map: dim0 = channels (extent c_ext, box 64 = one 128B swizzle row), dims 1.. = (ext, stride) pairs
 static int encode_map(CUtensorMap* tm, const void* base, int c_ext, int nd, const int64_t* ext, const int64_t* stride,
-                      const int* box) {
+                      const int* box, int inner_box = TG_KC, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
@@ -646,7 +688,7 @@ static int encode_map(CUtensorMap* tm, const void* base, int c_ext, int nd, cons
   cuuint64_t gdim[5], gstr[4];
   cuuint32_t bdim[5], estr[5];
   gdim[0] = (cuuint64_t)c_ext;
-  bdim[0] = TG_KC;
+  bdim[0] = (cuuint32_t)inner_box;
   estr[0] = 1;
   for (int i = 0; i < nd; ++i) {
     gdim[i + 1] = (cuuint64_t)ext[i];
@@ -663,7 +705,7 @@ static int encode_map(CUtensorMap* tm, const void* base, int c_ext, int nd, cons
     return ASF_E_BADARG;
   }
   CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)(nd + 1), const_cast<void*>(base), gdim, gstr, bdim,
-                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, c_ext %d)", (int)r, nd + 1, c_ext);
@@ -772,13 +814,38 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
 
   if (mode == 0) {
     ASF_CHECK_ARG(q->bw && q->out && q->ld_out >= q->N, "asf_tapgemm: mode 0 needs bw/out");
+    ASF_CHECK_ARG(q->out_dtype == ASF_BF16 || q->out_dtype == ASF_F32, "asf_tapgemm: bad out dtype");
+    p.out_bf16 = q->out_dtype == ASF_BF16;
+    bool vec = p.out_bf16 && (q->ld_out % 8 == 0) && (((uintptr_t)q->out & 15) == 0);
+    if (q->epi.res) vec = vec && (q->epi.ld_res % 8 == 0) && (((uintptr_t)q->epi.res & 15) == 0);
+    if (q->epi.mask) vec = vec && (q->epi.ld_mask % 8 == 0) && (((uintptr_t)q->epi.mask & 15) == 0);
+    p.vec_ok = vec ? 1 : 0;
+    // the TMA epilogue handles every launch of the network; the direct-store kernel stays for fp32 outputs,
+    // unaligned tensors, an explicit per-channel scale, or residual + accumulate in one launch
+    static int force_direct = -1;
+    if (force_direct < 0) {
+      const char* e = getenv("ASF_TG_DIRECT");
+      force_direct = (e && e[0] == '1') ? 1 : 0;
+    }
+    const bool use_tma = vec && !q->epi.scale && !(q->epi.res && q->epi.accumulate) && !force_direct;
+    const int n_add = (q->epi.res || q->epi.accumulate) ? 1 : 0, has_mask = q->epi.mask ? 1 : 0;
+    const int group_bytes = (2 + 2 * (n_add + has_mask)) * EPI_SLAB_BYTES;
+    const int tma_fixed = 2 * group_bytes + 2 * EPI_SHIFT_FLOATS * 4 + (int)sizeof(TgShared);
+    const int smem_cap = 227 * 1024;
     int bn = q->block_n;
     if (bn <= 0) {
       int n16 = (int)cdiv(q->N, 16) * 16;
       bn = n16 <= 256 ? n16 : 256;
       if (n16 > 256 && n16 % 256 != 0 && n16 % 128 == 0) bn = 128;
-      // keep at least ~1 wave of tiles on the chip when M is small
-      while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < num_sms() && bn % 32 == 0) bn /= 2;
+      if (use_tma) {
+        // N = 256 per MMA keeps the single issuing thread ahead of the tensor pipe; halve only when that at least
+        // doubles the number of busy SMs, or when the operand slabs leave fewer than 3 ring stages
+        while (bn > 64 && bn % 32 == 0 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) * 2 <= num_sms()) bn /= 2;
+        while (bn > 64 && bn % 32 == 0 && (smem_cap - tma_fixed) / (TG_A_BYTES + bn * 128) < 3) bn /= 2;
+      } else {
+        // keep at least ~1 wave of tiles on the chip when M is small
+        while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < num_sms() && bn % 32 == 0) bn /= 2;
+      }
     }
     ASF_CHECK_ARG(bn >= 16 && bn <= 256 && bn % 16 == 0, "asf_tapgemm: block_n %d must be a multiple of 16 in [16,256]", bn);
     p.block_n = bn;
@@ -795,24 +862,85 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: not enough shared memory for 2 stages");
     p.stages = stages;
     p.out = q->out;
-    p.out_bf16 = q->out_dtype == ASF_BF16;
-    ASF_CHECK_ARG(q->out_dtype == ASF_BF16 || q->out_dtype == ASF_F32, "asf_tapgemm: bad out dtype");
     p.ld_out = q->ld_out;
     for (int j = 0; j < 3; ++j) p.o_stride[j] = q->o_stride[j];
     p.epi = q->epi;
-    bool vec = p.out_bf16 && (q->ld_out % 8 == 0) && (((uintptr_t)q->out & 15) == 0);
-    if (q->epi.res) vec = vec && (q->epi.ld_res % 8 == 0) && (((uintptr_t)q->epi.res & 15) == 0);
-    if (q->epi.mask) vec = vec && (q->epi.ld_mask % 8 == 0) && (((uintptr_t)q->epi.mask & 15) == 0);
-    p.vec_ok = vec ? 1 : 0;
+    int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
+    int grid = (int)(total < num_sms() ? total : num_sms());
+    const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
+    if (use_tma) {
+      stages = (smem_cap - tma_fixed) / stage_bytes;
+      if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
+      ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: not enough shared memory for 2 stages");
+      p.stages = stages;
+      p.n_add = n_add;
+      p.has_mask = has_mask;
+      p.epi_smem_off = stages * stage_bytes;
+      // output-space tensor maps: dim 0 = channels, then every M dim that moves the output row
+      int64_t oext[3], ostr_rows[3];
+      int obox[3], nd_o = 0;
+      for (int j = 0; j < 3; ++j) {
+        p.o_dim[j] = 0;
+        if (q->m_ext[j] > 1 || q->m_box[j] > 1) {
+          ASF_CHECK_ARG(q->o_stride[j] > 0, "asf_tapgemm: M dim %d has extent > 1 but no output stride", j);
+          oext[nd_o] = q->m_ext[j];
+          ostr_rows[nd_o] = q->o_stride[j];
+          obox[nd_o] = q->m_box[j];
+          p.o_dim[j] = ++nd_o;
+        }
+      }
+      ASF_CHECK_ARG(nd_o >= 1, "asf_tapgemm: empty output space");
+      p.rank_o = nd_o + 1;
+      int64_t ostr[3];
+      for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->ld_out;
+      rc = encode_map(&p.tm_out, q->out, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS, CU_TENSOR_MAP_SWIZZLE_64B);
+      if (rc) return rc;
+      int no = 0;
+      if (n_add) {
+        if (q->epi.accumulate) {
+          p.tm_op[no++] = p.tm_out;
+        } else {
+          for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->epi.ld_res;
+          rc = encode_map(&p.tm_op[no++], q->epi.res, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS,
+                          CU_TENSOR_MAP_SWIZZLE_64B);
+          if (rc) return rc;
+        }
+      }
+      if (has_mask) {
+        for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->epi.ld_mask;
+        rc = encode_map(&p.tm_op[no++], q->epi.mask, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS,
+                        CU_TENSOR_MAP_SWIZZLE_64B);
+        if (rc) return rc;
+      }
+      const size_t smem_t = (size_t)stages * stage_bytes + tma_fixed;
+      static size_t smem_set_t[2] = {0, 0};
+      const int si = q->epi.stats ? 1 : 0;
+      if (smem_t > smem_set_t[si]) {
+        if (si)
+          ASF_CUDA(cudaFuncSetAttribute(tapgemm_fwd_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+        else
+          ASF_CUDA(cudaFuncSetAttribute(tapgemm_fwd_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+        smem_set_t[si] = smem_cap;
+      }
+      ProfRec* pr = prof_begin(st, 0, flops);
+      if (pr) {
+        pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
+        pr->block_n = bn; pr->grid = grid;
+      }
+      if (si)
+        tapgemm_fwd_tma_kernel<true><<<grid, TG_THREADS, smem_t, st>>>(p);
+      else
+        tapgemm_fwd_tma_kernel<false><<<grid, TG_THREADS, smem_t, st>>>(p);
+      prof_end(pr, st);
+      ASF_LAUNCH_CHECK();
+      return debug_sync(st);
+    }
     const size_t smem = (size_t)stages * stage_bytes + sizeof(TgShared) + 1024;
     static size_t smem_set = 0;
     if (smem > smem_set) {
       ASF_CUDA(cudaFuncSetAttribute(tapgemm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set = smem;
     }
-    int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
-    int grid = (int)(total < num_sms() ? total : num_sms());
-    const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
     ProfRec* pr = prof_begin(st, 0, flops);
     if (pr) {
       pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
