@@ -110,6 +110,7 @@ SIGNATURES = {
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "asf_bn_fold": [_P, _P, _P, _P, _F, _I, _P, _P, _P],
+    "asf_bn_train_fwd": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P],
     "asf_bn_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _I, _P],
     "asf_bn_bwd_reduce": [_P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P],
     "asf_bn_bwd_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _D, _P, _P, _I, _P],

@@ -648,14 +648,14 @@ class Engine:
         rows = raw.rows
         mom = bn.momentum if bn.momentum is not None else 0.1
         track = bn.track_running_stats
-        L.call("asf_bn_finalize", L.ptr(u.stats), u.Cout, C.c_double(rows), L.ptr(bn.weight), L.ptr(bn.bias),
-               C.c_float(bn.eps), C.c_float(mom), L.ptr(bn.running_mean) if track else None,
-               L.ptr(bn.running_var) if track else None, L.ptr(bn.num_batches_tracked) if track else None,
-               L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.mean), L.ptr(u.invstd), st)
-        if out is not None:
-            L.call("asf_bn_apply", C.c_void_p(raw.ptr), raw.ld, C.c_void_p(res.ptr) if res is not None else None,
-                   res.ld if res is not None else 0, C.c_void_p(out.ptr), out.ld, out.code, rows, u.Cout,
-                   L.ptr(u.scale), L.ptr(u.shift), int(relu), st)
+        # statistics -> scale / shift / saved mean, invstd / running stats, and the normalise(+res)(+ReLU) pass: one launch
+        L.call("asf_bn_train_fwd", C.c_void_p(raw.ptr), raw.ld, C.c_void_p(res.ptr) if res is not None else None,
+               res.ld if res is not None else 0, C.c_void_p(out.ptr) if out is not None else None,
+               out.ld if out is not None else 0, raw.code, rows, u.Cout, L.ptr(u.stats), C.c_double(rows),
+               L.ptr(bn.weight), L.ptr(bn.bias), C.c_float(bn.eps), C.c_float(mom),
+               L.ptr(bn.running_mean) if track else None, L.ptr(bn.running_var) if track else None,
+               L.ptr(bn.num_batches_tracked) if track else None, L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.mean),
+               L.ptr(u.invstd), int(relu), st)
 
     def _unit_forward(self, u, training, prepared=False):
         st = L.stream_ptr()

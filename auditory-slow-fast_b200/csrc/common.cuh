@@ -61,6 +61,10 @@ static inline bool ld8(int64_t ld) { return (ld & 7) == 0; }
 // elementwise_bf16.cu
 int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
                 int C, const float* scale, const float* shift, int relu, cudaStream_t st);
+int bn_train_fwd_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
+                    int C, const float* stats, double count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked, float* scale,
+                    float* shift, float* save_mean, float* save_invstd, int relu, cudaStream_t st);
 int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
                     int C, const float* gamma, const float* mean, const float* invstd, const float* red,
                     float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st);

@@ -619,6 +619,22 @@ int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, v
   });
 }
 
+int asf_bn_train_fwd(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
+                     int64_t rows, int C, const float* stats, double count, const float* gamma, const float* beta,
+                     float eps, float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                     float* scale, float* shift, float* save_mean, float* save_invstd, int relu, void* stream) {
+  ASF_CHECK_ARG(x && stats && scale && shift && rows > 0 && C > 0 && count > 0, "asf_bn_train_fwd: bad arguments");
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_x) && al16(x) && (!y || (ld8(ld_y) && al16(y))) &&
+      (!res || (ld8(ld_res) && al16(res))))
+    return bn_train_fwd_v8((const bf16*)x, ld_x, (const bf16*)res, ld_res, (bf16*)y, ld_y, rows, C, stats, count, gamma,
+                           beta, eps, momentum, running_mean, running_var, num_batches_tracked, scale, shift, save_mean,
+                           save_invstd, relu, (cudaStream_t)stream);
+  int rc = asf_bn_finalize(stats, C, count, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked,
+                           scale, shift, save_mean, save_invstd, stream);
+  if (rc || !y) return rc;
+  return asf_bn_apply(x, ld_x, res, ld_res, y, ld_y, dtype, rows, C, scale, shift, relu, stream);
+}
+
 int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, float* red, void* stream) {
   ASF_CHECK_ARG(dz && x && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_reduce: bad arguments");

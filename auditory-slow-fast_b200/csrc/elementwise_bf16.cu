@@ -45,94 +45,232 @@ static inline unsigned vgrid(int64_t nvec) {
   return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// ------------------------------------------------------------------------------------------- column streaming
+// The training-BN passes are "column-owned": a block is CVB vector-columns (8 channels each) x RP row lanes; a thread
+// keeps its 8 channels' parameters in registers and streams rows r0 + rl, + RP, ... four at a time (four independent
+// 16-byte loads per tensor in flight).  Consecutive threads touch consecutive 16-byte vectors, rows are contiguous.
+struct ColGeom {
+  int CVB, RP, cblocks;
+  int64_t rows_per_block;
+  dim3 grid;
+};
+static ColGeom col_geom(int64_t rows, int C, int blocks_per_sm) {
+  ColGeom g;
+  const int CV = C / 8;
+  g.CVB = CV < 256 ? CV : 256;
+  g.cblocks = (int)cdiv(CV, g.CVB);
+  g.RP = 256 / g.CVB;
+  int64_t target = 148 * blocks_per_sm / g.cblocks;
+  if (target < 1) target = 1;
+  int64_t rpb = cdiv(rows, target);
+  const int64_t quantum = (int64_t)g.RP * 4;
+  rpb = cdiv(rpb, quantum) * quantum;
+  g.rows_per_block = rpb;
+  g.grid = dim3((unsigned)cdiv(rows, rpb), (unsigned)g.cblocks);
+  return g;
+}
+
 // ------------------------------------------------------------------------------------------- BN apply (train)
+// FINALIZE: scale / shift are derived here from the conv epilogue's sums (stats[c], stats[C + c]); the blocks of the
+// first row range also publish scale / shift / mean / invstd and update the running statistics (what bn_finalize did
+// as a separate launch per layer).
+template <bool FINALIZE>
 __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict__ x, int64_t ld_x,
                                                           const bf16* __restrict__ res, int64_t ld_res,
-                                                          bf16* __restrict__ y, int64_t ld_y, int64_t nvec, int CV,
-                                                          const float* __restrict__ scale,
-                                                          const float* __restrict__ shift, int relu) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / CV;
-    const int c = (int)(i - r * CV) * 8;
-    F8 a = unpack8(*(const uint4*)(x + r * ld_x + c));
-    const F8 sc = ldf8(scale + c), sh = ldf8(shift + c);
+                                                          bf16* __restrict__ y, int64_t ld_y, int64_t rows, int C,
+                                                          int CVB, int64_t rows_per_block, float* scale, float* shift,
+                                                          int relu, const float* __restrict__ stats, double count,
+                                                          const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float eps, float momentum,
+                                                          float* running_mean, float* running_var,
+                                                          long long* num_batches_tracked, float* save_mean,
+                                                          float* save_invstd) {
+  const int RP = 256 / CVB;
+  const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
+  const int c = (blockIdx.y * CVB + cvl) * 8;
+  if (rl >= RP || c >= C) return;
+  F8 sc, sh;
+  if (FINALIZE) {
+    const bool publish = blockIdx.x == 0 && rl == 0;
+    if (publish && c == 0 && num_batches_tracked) *num_batches_tracked += 1;
+    const F8 s0 = ldf8(stats + c), s1 = ldf8(stats + C + c);
+    F8 ga, be;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a.v[j] = fmaf(a.v[j], sc.v[j], sh.v[j]);
-    if (res) {
-      const F8 q = unpack8(*(const uint4*)(res + r * ld_res + c));
-#pragma unroll
-      for (int j = 0; j < 8; ++j) a.v[j] += q.v[j];
+    for (int j = 0; j < 8; ++j) {
+      ga.v[j] = gamma ? gamma[c + j] : 1.f;
+      be.v[j] = beta ? beta[c + j] : 0.f;
     }
-    if (relu) {
+    if (!publish) {
+      // streaming blocks: fp32 (agrees with the published double-precision values to ~1e-6 relative, far below the
+      // bf16 rounding of y); the double divisions / square roots would otherwise dominate short row ranges
+      const float inv_n = (float)(1.0 / count);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) a.v[j] = fmaxf(a.v[j], 0.f);
+      for (int j = 0; j < 8; ++j) {
+        const float mean = s0.v[j] * inv_n;
+        const float var = fmaxf(fmaf(-mean, mean, s1.v[j] * inv_n), 0.f);
+        sc.v[j] = ga.v[j] * rsqrtf(var + eps);
+        sh.v[j] = fmaf(-mean, sc.v[j], be.v[j]);
+      }
     }
-    *(uint4*)(y + r * ld_y + c) = pack8(a);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (publish) {
+        const double mean = (double)s0.v[j] / count;
+        double var = (double)s1.v[j] / count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+        sc.v[j] = ga.v[j] * invstd;
+        sh.v[j] = be.v[j] - (float)mean * sc.v[j];
+        scale[c + j] = sc.v[j];
+        shift[c + j] = sh.v[j];
+        if (save_mean) save_mean[c + j] = (float)mean;
+        if (save_invstd) save_invstd[c + j] = invstd;
+        if (running_mean) {
+          const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+          running_mean[c + j] = (1.f - momentum) * running_mean[c + j] + momentum * (float)mean;
+          running_var[c + j] = (1.f - momentum) * running_var[c + j] + momentum * (float)unbiased;
+        }
+      }
+    }
+  } else {
+    sc = ldf8(scale + c);
+    sh = ldf8(shift + c);
+  }
+  if (!y) return;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  int64_t r1 = r0 + rows_per_block;
+  if (r1 > rows) r1 = rows;
+  for (int64_t r = r0 + rl; r < r1; r += (int64_t)RP * 4) {
+    uint4 xv[4], rv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t rr = r + (int64_t)k * RP;
+      if (rr < r1) {
+        xv[k] = *(const uint4*)(x + rr * ld_x + c);
+        if (res) rv[k] = *(const uint4*)(res + rr * ld_res + c);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t rr = r + (int64_t)k * RP;
+      if (rr < r1) {
+        F8 a = unpack8(xv[k]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a.v[j] = fmaf(a.v[j], sc.v[j], sh.v[j]);
+        if (res) {
+          const F8 q = unpack8(rv[k]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a.v[j] += q.v[j];
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a.v[j] = fmaxf(a.v[j], 0.f);
+        }
+        *(uint4*)(y + rr * ld_y + c) = pack8(a);
+      }
+    }
   }
 }
 
 int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
                 int C, const float* scale, const float* shift, int relu, cudaStream_t st) {
-  const int64_t nvec = rows * (C / 8);
-  bn_apply_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, nvec, C / 8, scale, shift, relu);
+  const ColGeom g = col_geom(rows, C, 4);
+  bn_apply_v8_kernel<false><<<g.grid, 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
+                                                   (float*)scale, (float*)shift, relu, nullptr, 1.0, nullptr, nullptr,
+                                                   0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr);
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+int bn_train_fwd_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
+                    int C, const float* stats, double count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked, float* scale,
+                    float* shift, float* save_mean, float* save_invstd, int relu, cudaStream_t st) {
+  const ColGeom g = col_geom(rows, C, 4);
+  bn_apply_v8_kernel<true><<<g.grid, 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
+                                                  scale, shift, relu, stats, count, gamma, beta, eps, momentum,
+                                                  running_mean, running_var, (long long*)num_batches_tracked, save_mean,
+                                                  save_invstd);
   ASF_LAUNCH_CHECK();
   return 0;
 }
 
 // ------------------------------------------------------------------------------------------- BN backward apply
-// dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count); block 0 also publishes dgamma / dbeta.
+// dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count); the first row range also publishes dgamma / dbeta.
 __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __restrict__ dz, int64_t ld_dz,
                                                               const bf16* __restrict__ x, int64_t ld_x,
-                                                              bf16* __restrict__ dx, int64_t ld_dx, int64_t nvec,
-                                                              int CV, const float* __restrict__ gamma,
+                                                              bf16* __restrict__ dx, int64_t ld_dx, int64_t rows, int C,
+                                                              int CVB, int64_t rows_per_block,
+                                                              const float* __restrict__ gamma,
                                                               const float* __restrict__ mean,
                                                               const float* __restrict__ invstd,
                                                               const float* __restrict__ red, float inv_count,
                                                               float* dgamma, float* dbeta, int accumulate) {
-  const int C = CV * 8;
-  if (blockIdx.x == 0 && (dgamma || dbeta)) {
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + red[c];
-      if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + red[C + c];
-    }
-  }
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / CV;
-    const int c = (int)(i - r * CV) * 8;
-    const F8 g = unpack8(*(const uint4*)(dz + r * ld_dz + c));
-    const F8 xv = unpack8(*(const uint4*)(x + r * ld_x + c));
-    const F8 mu = ldf8(mean + c), is = ldf8(invstd + c), r0 = ldf8(red + c), r1 = ldf8(red + C + c);
-    F8 ga;
-    if (gamma) {
-      ga = ldf8(gamma + c);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ga.v[j] = 1.f;
-    }
-    F8 o;
+  const int RP = 256 / CVB;
+  const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
+  const int c = (blockIdx.y * CVB + cvl) * 8;
+  if (rl >= RP || c >= C) return;
+  const F8 mu = ldf8(mean + c), is = ldf8(invstd + c), r0v = ldf8(red + c), r1v = ldf8(red + C + c);
+  if (blockIdx.x == 0 && rl == 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float xh = (xv.v[j] - mu.v[j]) * is.v[j];
-      o.v[j] = ga.v[j] * is.v[j] * (g.v[j] - r0.v[j] * inv_count - xh * r1.v[j] * inv_count);
+      if (dbeta) dbeta[c + j] = (accumulate ? dbeta[c + j] : 0.f) + r0v.v[j];
+      if (dgamma) dgamma[c + j] = (accumulate ? dgamma[c + j] : 0.f) + r1v.v[j];
     }
-    *(uint4*)(dx + r * ld_dx + c) = pack8(o);
+  }
+  // o = a * (g - k0 - (x - mu) * is * k1) = a * g - (a * k0 - a * is * k1 * mu) - (a * is * k1) * x
+  F8 ca, cb, cc;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float ga = gamma ? gamma[c + j] : 1.f;
+    ca.v[j] = ga * is.v[j];
+    cb.v[j] = r0v.v[j] * inv_count;
+    cc.v[j] = r1v.v[j] * inv_count;
+  }
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  int64_t r1 = r0 + rows_per_block;
+  if (r1 > rows) r1 = rows;
+  for (int64_t r = r0 + rl; r < r1; r += (int64_t)RP * 4) {
+    uint4 gv[4], xv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t rr = r + (int64_t)k * RP;
+      if (rr < r1) {
+        gv[k] = *(const uint4*)(dz + rr * ld_dz + c);
+        xv[k] = *(const uint4*)(x + rr * ld_x + c);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t rr = r + (int64_t)k * RP;
+      if (rr < r1) {
+        const F8 g = unpack8(gv[k]), xx = unpack8(xv[k]);
+        F8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (xx.v[j] - mu.v[j]) * is.v[j];
+          o.v[j] = ca.v[j] * (g.v[j] - cb.v[j] - xh * cc.v[j]);
+        }
+        *(uint4*)(dx + rr * ld_dx + c) = pack8(o);
+      }
+    }
   }
 }
 
 int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
                     int C, const float* gamma, const float* mean, const float* invstd, const float* red,
                     float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st) {
-  const int64_t nvec = rows * (C / 8);
-  bn_bwd_apply_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(dz, ld_dz, x, ld_x, dx, ld_dx, nvec, C / 8, gamma, mean, invstd,
-                                                      red, inv_count, dgamma, dbeta, accumulate);
+  const ColGeom g = col_geom(rows, C, 4);
+  bn_bwd_apply_v8_kernel<<<g.grid, 256, 0, st>>>(dz, ld_dz, x, ld_x, dx, ld_dx, rows, C, g.CVB, g.rows_per_block, gamma,
+                                                mean, invstd, red, inv_count, dgamma, dbeta, accumulate);
   ASF_LAUNCH_CHECK();
   return 0;
 }
 
 // ------------------------------------------------------------------------------------------- channel reductions
 // out[c] += sum_rows a ; out[C + c] += sum_rows (kBwd ? a * (x - mean) * invstd : a * a).
-// block = 256 threads = RP row-lanes x CVB vector-columns (CVB = min(CV, 256)); every thread streams its rows with
-// 16 fp32 accumulators, the block folds them with shared-memory atomics and flushes one global atomic per channel.
+// Row lanes that share a column inside a warp are folded with shuffles first (narrow tensors: C = 8 means 256 row
+// lanes per column), then the block folds through shared memory and issues one global atomic per channel.
 template <bool kBwd>
 __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __restrict__ a, int64_t ld_a,
                                                                 const bf16* __restrict__ x, int64_t ld_x,
@@ -148,10 +286,11 @@ __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __re
     s1[i] = 0.f;
   }
   __syncthreads();
-  if (rl < RP && c < C) {
-    float acc0[8], acc1[8];
+  float acc0[8], acc1[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc0[j] = acc1[j] = 0.f;
+  for (int j = 0; j < 8; ++j) acc0[j] = acc1[j] = 0.f;
+  const bool active = rl < RP && c < C;
+  if (active) {
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     int64_t r1 = r0 + rows_per_block;
     if (r1 > rows) r1 = rows;
@@ -160,23 +299,51 @@ __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __re
       mu = ldf8(mean + c);
       is = ldf8(invstd + c);
     }
-    for (int64_t r = r0 + rl; r < r1; r += RP) {
-      const F8 v = unpack8(*(const uint4*)(a + r * ld_a + c));
-      if (kBwd) {
-        const F8 xv = unpack8(*(const uint4*)(x + r * ld_x + c));
+    for (int64_t r = r0 + rl; r < r1; r += (int64_t)RP * 4) {
+      uint4 av[4], xv[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          acc0[j] += v.v[j];
-          acc1[j] = fmaf(v.v[j], (xv.v[j] - mu.v[j]) * is.v[j], acc1[j]);
+      for (int k = 0; k < 4; ++k) {
+        const int64_t rr = r + (int64_t)k * RP;
+        if (rr < r1) {
+          av[k] = *(const uint4*)(a + rr * ld_a + c);
+          if (kBwd) xv[k] = *(const uint4*)(x + rr * ld_x + c);
         }
-      } else {
+      }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          acc0[j] += v.v[j];
-          acc1[j] = fmaf(v.v[j], v.v[j], acc1[j]);
+      for (int k = 0; k < 4; ++k) {
+        const int64_t rr = r + (int64_t)k * RP;
+        if (rr < r1) {
+          const F8 v = unpack8(av[k]);
+          if (kBwd) {
+            const F8 xx = unpack8(xv[k]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              acc0[j] += v.v[j];
+              acc1[j] = fmaf(v.v[j], (xx.v[j] - mu.v[j]) * is.v[j], acc1[j]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              acc0[j] += v.v[j];
+              acc1[j] = fmaf(v.v[j], v.v[j], acc1[j]);
+            }
+          }
         }
       }
     }
+  }
+  // lanes of one warp that own the same column: lane ^ CVB, ^ 2 CVB, ... (CVB a power of two below 32)
+  const bool fold = CVB < 32 && (CVB & (CVB - 1)) == 0;
+  if (fold) {
+    for (int o = 16; o >= CVB; o >>= 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], o);
+        acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], o);
+      }
+    }
+  }
+  if (active && (!fold || (int)(threadIdx.x & 31) < CVB)) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       atomicAdd(&s0[cvl * 8 + j], acc0[j]);
@@ -196,16 +363,9 @@ __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __re
 template <bool kBwd>
 int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
                       const float* invstd, float* out, cudaStream_t st) {
-  const int CV = C / 8;
-  const int CVB = CV < 256 ? CV : 256;
-  const int cblocks = (int)cdiv(CV, CVB);
-  const int RP = 256 / CVB;
-  int64_t target = 148 * 6 / cblocks;
-  if (target < 1) target = 1;
-  int64_t rpb = cdiv(rows, target);
-  if (rpb < RP * 4) rpb = RP * 4;
-  dim3 grid((unsigned)cdiv(rows, rpb), cblocks);
-  channel_reduce_v8_kernel<kBwd><<<grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, CVB, rpb, mean, invstd, out);
+  const ColGeom g = col_geom(rows, C, 2);
+  channel_reduce_v8_kernel<kBwd><<<g.grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, g.CVB, g.rows_per_block, mean, invstd,
+                                                        out);
   ASF_LAUNCH_CHECK();
   return 0;
 }

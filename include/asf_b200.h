@@ -233,6 +233,13 @@ int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld,
 int asf_bn_finalize(const float* stats, int C, double count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                     float* scale, float* shift, float* save_mean, float* save_invstd, void* stream);
+/* train-mode BatchNorm forward in one pass over the raw conv output: asf_bn_finalize (same side effects, computed
+ * per block from `stats`) fused with asf_bn_apply; y == NULL publishes the statistics only.  Replaces the forward of
+ * nn.BatchNorm2d in training mode (+ ReLU / residual add: resnet_helper.py:181-225, :335-341). */
+int asf_bn_train_fwd(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
+                     int64_t rows, int C, const float* stats, double count, const float* gamma, const float* beta,
+                     float eps, float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                     float* scale, float* shift, float* save_mean, float* save_invstd, int relu, void* stream);
 /* eval/frozen: scale = gamma / sqrt(running_var + eps), shift = beta - running_mean*scale */
 int asf_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                 float eps, int C, float* scale, float* shift, void* stream);

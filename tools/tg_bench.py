@@ -37,7 +37,8 @@ CASES = [
 
 
 def main():
-    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    argv = sys.argv[1:]
+    args = [a for i, a in enumerate(argv) if not a.startswith("--") and (i == 0 or argv[i - 1] not in ("--reps", "--modes"))]
     sel = args[0] if args else ""
     once = "--once" in sys.argv
     reps = 20
