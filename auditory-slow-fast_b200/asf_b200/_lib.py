@@ -106,7 +106,8 @@ SIGNATURES = {
     "asf_pack_weight_t": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weights_multi": [_P, _I, C.c_longlong, _P],
     "asf_sgd_multi": [_P, _I, C.c_longlong, _P, _F, _F, _I, _I, _P],
-    "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _P],
+    "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _I, _P],
+    "asf_tapgemm_wgrad_ksplit": [C.POINTER(TapGemm)],
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "asf_bn_fold": [_P, _P, _P, _P, _F, _I, _P, _P, _P],

@@ -227,7 +227,7 @@ class Engine:
         self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
         self._flat_grad = None
         self._grad_views = {}
-        self._dwp = None
+        self._ws = None
 
     # ------------------------------------------------------------------------------------------ plan
     def invalidate_weights(self):
@@ -550,10 +550,16 @@ class Engine:
             tg.y_dim[i], tg.y_stride[i] = d, s_
         for j in range(3):
             tg.y_m_to_a[j] = m2a[j]
-        dwp = self._dwp_view(u)
-        tg.dwp = dwp.data_ptr()
+        ks = getattr(u, "wg_ksplit", None)
+        if ks is None:  # the launcher's split-K choice depends on the geometry only: ask once per unit
+            ks = L.lib().asf_tapgemm_wgrad_ksplit(C.byref(tg))
+            if ks < 1:
+                raise RuntimeError("asf_tapgemm_wgrad_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
+            u.wg_ksplit = ks
+        ws = self._wgrad_ws(ks * u.Cout * u.taps * u.Cin)
+        tg.dwp, tg.ksplit = ws.data_ptr(), ks
         L.call("asf_tapgemm", C.byref(tg), 1, st)
-        L.call("asf_unpack_wgrad", L.ptr(dwp), L.ptr(gview), u.Cout, u.Cin, u.taps, L.ptr(rscale), int(accumulate), st)
+        L.call("asf_unpack_wgrad", L.ptr(ws), L.ptr(gview), u.Cout, u.Cin, u.taps, L.ptr(rscale), int(accumulate), ks, st)
 
     # ------------------------------------------------------------------------------------------ grads
     def _ensure_grad_buffers(self):
@@ -572,15 +578,6 @@ class Engine:
             off += p.numel()
         self._param_by_name = dict(params)
         self._name_of = {id(p): n for n, p in params}
-        # packed wgrad workspace (fp32 [Cout][taps][Cin] per conv, accumulated with atomics, zeroed per pass)
-        tot = sum(u.Cout * u.taps * u.Cin for u in self.plan.units)
-        self._dwp = torch.zeros(tot, dtype=torch.float32, device=self.device)
-        o = 0
-        self._dwp_off = {}
-        for u in self.plan.units:
-            n = u.Cout * u.taps * u.Cin
-            self._dwp_off[u.name] = (o, n)
-            o += n
 
     def grad_prefix_end(self, names):
         """End offset (elements) of the flat gradient buffer covered by the parameters of the given finished
@@ -598,9 +595,13 @@ class Engine:
             end = max(end, e)
         return end
 
-    def _dwp_view(self, u):
-        o, n = self._dwp_off[u.name]
-        return self._dwp[o:o + n]
+    def _wgrad_ws(self, nfloats):
+        """Split-K workspace of the tcgen05 wgrad ([ksplit][Cout][taps][Cin] fp32 partial tiles, written then summed
+        by asf_unpack_wgrad on the same stream): one grow-only buffer shared by all layers."""
+        ws = getattr(self, "_ws", None)
+        if ws is None or ws.numel() < nfloats:
+            ws = self._ws = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=self.device)
+        return ws
 
     def _grad_target(self, p):
         """Returns (grad_view, accumulate) for a parameter following autograd semantics: a missing .grad is
@@ -766,7 +767,6 @@ class Engine:
         plan, m = self.plan, self.model
         st = L.stream_ptr()
         B = plan.B
-        self._dwp.zero_()
         plan.red_flat.zero_()
         # ---- head
         plan.dfeat.zero_()

@@ -487,18 +487,23 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const asf_sgd_desc_t* __
   }
 }
 
+// one thread per (o, c): reads of every split / tap are contiguous over c, the `taps` results of a thread are adjacent
+// in the OIHW master layout.
 __global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int I, int taps,
-                                    const float* __restrict__ rscale, int accumulate) {
-  int64_t total = (int64_t)O * I * taps;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int tp = (int)(i % taps);
-    int64_t r = i / taps;
-    int c = (int)(r % I);
-    int o = (int)(r / I);
-    float v = dwp[((int64_t)o * taps + tp) * I + c];
-    if (rscale) v *= rscale[o];
-    if (accumulate) v += dw[i];
-    dw[i] = v;
+                                    const float* __restrict__ rscale, int accumulate, int ksplit) {
+  const int64_t pairs = (int64_t)O * I, total = pairs * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % I);
+    const int o = (int)(i / I);
+    const float sc = rscale ? rscale[o] : 1.f;
+    for (int tp = 0; tp < taps; ++tp) {
+      const float* src = dwp + ((int64_t)o * taps + tp) * I + c;
+      float v = 0.f;
+      for (int k = 0; k < ksplit; ++k) v += src[(int64_t)k * total];  // split-K partial tiles, fixed order
+      v *= sc;
+      if (accumulate) v += dw[i * taps + tp];
+      dw[i * taps + tp] = v;
+    }
   }
 }
 
@@ -835,10 +840,10 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_
 }
 
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
-                     int accumulate, void* stream) {
-  ASF_CHECK_ARG(dwp && dw_oihw && O > 0 && I > 0 && taps > 0, "asf_unpack_wgrad: bad arguments");
-  unpack_wgrad_kernel<<<ew_grid((int64_t)O * I * taps), 256, 0, (cudaStream_t)stream>>>(dwp, dw_oihw, O, I, taps,
-                                                                                      rscale, accumulate);
+                     int accumulate, int ksplit, void* stream) {
+  ASF_CHECK_ARG(dwp && dw_oihw && O > 0 && I > 0 && taps > 0 && ksplit >= 1, "asf_unpack_wgrad: bad arguments");
+  unpack_wgrad_kernel<<<ew_grid((int64_t)O * I), 256, 0, (cudaStream_t)stream>>>(dwp, dw_oihw, O, I, taps,
+                                                                                      rscale, accumulate, ksplit);
   ASF_LAUNCH_CHECK();
   return 0;
 }

@@ -14,6 +14,7 @@
 constexpr int EPI_SLAB_COLS = 32;
 constexpr int EPI_SLAB_BYTES = TG_BLOCK_M * EPI_SLAB_COLS * 2;  // 8192
 constexpr int EPI_SHIFT_FLOATS = 256;
+constexpr int TGT_THREADS = 352;  // warp 0: TMA (activations), 1: MMA, 2..9: epilogue, 10: TMA (weights)
 
 __device__ __forceinline__ uint32_t slab_off(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
 
@@ -119,7 +120,7 @@ __device__ __forceinline__ void epi_slab_stats(const uint8_t* slab, int t, float
 // warp 0: TMA producer (mainloop operands), warp 1: MMA issuer + TMEM owner,
 // warps 2..5 / 6..9: two epilogue groups (group g drains TMEM buffer g, i.e. every other tile of this CTA).
 template <bool STATS>
-__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __grid_constant__ TgParams p) {
+__global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const __grid_constant__ TgParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;  // 1024-byte aligned (128B-swizzle atoms); checked below
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -156,16 +157,19 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
   // areas, unused in this mode, = [2][256] floats) and touches each global counter once, at the end; thousands of
   // same-address L2 atomics per launch serialise at ~7 ns each otherwise.
   const bool stats_smem = STATS && p.n_tiles == 1;
-  if (stats_smem && threadIdx.x >= 64)
-    for (int i = (int)threadIdx.x - 64; i < 2 * EPI_SHIFT_FLOATS; i += TG_THREADS - 64) shift_base[i] = 0.f;
+  if (stats_smem && threadIdx.x >= 64 && threadIdx.x < 320)
+    for (int i = (int)threadIdx.x - 64; i < 2 * EPI_SHIFT_FLOATS; i += 256) shift_base[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
 
-  if (warp == 0) {
-    // ===== TMA producer =====
+  if (warp == 0 || warp == 10) {
+    // ===== TMA producers: warp 0 streams the activation boxes, warp 10 the weight boxes.  One thread issuing both
+    // spends ~250 issue cycles per cp.async.bulk.tensor (coordinates, descriptor, barrier) -- as long as the four MMAs
+    // of a 128 x 128 k-chunk -- so the two streams run in parallel; warp 0 also posts the expected byte count. =====
     if (lane == 0) {
+      const bool act = warp == 0;
       int s = 0;
       uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -189,9 +193,12 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
           for (int kc = 0; kc < p.kchunks; ++kc) {
             mbar_wait(&sh->empty[s], ph ^ 1, 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
-            tma_load(&p.tm_a, &sh->full[s], sa, p.rank_a, kc * TG_KC, c1, c2, c3, c4);
-            tma_load(&p.tm_b, &sh->full[s], sa + TG_A_BYTES, 3, kc * TG_KC, wt, nrow, 0, 0);
+            if (act) {
+              mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
+              tma_load(&p.tm_a, &sh->full[s], sa, p.rank_a, kc * TG_KC, c1, c2, c3, c4);
+            } else {
+              tma_load(&p.tm_b, &sh->full[s], sa + TG_A_BYTES, 3, kc * TG_KC, wt, nrow, 0, 0);
+            }
             if (++s == p.stages) { s = 0; ph ^= 1; }
           }
         }
@@ -257,6 +264,38 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
     const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
     const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
     uint32_t gs = 0;  // slabs processed by this group so far (selects buffers and mbarrier parities)
+    // Operand prefetch runs one slab ahead of the math ACROSS tile boundaries (leader thread only): the sequence of
+    // (tile, slab) pairs of a group is known up front, and for narrow layers (one slab per tile) the TMA latency of
+    // the residual / mask slab would otherwise sit in every tile's critical path.
+    int pf_tile = blockIdx.x + group * gridDim.x, pf_s = 0;
+    uint32_t pf_gs = 0;
+    auto prefetch_next = [&]() {
+      if (pf_tile >= total_tiles) return;
+      const int n_tile = pf_tile % p.n_tiles, m_tile = pf_tile / p.n_tiles;
+      int st[3];
+      tile_coords(p, m_tile, st);
+      int o1 = 0, o2 = 0, o3 = 0;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int d = p.o_dim[j];
+        o1 = d == 1 ? st[j] : o1;
+        o2 = d == 2 ? st[j] : o2;
+        o3 = d == 3 ? st[j] : o3;
+      }
+      const int n0 = n_tile * p.block_n;
+      const int nslab = (min(p.block_n, p.N - n0) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
+      const int b = pf_gs & 1;
+      uint64_t* bar = &sh->op_full[group][b];
+      mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
+      for (int o = 0; o < n_ops; ++o)
+        tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + b) * EPI_SLAB_BYTES, p.rank_o, n0 + pf_s * 32, o1, o2, o3, 0);
+      ++pf_gs;
+      if (++pf_s == nslab) {
+        pf_s = 0;
+        pf_tile += 2 * gridDim.x;
+      }
+    };
+    if (leader && n_ops > 0) prefetch_next();  // slab 0 of this group's first tile
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       if ((it & 1) != group) continue;
@@ -278,12 +317,6 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
       if (g_shift) {
         for (int i = t; i < p.block_n; i += 128) s_shift[i] = (n0 + i < p.N) ? g_shift[n0 + i] : 0.f;
       }
-      if (leader && n_ops > 0) {  // operands of the first slab: in flight while the MMAs of this tile still run
-        uint64_t* bar = &sh->op_full[group][gs & 1];
-        mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
-        for (int o = 0; o < n_ops; ++o)
-          tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + (gs & 1)) * EPI_SLAB_BYTES, p.rank_o, n0, o1, o2, o3, 0);
-      }
       named_bar(bar_id, 128);  // s_shift visible to the group
       mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
       tc_fence_after();
@@ -293,13 +326,9 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
         uint32_t raw[32];
         tmem_ld32_issue(taddr0 + (uint32_t)(s * 32), raw);
         if (leader) {
-          if (n_ops > 0 && s + 1 < nslab) {
-            uint64_t* bar = &sh->op_full[group][b ^ 1];
-            mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
-            for (int o = 0; o < n_ops; ++o)
-              tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + (b ^ 1)) * EPI_SLAB_BYTES, p.rank_o, n0 + (s + 1) * 32, o1,
-                       o2, o3, 0);
-          }
+          // operands of the following slab (possibly of the next tile) into the other buffer: its last reader was
+          // slab gs-1, and every thread has passed that slab's closing barrier
+          if (n_ops > 0) prefetch_next();
           bulk_wait_read<1>();  // the store that last read out_buf[b] (two slabs ago) has drained it
         }
         tmem_ld_wait();
@@ -356,8 +385,8 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_tma_kernel(const __
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
-  if (stats_smem && threadIdx.x >= 64) {
-    for (int i = (int)threadIdx.x - 64; i < p.N; i += TG_THREADS - 64) {
+  if (stats_smem && threadIdx.x >= 64 && threadIdx.x < 320) {
+    for (int i = (int)threadIdx.x - 64; i < p.N; i += 256) {
       atomicAdd(p.epi.stats + i, shift_base[i]);
       atomicAdd(p.epi.stats + p.epi.stats_stride + i, shift_base[EPI_SHIFT_FLOATS + i]);
     }

@@ -176,7 +176,6 @@ constexpr int TG_BLOCK_M = 128;
 constexpr int TG_KC = 64;                 // bf16 elements per 128B swizzle row
 constexpr int TG_A_BYTES = TG_BLOCK_M * 128;
 constexpr int TG_THREADS = 320;           // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2..5 / 6..9 two epilogue groups
-constexpr int WG_THREADS = 192;           // wgrad: warp0 TMA, warp1 MMA, warps 2..5 epilogue
 constexpr int TG_SMEM_BUDGET = 200 * 1024;
 
 struct TgParams {
@@ -206,6 +205,7 @@ struct TgParams {
   // mode 1
   float* dwp;
   int ntaps_w, ksplit, c_tiles, r_tiles;
+  int wg_ny, wg_nx, wg_halves, wg_tn, wg_tmem_cols;  // second-generation wgrad tile (tapgemm_wgrad.cuh)
 };
 
 struct TgShared {
@@ -548,117 +548,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid
 
 #include "tapgemm_fwd_tma.cuh"
 
-// ------------------------------------------------------------------------------------------------ mode 1 (wgrad)
-constexpr int WG_STAGE_BYTES = 4 * 16384;  // Y: 2 boxes [128 rows][64 ch], X: 2 boxes [128 rows][64 ch]
-constexpr int WG_STAGES = 3;
-
-__global__ void __launch_bounds__(WG_THREADS, 1) tapgemm_wgrad_kernel(const __grid_constant__ TgParams p) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  TgShared* sh = (TgShared*)(smem + (size_t)WG_STAGES * WG_STAGE_BYTES);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-  // tile decode: blockIdx.x = ((r_tile * ntaps + tap) * c_tiles + c_tile) * ksplit + ks
-  int idx = blockIdx.x;
-  const int ks = idx % p.ksplit;
-  idx /= p.ksplit;
-  const int c_tile = idx % p.c_tiles;
-  idx /= p.c_tiles;
-  const int tap = idx % p.ntaps;
-  const int r_tile = idx / p.ntaps;
-  const int n_iters = (p.m_tiles_total - ks + p.ksplit - 1) / p.ksplit;  // row tiles ks, ks+ksplit, ...
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tm_a);
-    tma_prefetch_desc(&p.tm_b);
-    for (int s = 0; s < WG_STAGES; ++s) {
-      mbar_init(&sh->full[s], 1);
-      mbar_init(&sh->empty[s], 1);
-    }
-    mbar_init(&sh->tmem_full[0], 1);
-    fence_barrier_init();
-  }
-  if (warp == 1) tmem_alloc(&sh->tmem_base, 128);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = sh->tmem_base;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      for (int i = 0; i < n_iters; ++i) {
-        const int m_tile = ks + i * p.ksplit;
-        int st[3];
-        tile_coords(p, m_tile, st);
-        int xb[5] = {0, 0, 0, 0, 0}, yb[5] = {0, 0, 0, 0, 0};
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          if (p.m_to_a[j] > 0) xb[p.m_to_a[j]] = st[j];
-          if (p.y_m_to_a[j] > 0) yb[p.y_m_to_a[j]] = st[j];
-        }
-        mbar_wait(&sh->empty[s], ph ^ 1, 11);
-        uint8_t* sy = smem + (size_t)s * WG_STAGE_BYTES;
-        uint8_t* sx = sy + 2 * 16384;
-        mbar_expect_tx(&sh->full[s], (uint32_t)WG_STAGE_BYTES);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          tma_load(&p.tm_b, &sh->full[s], sy + h * 16384, p.rank_b, r_tile * 128 + h * 64, yb[1], yb[2], yb[3], yb[4]);
-          tma_load(&p.tm_a, &sh->full[s], sx + h * 16384, p.rank_a, c_tile * 128 + h * 64, xb[1] + p.a_off[tap][0],
-                   xb[2] + p.a_off[tap][1], xb[3] + p.a_off[tap][2], xb[4] + p.a_off[tap][3]);
-        }
-        if (++s == WG_STAGES) { s = 0; ph ^= 1; }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(128, 128, 1, 1);
-      int s = 0;
-      uint32_t ph = 0;
-      for (int i = 0; i < n_iters; ++i) {
-        mbar_wait(&sh->full[s], ph, 12);
-        tc_fence_after();
-        const uint32_t sy = smem_u32(smem + (size_t)s * WG_STAGE_BYTES);
-        const uint32_t sx = sy + 2 * 16384;
-        // MN-major, 128B swizzle: 64-channel chunks LBO = 16384 B apart, 8-row (K) groups SBO = 1024 B apart
-        const uint64_t adesc = make_sdesc(sy, 16384, 1024);
-        const uint64_t bdesc = make_sdesc(sx, 16384, 1024);
-#pragma unroll
-        for (int k = 0; k < 8; ++k)  // 16 rows (= 2048 B = 128 x 16B units) per UMMA_K step
-          umma_bf16(tmem_base, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc, (i | k) != 0);
-        umma_commit(&sh->empty[s]);
-        if (++s == WG_STAGES) { s = 0; ph ^= 1; }
-      }
-      umma_commit(&sh->tmem_full[0]);
-    }
-  } else {
-    const int quarter = warp & 3;
-    const int n = r_tile * 128 + quarter * 32 + lane;  // output channel (row of D)
-    mbar_wait(&sh->tmem_full[0], 0, 13);
-    tc_fence_after();
-    const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const int wt = p.b_tap[tap];
-    for (int ch = 0; ch < 8; ++ch) {
-      const int cb = c_tile * 128 + ch * 16;
-      if (cb >= p.K) break;
-      float v[16];
-      tmem_ld16(taddr0 + (uint32_t)(ch * 16), v);
-      if (n < p.N && n_iters > 0) {
-        float* o = p.dwp + ((long long)n * p.ntaps_w + wt) * p.K + cb;
-#pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (cb + j < p.K) atomicAdd(o + j, v[j]);
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
-  }
-}
+#include "tapgemm_wgrad.cuh"
 
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -762,6 +652,54 @@ static int debug_sync(cudaStream_t st) {
     g_debug_sync = (e && e[0] == '1') ? 1 : 0;
   }
   if (g_debug_sync) ASF_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// wgrad tiling: 64-row boxes (half of the 128-row M tile, split on its slowest boxed dim), output-channel tile of one
+// or two 128-row halves, input-channel tile <= 256, split-K so that about one wave of CTAs is in flight.
+struct WgPlan {
+  int box[3];
+  int halves, tn, ny, nx, r_tiles, c_tiles, tmem_cols, stages, ksplit, m_tiles;
+};
+static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
+  int prod = 1;
+  for (int j = 0; j < 3; ++j) {
+    w->box[j] = q->m_box[j];
+    prod *= q->m_box[j];
+  }
+  ASF_CHECK_ARG(prod == TG_BLOCK_M, "asf_tapgemm: product of m_box must be %d (got %d)", TG_BLOCK_M, prod);
+  for (int j = 2; j >= 0; --j)
+    if (w->box[j] > 1) {
+      w->box[j] /= 2;
+      break;
+    }
+  w->m_tiles = 1;
+  for (int j = 0; j < 3; ++j) {
+    ASF_CHECK_ARG(ilog2_exact(w->box[j]) >= 0 && q->m_ext[j] >= 1, "asf_tapgemm: m_box must be powers of two");
+    w->m_tiles *= (int)cdiv(q->m_ext[j], w->box[j]);
+  }
+  w->halves = q->N > 128 ? 2 : 1;
+  const int TM = w->halves * 128;
+  w->r_tiles = (int)cdiv(q->N, TM);
+  const int k16 = (int)cdiv(q->K, 16) * 16;
+  w->tn = k16 < 256 ? k16 : 256;
+  w->c_tiles = (int)cdiv(q->K, w->tn);
+  w->ny = (int)cdiv(q->N < TM ? q->N : TM, 64);
+  w->nx = (int)cdiv(w->tn, 64);
+  const int need = (w->halves - 1) * w->tn + (int)cdiv(w->tn, 32) * 32;
+  int cols = 32;
+  while (cols < need) cols *= 2;
+  w->tmem_cols = cols;
+  const int stage_bytes = (w->ny + w->nx) * WG2_BOX_BYTES;
+  int stages = (227 * 1024 - (int)sizeof(TgShared)) / stage_bytes;
+  if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
+  ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: wgrad stage does not fit twice in shared memory");
+  w->stages = stages;
+  const int64_t base_tiles = (int64_t)w->r_tiles * w->c_tiles * q->ntaps;
+  int ks = (int)cdiv(num_sms(), base_tiles);
+  if (ks > w->m_tiles / 4) ks = w->m_tiles / 4;  // at least four 64-row stages of MMA work per partial tile
+  if (ks < 1) ks = 1;
+  w->ksplit = ks;
   return 0;
 }
 
@@ -928,9 +866,9 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
         pr->block_n = bn; pr->grid = grid;
       }
       if (si)
-        tapgemm_fwd_tma_kernel<true><<<grid, TG_THREADS, smem_t, st>>>(p);
+        tapgemm_fwd_tma_kernel<true><<<grid, TGT_THREADS, smem_t, st>>>(p);
       else
-        tapgemm_fwd_tma_kernel<false><<<grid, TG_THREADS, smem_t, st>>>(p);
+        tapgemm_fwd_tma_kernel<false><<<grid, TGT_THREADS, smem_t, st>>>(p);
       prof_end(pr, st);
       ASF_LAUNCH_CHECK();
       return debug_sync(st);
@@ -952,15 +890,30 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     return debug_sync(st);
   }
 
-  // mode 1: wgrad
+  // mode 1: wgrad (second generation: 64-row stages, up to 256 x 256 per CTA, split-K partials by plain stores)
   ASF_CHECK_ARG(q->y && q->dwp && q->y_nd >= 1 && q->y_nd <= 4, "asf_tapgemm: mode 1 needs y/dwp");
+  WgPlan wp;
+  rc = wgrad_plan(q, &wp);
+  if (rc) return rc;
+  // re-tile the M-space with the 64-row boxes of the plan
+  p.m_tiles_total = 1;
+  for (int j = 0; j < 3; ++j) {
+    p.m_log2[j] = ilog2_exact(wp.box[j]);
+    p.m_tiles[j] = (int)cdiv(q->m_ext[j], wp.box[j]);
+    p.m_tiles_total *= p.m_tiles[j];
+  }
+  for (int j = 0; j < 4; ++j) box_a[j] = 1;
+  for (int j = 0; j < 3; ++j)
+    if (q->m_to_a[j] > 0) box_a[q->m_to_a[j] - 1] = wp.box[j];
+  rc = encode_map(&p.tm_a, q->a, q->K, q->nd, q->a_dim, q->a_stride, box_a);
+  if (rc) return rc;
   last = 0;
   for (int j = 0; j < 3; ++j) {
     p.y_m_to_a[j] = q->y_m_to_a[j];
     if (q->y_m_to_a[j] > 0) {
       ASF_CHECK_ARG(q->y_m_to_a[j] <= q->y_nd && q->y_m_to_a[j] > last, "asf_tapgemm: y_m_to_a must be increasing");
       last = q->y_m_to_a[j];
-      box_y[q->y_m_to_a[j] - 1] = q->m_box[j];
+      box_y[q->y_m_to_a[j] - 1] = wp.box[j];
     } else {
       ASF_CHECK_ARG(q->m_box[j] == 1, "asf_tapgemm: unmapped Y M-dim must have box 1");
     }
@@ -969,25 +922,24 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   if (rc) return rc;
   p.rank_b = q->y_nd + 1;
   p.dwp = q->dwp;
-  p.c_tiles = (int)cdiv(q->K, 128);
-  p.r_tiles = (int)cdiv(q->N, 128);
-  int64_t base_tiles = (int64_t)p.c_tiles * p.r_tiles * p.ntaps;
-  int ks = q->ksplit;
-  if (ks <= 0) {
-    ks = (int)cdiv(2 * num_sms(), base_tiles);
-    // every CTA ends with a 128x128 fp32 atomic flush: give it at least 8 row tiles of MMA work to amortise that
-    if (ks > p.m_tiles_total / 8) ks = p.m_tiles_total / 8;
-    if (ks < 1) ks = 1;
-  }
+  p.c_tiles = wp.c_tiles;
+  p.r_tiles = wp.r_tiles;
+  p.wg_halves = wp.halves;
+  p.wg_tn = wp.tn;
+  p.wg_ny = wp.ny;
+  p.wg_nx = wp.nx;
+  p.wg_tmem_cols = wp.tmem_cols;
+  p.stages = wp.stages;
+  int ks = q->ksplit > 0 ? q->ksplit : wp.ksplit;
   ASF_CHECK_ARG(ks >= 1 && ks <= p.m_tiles_total, "asf_tapgemm: ksplit %d out of range (row tiles %d)", ks, p.m_tiles_total);
   p.ksplit = ks;
-  const size_t smem = (size_t)WG_STAGES * WG_STAGE_BYTES + sizeof(TgShared) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ASF_CUDA(cudaFuncSetAttribute(tapgemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+  const size_t smem = (size_t)wp.stages * (wp.ny + wp.nx) * WG2_BOX_BYTES + sizeof(TgShared);
+  static size_t smem_set_w = 0;
+  if (smem > smem_set_w) {
+    ASF_CUDA(cudaFuncSetAttribute(tapgemm_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    smem_set_w = 227 * 1024;
   }
-  int64_t grid = base_tiles * ks;
+  int64_t grid = (int64_t)wp.r_tiles * wp.c_tiles * p.ntaps * ks;
   ASF_CHECK_ARG(grid < (1ll << 31), "asf_tapgemm: wgrad grid too large");
   const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
   ProfRec* pr = prof_begin(st, 1, flops);
@@ -995,10 +947,18 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
     pr->block_n = ks; pr->grid = (int)grid;
   }
-  tapgemm_wgrad_kernel<<<(unsigned)grid, WG_THREADS, smem, st>>>(p);
+  tapgemm_wgrad2_kernel<<<(unsigned)grid, WG2_THREADS, smem, st>>>(p);
   prof_end(pr, st);
   ASF_LAUNCH_CHECK();
   return debug_sync(st);
+}
+
+extern "C" int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* q) {
+  ASF_CHECK_ARG(q != nullptr, "asf_tapgemm_wgrad_ksplit: null");
+  WgPlan wp;
+  int rc = wgrad_plan(q, &wp);
+  if (rc) return rc;
+  return wp.ksplit;
 }
 
 extern "C" int asf_prof_start(int max_records) {

@@ -139,7 +139,9 @@ int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout
  *
  * mode 0 (forward / dgrad): as above, out dtype out_dtype with the fused epilogue.
  * mode 1 (wgrad): D[n][c] = sum_rows Y[row][n] * A[row + a_off[tap]][c]; Y uses the same M-space through its
- *         own tensor map (y_*), result atomically added (fp32) into dwp[N][ntaps_w][K] at tap b_tap[tap].
+ *         own tensor map (y_*).  The rows are split over `ksplit` groups of CTAs; group k WRITES (no atomics, no
+ *         pre-zeroing) its partial sums to dwp[k][N][ntaps_w][K] at tap b_tap[tap]; asf_unpack_wgrad adds the
+ *         groups.  ksplit = 0 lets the launcher choose -- query it first with asf_tapgemm_wgrad_ksplit to size dwp.
  */
 typedef struct {
   const void* a;      /* bf16 */
@@ -165,12 +167,14 @@ typedef struct {
   int64_t y_dim[4];
   int64_t y_stride[4];
   int32_t y_nd, y_m_to_a[3];
-  float* dwp;         /* fp32 [N][ntaps_w][K], accumulated */
+  float* dwp;         /* fp32 [ksplit][N][ntaps_w][K] workspace, written */
   int32_t ksplit;
   int32_t block_n;    /* 0 = choose */
 } asf_tapgemm_t;
 
 int asf_tapgemm(const asf_tapgemm_t* p, int mode, void* stream);
+/* the ksplit asf_tapgemm(p, 1, ...) uses when p->ksplit == 0 (>= 1), or a negative error code */
+int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* p);
 
 /* Stem weight gradient (Cin = 1, <= 35 taps): in fp32 [B][Tin][Fin], dout [rows][Cout] -> dw OIHW fp32.
  * Replaces cuDNN wgrad of the stem convs (stem_helper.py:150-157). */
@@ -218,9 +222,10 @@ typedef struct {
 #define ASF_SGD_CHUNK 4096
 int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks, const float* lr_dev, float momentum,
                   float dampening, int nesterov, int first_step, void* stream);
-/* dwp [O][taps][I] fp32 -> dw_oihw [O][I][taps] = (accumulate ? dw : 0) + rscale[o] * dwp */
+/* dwp [ksplit][O][taps][I] fp32 (the split-K partial tiles of asf_tapgemm mode 1)
+ *   -> dw_oihw [O][I][taps] = (accumulate ? dw : 0) + rscale[o] * sum_k dwp[k] */
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
-                     int accumulate, void* stream);
+                     int accumulate, int ksplit, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * BatchNorm2d (audio_slowfast/models/batchnorm_helper.py:16-31 -> nn.BatchNorm2d; train / eval / frozen,

@@ -28,16 +28,8 @@ class Harness(Engine):
         self.use_tc = dtype == torch.bfloat16
         self.force_simt = force_simt
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self._dwp_buf = None
+        self._ws = None
         self.grad_hook = None
-
-    def _dwp_view(self, u):
-        n = u.Cout * u.taps * u.Cin
-        if self._dwp_buf is None or self._dwp_buf.numel() < n:
-            self._dwp_buf = torch.zeros(n, dtype=torch.float32, device=self.device)
-        v = self._dwp_buf[:n]
-        v.zero_()
-        return v
 
 
 def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, in_scale=1.0):

@@ -288,7 +288,7 @@ def test_weight_pack_roundtrip():
     assert torch.equal(p, ws.permute(0, 2, 1).contiguous())
     assert torch.equal(pt, ws.permute(1, 2, 0).contiguous())
     back = torch.ones_like(w)
-    L.call("asf_unpack_wgrad", L.ptr(p), L.ptr(back), O, I, taps, None, 1, st)
+    L.call("asf_unpack_wgrad", L.ptr(p), L.ptr(back), O, I, taps, None, 1, 1, st)
     torch.cuda.synchronize()
     assert torch.allclose(back[..., 0], 1 + ws)
 
