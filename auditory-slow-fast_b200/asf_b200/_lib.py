@@ -51,7 +51,7 @@ class TapGemm(C.Structure):
         ("epi", Epilogue),
         ("y", C.c_void_p), ("y_dim", C.c_int64 * 4), ("y_stride", C.c_int64 * 4),
         ("y_nd", C.c_int32), ("y_m_to_a", C.c_int32 * 3),
-        ("dwp", C.c_void_p), ("ksplit", C.c_int32), ("block_n", C.c_int32),
+        ("dwp", C.c_void_p), ("ksplit", C.c_int32), ("block_n", C.c_int32), ("max_ctas", C.c_int32),
     ]
 
 

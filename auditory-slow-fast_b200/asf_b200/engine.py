@@ -23,8 +23,10 @@ instead: that is the fp32 parity mode (1e-3 logits criterion), not a fallback --
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -227,7 +229,14 @@ class Engine:
         self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
         self._flat_grad = None
         self._grad_views = {}
-        self._ws = None
+        self._ws = {}
+        # Two-stream execution (SlowFast only): the fast pathway depends on the slow one only through the lateral
+        # convs, so it runs on a side stream next to the slow pathway; each stream sizes its persistent tap-GEMM
+        # grids for its share of the SMs so that the two sets of CTAs are resident side by side.
+        self.two_stream = model.num_pathways == 2 and os.environ.get("ASF_TWO_STREAM", "1") != "0"
+        split = os.environ.get("ASF_SM_SPLIT", "0,0").split(",")  # 0 = no cap: CTAs of both streams share all SMs
+        self.sm_split = (int(split[0]), int(split[1]))
+        self._side = None
 
     # ------------------------------------------------------------------------------------------ plan
     def invalidate_weights(self):
@@ -277,6 +286,7 @@ class Engine:
             u.bn_name = "s1.pathway%d_stem.bn" % p
             u.pooled = pooled
             u.is_stem = True
+            u.path = p
             plan.stems.append(u)
             x.append(pooled)
 
@@ -297,6 +307,7 @@ class Engine:
                 fuse_out = xs_full.slice(x[0].C, f.conv_f2s.out_channels, name="s%d_fuse.out" % (si + 1))
                 fu = add_unit("s%d_fuse" % (si + 1), f.conv_f2s, f.bn, x[1], fuse_out, relu=True,
                               bn_name="s%d_fuse.bn" % (si + 1))
+                fu.path = 1
                 order.append(("fuse", fu))
                 x[0] = xs_full  # the stage reads slow + lateral channels
             for p in range(npath):
@@ -318,7 +329,7 @@ class Engine:
                     else:
                         out = Act(B, T, Fo, cout, dt, dev, name=pre + ".out")
                         out.full = out
-                    entry = {"name": pre, "x": h, "out": out}
+                    entry = {"name": pre, "x": h, "out": out, "path": p}
                     if hasattr(blk, "branch1"):
                         sc = Act(B, T, Fo, cout, dt, dev, name=pre + ".sc")
                         entry["b1"] = add_unit(pre + ".branch1", blk.branch1, blk.branch1_bn, h, sc, relu=False,
@@ -332,6 +343,9 @@ class Engine:
                     entry["b"] = add_unit(pre + ".branch2.b", b2.b, b2.b_bn, ha, hb, relu=True, bn_name=pre + ".branch2.b_bn")
                     entry["c"] = add_unit(pre + ".branch2.c", b2.c, b2.c_bn, hb, out, relu=True, res=res,
                                           bn_name=pre + ".branch2.c_bn")
+                    for k_ in ("b1", "a", "b", "c"):
+                        if k_ in entry:
+                            entry[k_].path = p
                     order.append(("block", entry))
                     h = out
                 x[p] = h
@@ -453,6 +467,24 @@ class Engine:
         L.call("asf_pack_weights_multi", L.ptr(ent[0]), ent[1], ent[2], st)
 
     # ------------------------------------------------------------------------------------------ conv launches
+    # ------------------------------------------------------------------------------------------ streams
+    def _ts(self):
+        return self.two_stream and self.plan is not None and len(self.plan.stems) == 2
+
+    def _side_stream(self):
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        return self._side
+
+    def _on(self, path):
+        """Context that issues work of pathway ``path`` on its stream (fast pathway -> side stream)."""
+        if path == 1 and self._ts():
+            return torch.cuda.stream(self._side_stream())
+        return contextlib.nullcontext()
+
+    def _cap(self, u):
+        return self.sm_split[getattr(u, "path", 0)] if self._ts() else 0
+
     def _tc_ok(self, u):
         return self.use_tc and not self.force_simt and u.axis is not None and u.Cin % 8 == 0
 
@@ -462,6 +494,7 @@ class Engine:
             tg = L.TapGemm()
             o_stride = tg_forward_geometry(u, tg, u.x)
             tg.bw, tg.N = u.w_pack.data_ptr(), u.Cout
+            tg.max_ctas = self._cap(u)
             tg.out, tg.out_dtype, tg.ld_out = out.ptr, out.code, out.ld
             for j in range(3):
                 tg.o_stride[j] = o_stride[j]
@@ -519,6 +552,7 @@ class Engine:
             for i, (j, off) in enumerate(taps):
                 tg.b_tap[i] = j
             tg.bw = u.w_pack_t.data_ptr()
+            tg.max_ctas = self._cap(u)
             tg.out, tg.out_dtype, tg.ld_out = dx.row_ptr(row_off), dx.code, dx.ld
             for j in range(3):
                 tg.o_stride[j] = o_stride[j]
@@ -544,18 +578,19 @@ class Engine:
         tg = L.TapGemm()
         tg_forward_geometry(u, tg, u.x)
         tg.N = u.Cout
+        tg.max_ctas = self._cap(u)
         dims, strides, m2a = tg_output_space(u, dy)
         tg.y, tg.y_nd = dy.ptr, len(dims)
         for i, (d, s_) in enumerate(zip(dims, strides)):
             tg.y_dim[i], tg.y_stride[i] = d, s_
         for j in range(3):
             tg.y_m_to_a[j] = m2a[j]
-        ks = getattr(u, "wg_ksplit", None)
+        ks = getattr(u, "wg_ksplit", None) if getattr(u, "wg_ksplit_cap", None) == tg.max_ctas else None
         if ks is None:  # the launcher's split-K choice depends on the geometry only: ask once per unit
             ks = L.lib().asf_tapgemm_wgrad_ksplit(C.byref(tg))
             if ks < 1:
                 raise RuntimeError("asf_tapgemm_wgrad_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
-            u.wg_ksplit = ks
+            u.wg_ksplit, u.wg_ksplit_cap = ks, tg.max_ctas
         ws = self._wgrad_ws(ks * u.Cout * u.taps * u.Cin)
         tg.dwp, tg.ksplit = ws.data_ptr(), ks
         L.call("asf_tapgemm", C.byref(tg), 1, st)
@@ -597,10 +632,12 @@ class Engine:
 
     def _wgrad_ws(self, nfloats):
         """Split-K workspace of the tcgen05 wgrad ([ksplit][Cout][taps][Cin] fp32 partial tiles, written then summed
-        by asf_unpack_wgrad on the same stream): one grow-only buffer shared by all layers."""
-        ws = getattr(self, "_ws", None)
+        by asf_unpack_wgrad on the same stream): one grow-only buffer per stream, shared by the layers issued on it."""
+        side = self._side is not None and torch.cuda.current_stream(self.device) == self._side
+        key = 1 if side else 0  # one workspace per issuing stream (main / fast-pathway side stream)
+        ws = self._ws.get(key)
         if ws is None or ws.numel() < nfloats:
-            ws = self._ws = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=self.device)
+            ws = self._ws[key] = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=self.device)
         return ws
 
     def _grad_target(self, p):
@@ -681,31 +718,52 @@ class Engine:
         if training:
             plan.stats_flat.zero_()
         self._prepare_all(training)
+        ts = self._ts()
+        main = torch.cuda.current_stream(self.device)
+        side = self._side_stream() if ts else None
+        if ts:
+            side.wait_stream(main)  # fork: inputs, zeroed statistics and refreshed weights are ready on `main`
         # stems
         for p, u in enumerate(plan.stems):
-            xin = xs[p]
-            if xin.dtype != torch.float32:
-                xin = xin.float()
-            u.x.buf.copy_(xin.reshape(u.x.buf.shape))  # (B,1,T,F) fp32 is already channels-last for C = 1
-            g = u.geom()
-            e = _epilogue()
-            L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), L.F32, L.ptr(u.w_pack), L.F32, C.c_void_p(u.y.ptr),
-                   u.y.code, C.byref(g), C.byref(e), st)
-            if u.batch_mode:
-                L.call("asf_channel_stats", C.c_void_p(u.y.ptr), u.y.code, u.y.rows, u.Cout, u.y.ld, L.ptr(u.stats), st)
-                self._bn_forward(u, u.y, None, None, False, training, st)
-            L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld, u.y.code,
-                   u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
-        # stages
+            with self._on(p):
+                st = L.stream_ptr()
+                xin = xs[p]
+                if xin.dtype != torch.float32:
+                    xin = xin.float()
+                u.x.buf.copy_(xin.reshape(u.x.buf.shape))  # (B,1,T,F) fp32 is already channels-last for C = 1
+                g = u.geom()
+                e = _epilogue()
+                L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), L.F32, L.ptr(u.w_pack), L.F32, C.c_void_p(u.y.ptr),
+                       u.y.code, C.byref(g), C.byref(e), st)
+                if u.batch_mode:
+                    L.call("asf_channel_stats", C.c_void_p(u.y.ptr), u.y.code, u.y.rows, u.Cout, u.y.ld,
+                           L.ptr(u.stats), st)
+                    self._bn_forward(u, u.y, None, None, False, training, st)
+                L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld,
+                       u.y.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+        # stages.  Two-stream mode: laterals and fast blocks run ahead on the side stream; the slow blocks of a stage
+        # wait for that stage's lateral (which writes the lateral channels of the buffer they read).
+        ev_fuse = None
         for kind, item in plan.order:
             if kind == "fuse":
-                self._unit_forward(item, training, True)
+                with self._on(1):
+                    self._unit_forward(item, training, True)
+                    if ts:
+                        ev_fuse = torch.cuda.Event()
+                        ev_fuse.record(side)
             else:
-                if "b1" in item:
-                    self._unit_forward(item["b1"], training, True)
-                self._unit_forward(item["a"], training, True)
-                self._unit_forward(item["b"], training, True)
-                self._unit_forward(item["c"], training, True)
+                if ts and item["path"] == 0 and ev_fuse is not None:
+                    main.wait_event(ev_fuse)
+                    ev_fuse = None
+                with self._on(item["path"]):
+                    if "b1" in item:
+                        self._unit_forward(item["b1"], training, True)
+                    self._unit_forward(item["a"], training, True)
+                    self._unit_forward(item["b"], training, True)
+                    self._unit_forward(item["c"], training, True)
+        if ts:
+            main.wait_stream(side)  # join
+        st = L.stream_ptr()
         # head
         head = m.head
         c_off = 0
@@ -809,51 +867,74 @@ class Engine:
             written.add(key)
             return fresh
 
+        ts = self._ts()
+        main = torch.cuda.current_stream(self.device)
+        side = self._side_stream() if ts else None
+        if ts:
+            side.wait_stream(main)  # fork: head gradients / pooled gradients of both pathways are on `main`
+        pending = []  # two-stream mode: units finished since the last point where both streams were ordered
         for kind, item in reversed(plan.order):
             if kind == "fuse":
                 u = item
-                # dz of the lateral = its channel slice of the slow concat gradient (already masked by the
-                # consumer block's last dgrad); dx accumulates into the fast activation's gradient.
-                fresh = first_write(u.x)
-                u.x.grad.zeroed = False
-                # the lateral is always the LAST writer of its (fast) input's gradient: it applies the ReLU mask
-                self._unit_backward(u, u.y.grad, True, not fresh, dx_mask=u.x)
-                self._notify([u.name])
+                if ts:
+                    # the lateral reads its slice of the slow concat gradient (written by the first slow block of the
+                    # stage above, on `main`) and is the last writer of the fast activation's gradient (side stream)
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    side.wait_event(ev)
+                with self._on(1):
+                    # dz of the lateral = its channel slice of the slow concat gradient (already masked by the
+                    # consumer block's last dgrad); dx accumulates into the fast activation's gradient.
+                    fresh = first_write(u.x)
+                    u.x.grad.zeroed = False
+                    # the lateral is always the LAST writer of its (fast) input's gradient: it applies the ReLU mask
+                    self._unit_backward(u, u.y.grad, True, not fresh, dx_mask=u.x)
+                    # on the side stream, after the wait above, everything issued so far on either stream is ordered
+                    self._notify(pending + [u.name])
+                    pending = []
             else:
                 blk = item
-                xin, out = blk["x"], blk["out"]
-                dz_out = out.grad
-                c, b_, a = blk["c"], blk["b"], blk["a"]
-                # c: dgrad -> d(h_b), masked by h_b > 0
-                self._unit_backward(c, dz_out, True, False, dx_mask=c.x)
-                self._unit_backward(b_, b_.y.grad, True, False, dx_mask=b_.x)
-                fresh = first_write(xin)
-                xg = xin.grad
-                # is this block input also consumed elsewhere later in the backward (lateral of the fast path)?
-                # the mask is applied by the LAST writer; a stage's first fast block is followed (in backward
-                # order) by the lateral conv that reads the same activation, so the mask must wait for it.
-                later = blk.get("mask_later", False)
-                if "b1" in blk:
-                    b1 = blk["b1"]
-                    if fresh and b1.s > 1:
-                        xg.buf.zero_() if xg.parent is None else xg.view().zero_()
-                        xg.zeroed = True
-                        fresh = False
-                    self._unit_backward(b1, dz_out, True, not fresh)
-                    self._unit_backward(a, a.y.grad, True, True, dx_mask=None if later else xin)
-                else:
-                    self._unit_backward(a, a.y.grad, True, not fresh, dx_res=dz_out, dx_mask=None if later else xin)
-                self._notify([blk["name"]])
+                with self._on(blk["path"]):
+                    xin, out = blk["x"], blk["out"]
+                    dz_out = out.grad
+                    c, b_, a = blk["c"], blk["b"], blk["a"]
+                    # c: dgrad -> d(h_b), masked by h_b > 0
+                    self._unit_backward(c, dz_out, True, False, dx_mask=c.x)
+                    self._unit_backward(b_, b_.y.grad, True, False, dx_mask=b_.x)
+                    fresh = first_write(xin)
+                    xg = xin.grad
+                    # is this block input also consumed elsewhere later in the backward (lateral of the fast path)?
+                    # the mask is applied by the LAST writer; a stage's first fast block is followed (in backward
+                    # order) by the lateral conv that reads the same activation, so the mask must wait for it.
+                    later = blk.get("mask_later", False)
+                    if "b1" in blk:
+                        b1 = blk["b1"]
+                        if fresh and b1.s > 1:
+                            xg.buf.zero_() if xg.parent is None else xg.view().zero_()
+                            xg.zeroed = True
+                            fresh = False
+                        self._unit_backward(b1, dz_out, True, not fresh)
+                        self._unit_backward(a, a.y.grad, True, True, dx_mask=None if later else xin)
+                    else:
+                        self._unit_backward(a, a.y.grad, True, not fresh, dx_res=dz_out, dx_mask=None if later else xin)
+                    if ts:
+                        pending.append(blk["name"])
+                    else:
+                        self._notify([blk["name"]])
         # ---- stems
         for u in plan.stems:
-            pooled = u.pooled
-            dz = u.y.grad
-            L.call("asf_bn_relu_maxpool_bwd", C.c_void_p(u.y.ptr), C.c_void_p(pooled.grad.ptr), pooled.grad.ld,
-                   C.c_void_p(dz.ptr), dz.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
-            if u.batch_mode:
-                u.raw = u.y  # the stem keeps its raw conv output in u.y
-            self._unit_backward(u, dz, False, False)
-        self._notify(["stems"])
+            with self._on(u.path):
+                st = L.stream_ptr()
+                pooled = u.pooled
+                dz = u.y.grad
+                L.call("asf_bn_relu_maxpool_bwd", C.c_void_p(u.y.ptr), C.c_void_p(pooled.grad.ptr), pooled.grad.ld,
+                       C.c_void_p(dz.ptr), dz.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+                if u.batch_mode:
+                    u.raw = u.y  # the stem keeps its raw conv output in u.y
+                self._unit_backward(u, dz, False, False)
+        if ts:
+            main.wait_stream(side)  # join
+        self._notify(pending + ["stems"])
 
     def _notify(self, names):
         if self.grad_hook is not None:

@@ -54,6 +54,32 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// Programmatic dependent launch.  Every hot kernel starts with pdl_trigger() (its successor may be scheduled as soon
+// as all CTAs of this grid have started), runs its prologue (barrier init, TMEM allocation, descriptor prefetch,
+// index arithmetic -- nothing that touches global memory another kernel produces or consumes) and then pdl_wait(),
+// which returns once every prerequisite grid has completed and its writes are visible.  In a stream (or a captured
+// graph) of such launches the prologue / launch latency of kernel i+1 overlaps the tail of kernel i.
+// ASF_PDL=0 in the environment launches without the attribute (both instructions are then no-ops).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // 16-byte vector path: bf16 rows of C % 8 == 0 channels whose pitch and base keep every 8-channel group aligned
 static inline bool al16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 static inline bool ld8(int64_t ld) { return (ld & 7) == 0; }

@@ -2,6 +2,7 @@
 // All kernels are HBM-bound streaming passes: channel index is the fastest-varying thread index so every
 // warp touches contiguous addresses; reductions go warp/block-level first and finish with a few fp32 atomics.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -11,6 +12,14 @@ static thread_local char g_err[512] = "";
 static long long g_launches = 0;
 
 void count_launch() { __atomic_add_fetch(&g_launches, 1, __ATOMIC_RELAXED); }
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("ASF_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -487,23 +496,48 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const asf_sgd_desc_t* __
   }
 }
 
-// one thread per (o, c): reads of every split / tap are contiguous over c, the `taps` results of a thread are adjacent
-// in the OIHW master layout.
-__global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int I, int taps,
-                                    const float* __restrict__ rscale, int accumulate, int ksplit) {
-  const int64_t pairs = (int64_t)O * I, total = pairs * taps;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % I);
-    const int o = (int)(i / I);
-    const float sc = rscale ? rscale[o] : 1.f;
-    for (int tp = 0; tp < taps; ++tp) {
-      const float* src = dwp + ((int64_t)o * taps + tp) * I + c;
-      float v = 0.f;
-      for (int k = 0; k < ksplit; ++k) v += src[(int64_t)k * total];  // split-K partial tiles, fixed order
-      v *= sc;
-      if (accumulate) v += dw[i * taps + tp];
-      dw[i * taps + tp] = v;
+// Split-K reduction + re-layout.  dwp is [ksplit][E] with E = O*taps*I elements in (o, tap, c) order.  A block owns
+// 256 / SL consecutive elements; SL "split lanes" share the ksplit partial tiles of an element (lane j adds tiles
+// j, j + SL, ... in ascending order, four loads in flight), then the lanes are folded in shared memory in a fixed
+// order -- bit-reproducible, and narrow layers with a deep split (8 x 8 x 3 weights, 148 partial tiles) no longer
+// serialise hundreds of dependent loads in 64 threads.
+__global__ void __launch_bounds__(256) unpack_wgrad_kernel(const float* __restrict__ dwp, float* __restrict__ dw,
+                                                           int O, int I, int taps, const float* __restrict__ rscale,
+                                                           int accumulate, int ksplit, int sl_log2) {
+  __shared__ float part[256];
+  pdl_trigger();
+  const int SL = 1 << sl_log2, EL = 256 >> sl_log2;
+  const int el = threadIdx.x & (EL - 1), sl = threadIdx.x >> (8 - sl_log2);
+  const int64_t E = (int64_t)O * taps * I;
+  const int64_t e = (int64_t)blockIdx.x * EL + el;
+  pdl_wait();
+  float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+  if (e < E) {
+    const float* src = dwp + e;
+    int k = sl;
+    for (; k + 3 * SL < ksplit; k += 4 * SL) {
+      v0 += src[(int64_t)k * E];
+      v1 += src[(int64_t)(k + SL) * E];
+      v2 += src[(int64_t)(k + 2 * SL) * E];
+      v3 += src[(int64_t)(k + 3 * SL) * E];
     }
+    for (; k < ksplit; k += SL) v0 += src[(int64_t)k * E];
+  }
+  float v = (v0 + v1) + (v2 + v3);
+  if (SL > 1) {
+    part[threadIdx.x] = v;
+    __syncthreads();
+    if (sl == 0)
+      for (int j = 1; j < SL; ++j) v += part[j * EL + el];
+  }
+  if (sl == 0 && e < E) {
+    const int c = (int)(e % I);
+    const int64_t ot = e / I;
+    const int tp = (int)(ot % taps), o = (int)(ot / taps);
+    if (rscale) v *= rscale[o];
+    const int64_t d = ((int64_t)o * I + c) * taps + tp;
+    if (accumulate) v += dw[d];
+    dw[d] = v;
   }
 }
 
@@ -842,8 +876,10 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
                      int accumulate, int ksplit, void* stream) {
   ASF_CHECK_ARG(dwp && dw_oihw && O > 0 && I > 0 && taps > 0 && ksplit >= 1, "asf_unpack_wgrad: bad arguments");
-  unpack_wgrad_kernel<<<ew_grid((int64_t)O * I), 256, 0, (cudaStream_t)stream>>>(dwp, dw_oihw, O, I, taps,
-                                                                                      rscale, accumulate, ksplit);
+  const int sl_log2 = ksplit < 4 ? 0 : (ksplit < 32 ? 2 : 4);
+  const int64_t E = (int64_t)O * I * taps;
+  ASF_CUDA(launch_pdl(unpack_wgrad_kernel, dim3((unsigned)cdiv(E, 256 >> sl_log2)), dim3(256), 0, (cudaStream_t)stream,
+                      dwp, dw_oihw, O, I, taps, rscale, accumulate, ksplit, sl_log2));
   ASF_LAUNCH_CHECK();
   return 0;
 }

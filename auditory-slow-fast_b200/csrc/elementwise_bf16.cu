@@ -85,6 +85,8 @@ __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict
                                                           float* running_mean, float* running_var,
                                                           long long* num_batches_tracked, float* save_mean,
                                                           float* save_invstd) {
+  pdl_trigger();
+  pdl_wait();
   const int RP = 256 / CVB;
   const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
   const int c = (blockIdx.y * CVB + cvl) * 8;
@@ -175,9 +177,9 @@ __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict
 int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
                 int C, const float* scale, const float* shift, int relu, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 4);
-  bn_apply_v8_kernel<false><<<g.grid, 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
+  ASF_CUDA(launch_pdl(bn_apply_v8_kernel<false>, dim3(g.grid), dim3(256), 0, st, x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
                                                    (float*)scale, (float*)shift, relu, nullptr, 1.0, nullptr, nullptr,
-                                                   0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr);
+                                                   0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -187,10 +189,10 @@ int bn_train_fwd_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked, float* scale,
                     float* shift, float* save_mean, float* save_invstd, int relu, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 4);
-  bn_apply_v8_kernel<true><<<g.grid, 256, 0, st>>>(x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
+  ASF_CUDA(launch_pdl(bn_apply_v8_kernel<true>, dim3(g.grid), dim3(256), 0, st, x, ld_x, res, ld_res, y, ld_y, rows, C, g.CVB, g.rows_per_block,
                                                   scale, shift, relu, stats, count, gamma, beta, eps, momentum,
                                                   running_mean, running_var, (long long*)num_batches_tracked, save_mean,
-                                                  save_invstd);
+                                                  save_invstd));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -206,6 +208,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __rest
                                                               const float* __restrict__ invstd,
                                                               const float* __restrict__ red, float inv_count,
                                                               float* dgamma, float* dbeta, int accumulate) {
+  pdl_trigger();
+  pdl_wait();
   const int RP = 256 / CVB;
   const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
   const int c = (blockIdx.y * CVB + cvl) * 8;
@@ -261,8 +265,8 @@ int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, 
                     int C, const float* gamma, const float* mean, const float* invstd, const float* red,
                     float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 4);
-  bn_bwd_apply_v8_kernel<<<g.grid, 256, 0, st>>>(dz, ld_dz, x, ld_x, dx, ld_dx, rows, C, g.CVB, g.rows_per_block, gamma,
-                                                mean, invstd, red, inv_count, dgamma, dbeta, accumulate);
+  ASF_CUDA(launch_pdl(bn_bwd_apply_v8_kernel, dim3(g.grid), dim3(256), 0, st, dz, ld_dz, x, ld_x, dx, ld_dx, rows, C, g.CVB, g.rows_per_block, gamma,
+                                                mean, invstd, red, inv_count, dgamma, dbeta, accumulate));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -277,6 +281,8 @@ __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __re
                                                                 int64_t rows, int C, int CVB, int64_t rows_per_block,
                                                                 const float* __restrict__ mean,
                                                                 const float* __restrict__ invstd, float* out) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s0[2048], s1[2048];
   const int RP = 256 / CVB;
   const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
@@ -364,8 +370,8 @@ template <bool kBwd>
 int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
                       const float* invstd, float* out, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 2);
-  channel_reduce_v8_kernel<kBwd><<<g.grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, g.CVB, g.rows_per_block, mean, invstd,
-                                                        out);
+  ASF_CUDA(launch_pdl(channel_reduce_v8_kernel<kBwd>, dim3(g.grid), dim3(256), 0, st, a, ld_a, x, ld_x, rows, C, g.CVB, g.rows_per_block, mean, invstd,
+                                                        out));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -379,6 +385,8 @@ __global__ void __launch_bounds__(256) relu_bwd_v8_kernel(const bf16* __restrict
                                                           const bf16* __restrict__ b, int64_t ld_b,
                                                           const bf16* __restrict__ mask, int64_t ld_mask,
                                                           bf16* __restrict__ y, int64_t ld_y, int64_t nvec, int CV) {
+  pdl_trigger();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / CV;
     const int c = (int)(i - r * CV) * 8;
@@ -401,7 +409,7 @@ __global__ void __launch_bounds__(256) relu_bwd_v8_kernel(const bf16* __restrict
 int relu_bwd_v8(const bf16* a, int64_t ld_a, const bf16* b, int64_t ld_b, const bf16* mask, int64_t ld_mask, bf16* y,
                 int64_t ld_y, int64_t rows, int C, cudaStream_t st) {
   const int64_t nvec = rows * (C / 8);
-  relu_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(a, ld_a, b, ld_b, mask, ld_mask, y, ld_y, nvec, C / 8);
+  ASF_CUDA(launch_pdl(relu_bwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, a, ld_a, b, ld_b, mask, ld_mask, y, ld_y, nvec, C / 8));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -411,6 +419,8 @@ __global__ void __launch_bounds__(256) avgpool_bwd_v8_kernel(const float* __rest
                                                              int c_off, const bf16* __restrict__ mask,
                                                              bf16* __restrict__ dx, int64_t nvec, int P, int CV,
                                                              float inv) {
+  pdl_trigger();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / CV;
     const int c = (int)(i - r * CV) * 8;
@@ -431,7 +441,7 @@ __global__ void __launch_bounds__(256) avgpool_bwd_v8_kernel(const float* __rest
 int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* mask, bf16* dx, int B, int P, int C,
                    cudaStream_t st) {
   const int64_t nvec = (int64_t)B * P * (C / 8);
-  avgpool_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(dfeat, ld_feat, c_off, mask, dx, nvec, P, C / 8, 1.f / (float)P);
+  ASF_CUDA(launch_pdl(avgpool_bwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, dfeat, ld_feat, c_off, mask, dx, nvec, P, C / 8, 1.f / (float)P));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -442,6 +452,8 @@ __global__ void __launch_bounds__(256) bn_relu_maxpool_fwd_v8_kernel(const bf16*
                                                                      int64_t ld_y, int64_t nvec, int Tn, int F, int CV,
                                                                      int To, int Fo, const float* __restrict__ scale,
                                                                      const float* __restrict__ shift) {
+  pdl_trigger();
+  pdl_wait();
   const int C = CV * 8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % CV) * 8;
@@ -474,7 +486,7 @@ int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, i
                            const float* shift, cudaStream_t st) {
   const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
   const int64_t nvec = (int64_t)B * To * Fo * (C / 8);
-  bn_relu_maxpool_fwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, y, ld_y, nvec, T, F, C / 8, To, Fo, scale, shift);
+  ASF_CUDA(launch_pdl(bn_relu_maxpool_fwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, x, y, ld_y, nvec, T, F, C / 8, To, Fo, scale, shift));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -486,6 +498,8 @@ __global__ void __launch_bounds__(256) bn_relu_maxpool_bwd_v8_kernel(const bf16*
                                                                      int CV, int To, int Fo,
                                                                      const float* __restrict__ scale,
                                                                      const float* __restrict__ shift) {
+  pdl_trigger();
+  pdl_wait();
   const int C = CV * 8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % CV) * 8;
@@ -547,7 +561,7 @@ int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* d
                            const float* scale, const float* shift, cudaStream_t st) {
   const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
   const int64_t nvec = (int64_t)B * T * F * (C / 8);
-  bn_relu_maxpool_bwd_v8_kernel<<<vgrid(nvec), 256, 0, st>>>(x, dy, ld_dy, dz, nvec, T, F, C / 8, To, Fo, scale, shift);
+  ASF_CUDA(launch_pdl(bn_relu_maxpool_bwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, x, dy, ld_dy, dz, nvec, T, F, C / 8, To, Fo, scale, shift));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -557,6 +571,8 @@ int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* d
 // one thread = one output position x 8 output channels; the weights sit transposed in shared memory.
 __global__ void __launch_bounds__(256) stem_conv_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                                                             bf16* __restrict__ out, asf_conv_geom_t g, int64_t nvec) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float sw[];  // [taps][Cout]
   const int taps = g.kt * g.kf, CG = g.Cout / 8;
   for (int i = threadIdx.x; i < taps * g.Cout; i += blockDim.x) {
@@ -595,7 +611,7 @@ __global__ void __launch_bounds__(256) stem_conv_fwd_kernel(const float* __restr
 int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st) {
   const int64_t nvec = (int64_t)g->B * g->Tout * g->Fout * (g->Cout / 8);
   const size_t smem = sizeof(float) * (size_t)g->kt * g->kf * g->Cout;
-  stem_conv_fwd_kernel<<<vgrid(nvec), 256, smem, st>>>(in, w, out, *g, nvec);
+  ASF_CUDA(launch_pdl(stem_conv_fwd_kernel, dim3(vgrid(nvec)), dim3(256), smem, st, in, w, out, *g, nvec));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -607,6 +623,8 @@ constexpr int STEM_KF_MAX = 8;
 __global__ void __launch_bounds__(256) stem_wgrad_v8_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
                                                             float* __restrict__ dw, asf_conv_geom_t g,
                                                             int64_t rows_per_block) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float sacc[];  // [Cout][taps]
   const int taps = g.kt * g.kf, CG = g.Cout / 8;
   const int ngroups = CG * g.kt;
@@ -663,7 +681,7 @@ int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_g
   if (rpb < RL * 8) rpb = RL * 8;
   blocks = cdiv(rows, rpb);
   const size_t smem = sizeof(float) * (size_t)g->Cout * g->kt * g->kf;
-  stem_wgrad_v8_kernel<<<(unsigned)blocks, 256, smem, st>>>(in, dout, dw, *g, rpb);
+  ASF_CUDA(launch_pdl(stem_wgrad_v8_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dw, *g, rpb));
   ASF_LAUNCH_CHECK();
   return 0;
 }

@@ -122,6 +122,7 @@ __device__ __forceinline__ void epi_slab_stats(const uint8_t* slab, int t, float
 template <bool STATS>
 __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const __grid_constant__ TgParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  pdl_trigger();
   uint8_t* smem = smem_raw;  // 1024-byte aligned (128B-swizzle atoms); checked below
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int b_bytes = p.block_n * 128;
@@ -163,6 +164,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
+  pdl_wait();  // everything above touched only shared memory, TMEM and kernel parameters
 
   if (warp == 0 || warp == 10) {
     // ===== TMA producers: warp 0 streams the activation boxes, warp 10 the weight boxes.  One thread issuing both

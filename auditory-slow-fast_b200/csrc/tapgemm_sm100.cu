@@ -620,6 +620,12 @@ static int num_sms() {
   }
   return n;
 }
+// SMs this launch may occupy: the engine runs the slow and the fast pathway on two streams and gives each a share of
+// the SMs (asf_tapgemm_t::max_ctas), so that their persistent CTAs run side by side instead of queueing.
+static int sm_budget(const asf_tapgemm_t* q) {
+  const int n = num_sms();
+  return (q->max_ctas > 0 && q->max_ctas < n) ? q->max_ctas : n;
+}
 
 // ---- optional per-launch timing (bench.py's roofline leg): cudaEvent pairs around every tap-GEMM launch
 struct ProfRec {
@@ -696,7 +702,7 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: wgrad stage does not fit twice in shared memory");
   w->stages = stages;
   const int64_t base_tiles = (int64_t)w->r_tiles * w->c_tiles * q->ntaps;
-  int ks = (int)cdiv(num_sms(), base_tiles);
+  int ks = (int)cdiv(sm_budget(q), base_tiles);
   if (ks > w->m_tiles / 4) ks = w->m_tiles / 4;  // at least four 64-row stages of MMA work per partial tile
   if (ks < 1) ks = 1;
   w->ksplit = ks;
@@ -778,11 +784,11 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       if (use_tma) {
         // N = 256 per MMA keeps the single issuing thread ahead of the tensor pipe; halve only when that at least
         // doubles the number of busy SMs, or when the operand slabs leave fewer than 3 ring stages
-        while (bn > 64 && bn % 32 == 0 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) * 2 <= num_sms()) bn /= 2;
+        while (bn > 64 && bn % 32 == 0 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) * 2 <= sm_budget(q)) bn /= 2;
         while (bn > 64 && bn % 32 == 0 && (smem_cap - tma_fixed) / (TG_A_BYTES + bn * 128) < 3) bn /= 2;
       } else {
         // keep at least ~1 wave of tiles on the chip when M is small
-        while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < num_sms() && bn % 32 == 0) bn /= 2;
+        while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < sm_budget(q) && bn % 32 == 0) bn /= 2;
       }
     }
     ASF_CHECK_ARG(bn >= 16 && bn <= 256 && bn % 16 == 0, "asf_tapgemm: block_n %d must be a multiple of 16 in [16,256]", bn);
@@ -804,7 +810,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     for (int j = 0; j < 3; ++j) p.o_stride[j] = q->o_stride[j];
     p.epi = q->epi;
     int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
-    int grid = (int)(total < num_sms() ? total : num_sms());
+    int grid = (int)(total < sm_budget(q) ? total : sm_budget(q));
     const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
     if (use_tma) {
       stages = (smem_cap - tma_fixed) / stage_bytes;
@@ -866,9 +872,9 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
         pr->block_n = bn; pr->grid = grid;
       }
       if (si)
-        tapgemm_fwd_tma_kernel<true><<<grid, TGT_THREADS, smem_t, st>>>(p);
+        ASF_CUDA(launch_pdl(tapgemm_fwd_tma_kernel<true>, dim3(grid), dim3(TGT_THREADS), smem_t, st, p));
       else
-        tapgemm_fwd_tma_kernel<false><<<grid, TGT_THREADS, smem_t, st>>>(p);
+        ASF_CUDA(launch_pdl(tapgemm_fwd_tma_kernel<false>, dim3(grid), dim3(TGT_THREADS), smem_t, st, p));
       prof_end(pr, st);
       ASF_LAUNCH_CHECK();
       return debug_sync(st);
@@ -947,7 +953,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
     pr->block_n = ks; pr->grid = (int)grid;
   }
-  tapgemm_wgrad2_kernel<<<(unsigned)grid, WG2_THREADS, smem, st>>>(p);
+  ASF_CUDA(launch_pdl(tapgemm_wgrad2_kernel, dim3((unsigned)grid), dim3(WG2_THREADS), smem, st, p));
   prof_end(pr, st);
   ASF_LAUNCH_CHECK();
   return debug_sync(st);

@@ -18,6 +18,7 @@ constexpr int WG2_THREADS = 320;                // warp 0 TMA, warp 1 MMA, warps
 
 __global__ void __launch_bounds__(WG2_THREADS, 1) tapgemm_wgrad2_kernel(const __grid_constant__ TgParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  pdl_trigger();
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int ny = p.wg_ny, nx = p.wg_nx;
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(WG2_THREADS, 1) tapgemm_wgrad2_kernel(const __
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
+  pdl_wait();  // everything above touched only shared memory, TMEM and kernel parameters
 
   if (warp != 1 && lane == 0) {
     // ===== TMA issue, spread over nine threads: a thread spends ~250 issue cycles per cp.async.bulk.tensor, and a

@@ -170,6 +170,7 @@ typedef struct {
   float* dwp;         /* fp32 [ksplit][N][ntaps_w][K] workspace, written */
   int32_t ksplit;
   int32_t block_n;    /* 0 = choose */
+  int32_t max_ctas;   /* 0 = all SMs; otherwise the launch sizes its persistent grid / split-K for this many SMs */
 } asf_tapgemm_t;
 
 int asf_tapgemm(const asf_tapgemm_t* p, int mode, void* stream);

@@ -28,8 +28,12 @@ class Harness(Engine):
         self.use_tc = dtype == torch.bfloat16
         self.force_simt = force_simt
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self._ws = None
+        self._ws = {}
         self.grad_hook = None
+        self.plan = None
+        self.two_stream = False
+        self.sm_split = (0, 0)
+        self._side = None
 
 
 def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, in_scale=1.0):
