@@ -98,10 +98,15 @@ SIGNATURES = {
     "asf_prof_record": [_I, _P],
     "asf_logmel_tables": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "asf_logmel_fwd": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _I, _P, _I, _P],
+    "asf_logmel_tc_supported": [_I, _I, _I],
+    "asf_logmel_tc_btab_floats": [_I],
+    "asf_logmel_tc_tables": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
+    "asf_logmel_fwd_tc": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _P, _I, _P],
     "asf_conv_fwd_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
     "asf_conv_dgrad_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
     "asf_conv_wgrad_simt": [_P, _I, _P, _I, _P, C.POINTER(ConvGeom), _P, _I, _P],
     "asf_tapgemm": [C.POINTER(TapGemm), _I, _P],
+    "asf_tapgemm_probe": [_P],
     "asf_pack_weight": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weight_t": [_P, _P, _I, _I, _I, _I, _P, _P],
     "asf_pack_weights_multi": [_P, _I, C.c_longlong, _P],

@@ -11,6 +11,7 @@ DataLoader workers; here the loader hands over raw waveforms and extraction is o
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -45,9 +46,26 @@ def _tables(device, sr, n_fft, win, n_mels):
     return t
 
 
-def logmel_cuda(waveforms, sr=24000, n_fft=2048, win=240, hop=120, n_mels=128, eps=1e-6, num_frames=None):
+def _tc_tables(device, sr, n_fft, win, hop, n_mels):
+    """Tables of the tensor-core kernel (pre-split TF32 basis image, per-bin mel pair); None when the mel layout
+    cannot be expressed as adjacent filter pairs (then the CUDA-core kernel runs)."""
+    key = ("tc", device.index, sr, n_fft, win, hop, n_mels)
+    if key not in _TABLES:
+        nbp = (n_fft // 2 + 1 + 103) // 104 * 104
+        btab = torch.zeros(L.lib().asf_logmel_tc_btab_floats(n_fft), dtype=torch.float32, device=device)
+        melw = torch.zeros((nbp, 2), dtype=torch.float32, device=device)
+        melj = torch.zeros(nbp, dtype=torch.int32, device=device)
+        rc = L.lib().asf_logmel_tc_tables(L.ptr(btab), L.ptr(melw), L.ptr(melj), sr, n_fft, win, hop, n_mels,
+                                          L.stream_ptr())
+        _TABLES[key] = (btab, melw, melj) if rc == 0 else None
+    return _TABLES[key]
+
+
+def logmel_cuda(waveforms, sr=24000, n_fft=2048, win=240, hop=120, n_mels=128, eps=1e-6, num_frames=None, impl=None):
     """waveforms: CUDA float32 [B, N] -> CUDA float32 [B, 1, T, n_mels] with T = max(1 + N//hop, num_frames)
-    (rows past the last frame replicate it, as np.pad(..., "edge") does in the reference)."""
+    (rows past the last frame replicate it, as np.pad(..., "edge") does in the reference).
+    ``impl``: None = the tcgen05 kernel when the configuration allows it (win = 240, hop = 120: every shipped
+    config), else the CUDA-core kernel; "simt" / "tc" force one of them."""
     L.require_cuda_sm100()
     if waveforms.dim() != 2 or waveforms.dtype != torch.float32 or not waveforms.is_cuda:
         raise ValueError("logmel_cuda expects a CUDA float32 tensor of shape [B, N]")
@@ -56,8 +74,20 @@ def logmel_cuda(waveforms, sr=24000, n_fft=2048, win=240, hop=120, n_mels=128, e
     B, N = waveforms.shape
     T = 1 + N // hop
     T_out = max(T, num_frames or 0)
-    basis, melT, rng, nbp = _tables(waveforms.device, sr, n_fft, win, n_mels)
     out = torch.empty((B, 1, T_out, n_mels), dtype=torch.float32, device=waveforms.device)
+    if impl is None:
+        impl = os.environ.get("ASF_LOGMEL_IMPL") or None
+    tc = None
+    if impl != "simt" and L.lib().asf_logmel_tc_supported(n_fft, win, hop):
+        tc = _tc_tables(waveforms.device, sr, n_fft, win, hop, n_mels)
+    if impl == "tc" and tc is None:
+        raise RuntimeError("logmel_cuda: the tensor-core kernel does not support n_fft=%d win=%d hop=%d n_mels=%d"
+                           % (n_fft, win, hop, n_mels))
+    if tc is not None:
+        L.call("asf_logmel_fwd_tc", L.ptr(waveforms), waveforms.stride(0), B, N, n_fft, win, hop, n_mels,
+               C.c_float(eps), L.ptr(tc[0]), L.ptr(tc[1]), L.ptr(tc[2]), L.ptr(out), T_out, L.stream_ptr())
+        return out
+    basis, melT, rng, nbp = _tables(waveforms.device, sr, n_fft, win, n_mels)
     L.call("asf_logmel_fwd", L.ptr(waveforms), waveforms.stride(0), B, N, n_fft, win, hop, n_mels, C.c_float(eps),
            L.ptr(basis), L.ptr(melT), L.ptr(rng), nbp, L.ptr(out), T_out, L.stream_ptr())
     return out

@@ -237,6 +237,8 @@ class Engine:
         split = os.environ.get("ASF_SM_SPLIT", "0,0").split(",")  # 0 = no cap: CTAs of both streams share all SMs
         self.sm_split = (int(split[0]), int(split[1]))
         self._side = None
+        self._wg = [None, None]  # weight-gradient streams (one per pathway), off the dz -> dgrad critical chain
+        self.wgrad_streams = os.environ.get("ASF_WGRAD_STREAMS", "1") != "0"
 
     # ------------------------------------------------------------------------------------------ plan
     def invalidate_weights(self):
@@ -473,8 +475,14 @@ class Engine:
 
     def _side_stream(self):
         if self._side is None:
-            self._side = torch.cuda.Stream(device=self.device)
+            self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_SIDE_PRIO", "0")))
         return self._side
+
+    def _wg_stream(self, path):
+        if self._wg[path] is None:
+            # lower priority than the pathway streams: dgrad / BN backward feed the next layer, wgrad feeds nobody
+            self._wg[path] = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_WG_PRIO", "0")))
+        return self._wg[path]
 
     def _on(self, path):
         """Context that issues work of pathway ``path`` on its stream (fast pathway -> side stream)."""
@@ -633,8 +641,11 @@ class Engine:
     def _wgrad_ws(self, nfloats):
         """Split-K workspace of the tcgen05 wgrad ([ksplit][Cout][taps][Cin] fp32 partial tiles, written then summed
         by asf_unpack_wgrad on the same stream): one grow-only buffer per stream, shared by the layers issued on it."""
-        side = self._side is not None and torch.cuda.current_stream(self.device) == self._side
-        key = 1 if side else 0  # one workspace per issuing stream (main / fast-pathway side stream)
+        cur = torch.cuda.current_stream(self.device)  # one workspace per issuing stream
+        key = 0
+        for i, s_ in enumerate((self._side, self._wg[0], self._wg[1])):
+            if s_ is not None and cur == s_:
+                key = i + 1
         ws = self._ws.get(key)
         if ws is None or ws.numel() < nfloats:
             ws = self._ws[key] = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=self.device)
@@ -817,7 +828,16 @@ class Engine:
                     "(use freeze_fn('bn_parameters') together with freeze_fn('bn_statistics'))" % u.name)
         gview, acc = self._grad_target(conv.weight)
         if gview is not None:
-            self._conv_wgrad(u, dconv, rscale, gview, acc)
+            if self._ts() and self.wgrad_streams and not u.is_stem:
+                # dW needs dconv and the saved input only; nothing downstream in this pass reads it
+                wg = self._wg_stream(u.path)
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+                wg.wait_event(ev)
+                with torch.cuda.stream(wg):
+                    self._conv_wgrad(u, dconv, rscale, gview, acc)
+            else:
+                self._conv_wgrad(u, dconv, rscale, gview, acc)
         if need_dx:
             self._conv_dgrad(u, dconv, u.x.grad, dx_accumulate, res=dx_res, mask=dx_mask)
 
@@ -890,7 +910,7 @@ class Engine:
                     # the lateral is always the LAST writer of its (fast) input's gradient: it applies the ReLU mask
                     self._unit_backward(u, u.y.grad, True, not fresh, dx_mask=u.x)
                     # on the side stream, after the wait above, everything issued so far on either stream is ordered
-                    self._notify(pending + [u.name])
+                    self._notify_joined(pending + [u.name])
                     pending = []
             else:
                 blk = item
@@ -934,7 +954,29 @@ class Engine:
                 self._unit_backward(u, dz, False, False)
         if ts:
             main.wait_stream(side)  # join
+            for wg in self._wg:
+                if wg is not None:
+                    main.wait_stream(wg)
         self._notify(pending + ["stems"])
+
+    def _notify_joined(self, names):
+        """Two-stream mode: gradient-ready notification issued where the current (side) stream is ordered after
+        everything both pathway streams have been given so far.  The weight gradients live on the wgrad streams, so
+        the hook runs on one of those after it has been ordered behind the other and behind the current stream --
+        nothing on the dz -> dgrad chain waits."""
+        if self.grad_hook is None:
+            return
+        cur = torch.cuda.current_stream(self.device)
+        if not self.wgrad_streams:
+            self.grad_hook(self, names)
+            return
+        j = self._wg_stream(1)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        j.wait_event(ev)
+        j.wait_stream(self._wg_stream(0))
+        with torch.cuda.stream(j):
+            self.grad_hook(self, names)
 
     def _notify(self, names):
         if self.grad_hook is not None:

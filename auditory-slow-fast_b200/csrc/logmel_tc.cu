@@ -1,0 +1,430 @@
+// Log-mel extraction on the tensor cores (tcgen05 / TMEM), the shipped configuration of the reference:
+// 24 kHz, n_fft 2048, 10 ms Hann window (240 samples), 5 ms hop (120 samples), 128 HTK mel bands
+//   /root/reference/audio_slowfast/datasets/audio_loader_epic.py:66-97 (+ edge padding :151-154).
+//
+// The STFT of a frame is a dense contraction of its 240 non-zero windowed samples with a [240 x 2*1025] basis.
+// Because win = 2*hop, frame t is the concatenation of two consecutive 120-sample "chunk rows" of the clip, so
+//
+//     DFT[frame t] = chunk_row[t] . B_top  +  chunk_row[t+1] . B_bot            (K = 120 each)
+//
+// and ONE staged copy of 129 chunk rows serves both halves of 128 frames: the A operand is kept in the canonical
+// no-swizzle K-major layout with 8-row groups packed back to back (SBO = 128 B), which makes a row a 16-byte pitch
+// and "the same matrix shifted by one row" simply the descriptor start address + 16.
+//
+// fp32 accuracy (log-mel within 1e-4 of the reference, bins 80 dB below the peak included) on TF32 tensor cores
+// comes from the 3-term split  a.b ~= a_hi.b_hi + a_lo.b_hi + a_hi.b_lo  (hi = round-to-nearest TF32, lo = TF32 of
+// the remainder): three kind::tf32 MMAs per K = 8 step accumulate into the same fp32 TMEM accumulator.
+//
+// One CTA per SM, persistent over tiles of 128 frame rows of the flattened (clip, frame) space:
+//   warp 0      streams the basis (pre-split, pre-arranged as the shared-memory image) with cp.async.bulk
+//   warp 1      issues tcgen05.mma: per tile 10 bin chunks x 2 halves x 5 slabs x 3 K-steps x 3 split terms
+//   warps 2-5   drain TMEM (double-buffered 208-column accumulators = re | im of 104 bins): magnitude, then the
+//               HTK mel filterbank as a running two-filter accumulation (a bin touches the descending side of
+//               filter j-1 and the ascending side of filter j), log, store -- one thread per frame
+//   warps 6-9   stage the next tile's chunk rows: coalesced loads, hi/lo split, conflict-free smem stores
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace asf {
+
+constexpr int LT_HOP = 120;
+constexpr int LT_K4H = LT_HOP / 4;         // 16-byte K groups per half
+constexpr int LT_NBC = 104;                // bins per chunk
+constexpr int LT_NCOL = 2 * LT_NBC;        // accumulator columns: re | im
+constexpr int LT_KS = 24;                  // K floats per pipeline slab (3 MMA K-steps)
+constexpr int LT_SLABS = LT_HOP / LT_KS;   // 5 per half
+constexpr int LT_NR = 137;                 // padded row count of the A image (row pitch 16 B, K-group pitch 137*16)
+constexpr int LT_A_LBO = LT_NR * 16;       // 2192 B between K groups: 548 words = 4 (mod 32) -> conflict-free staging
+constexpr int LT_A_BYTES = LT_K4H * LT_A_LBO;          // 65,760
+constexpr int LT_A_STRIDE = 65792;                     // hi / lo images, 128-byte aligned
+constexpr int LT_B_LBO = LT_NCOL * 16;                 // 3328
+constexpr int LT_B_HALF = (LT_KS / 4) * LT_B_LBO;      // 19,968: hi (or lo) part of a stage
+constexpr int LT_B_STAGE = 2 * LT_B_HALF;              // 39,936
+constexpr int LT_STAGES = 2;
+constexpr int LT_MAX_BINS = 1040;                      // 10 chunks (n_fft <= 2048)
+constexpr int LT_OFF_B = 2 * LT_A_STRIDE;
+constexpr int LT_OFF_W = LT_OFF_B + LT_STAGES * LT_B_STAGE;
+constexpr int LT_OFF_J = LT_OFF_W + LT_MAX_BINS * 8;
+constexpr int LT_OFF_BAR = LT_OFF_J + LT_MAX_BINS * 4;
+constexpr int LT_SMEM = LT_OFF_BAR + 16 * 8;
+constexpr int LT_THREADS = 320;
+static_assert(LT_A_BYTES <= LT_A_STRIDE && LT_SMEM <= 227 * 1024, "log-mel tile does not fit in shared memory");
+
+struct LtBars {
+  uint64_t b_full[LT_STAGES], b_empty[LT_STAGES];
+  uint64_t a_full, a_free;
+  uint64_t tmem_full[2], tmem_empty[2];
+  uint32_t tmem_base;
+};
+static_assert(sizeof(LtBars) <= 16 * 8, "barrier block");
+
+// no-swizzle K-major operand: core matrices (8 rows x 16 B) LBO bytes apart along K, SBO bytes apart along M/N
+__device__ __forceinline__ uint64_t lt_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"((uint64_t)src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void lt_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t tf32_rna(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return u;
+}
+
+__global__ void __launch_bounds__(LT_THREADS, 1)
+logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_samples, int T_valid, int T_out,
+                 int n_chunks, int n_mels, float eps, const float* __restrict__ btab,
+                 const float2* __restrict__ melw, const int* __restrict__ melj, float* __restrict__ out,
+                 long long total_rows, int n_tiles) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  pdl_trigger();
+  LtBars* bars = (LtBars*)(smem + LT_OFF_BAR);
+  float2* sw = (float2*)(smem + LT_OFF_W);
+  int* sj = (int*)(smem + LT_OFF_J);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int RP = T_valid + 1;  // chunk rows (= frame rows, the last one unused) per clip
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < LT_STAGES; ++s) {
+      mbar_init(&bars->b_full[s], 1);
+      mbar_init(&bars->b_empty[s], 1);
+    }
+    mbar_init(&bars->a_full, 128);
+    mbar_init(&bars->a_free, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->tmem_full[i], 1);
+      mbar_init(&bars->tmem_empty[i], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
+  for (int i = threadIdx.x; i < n_chunks * LT_NBC; i += LT_THREADS) {  // constant tables (never written by a kernel)
+    sw[i] = melw[i];
+    sj[i] = melj[i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===== basis producer =====
+    if (lane == 0) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint8_t* src = (const uint8_t*)btab;
+        for (int i = 0; i < n_chunks * 2 * LT_SLABS; ++i) {
+          mbar_wait(&bars->b_empty[st], ph ^ 1, 21);
+          mbar_expect_tx(&bars->b_full[st], LT_B_STAGE);
+          bulk_g2s(smem + LT_OFF_B + st * LT_B_STAGE, src, LT_B_STAGE, &bars->b_full[st]);
+          src += LT_B_STAGE;
+          if (++st == LT_STAGES) { st = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(LT_NCOL >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      const uint32_t s0 = smem_u32(smem);
+      const uint64_t a_hi0 = lt_desc(s0, LT_A_LBO, 128), a_lo0 = lt_desc(s0 + LT_A_STRIDE, LT_A_LBO, 128);
+      const uint64_t b0 = lt_desc(s0 + LT_OFF_B, LT_B_LBO, 128);
+      int st = 0;
+      uint32_t ph = 0;
+      uint32_t g = 0;  // accumulator use counter
+      int it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        mbar_wait(&bars->a_full, (uint32_t)(it & 1), 22);
+        tc_fence_after();
+        for (int c = 0; c < n_chunks; ++c, ++g) {
+          const uint32_t buf = g & 1;
+          mbar_wait(&bars->tmem_empty[buf], ((g >> 1) & 1) ^ 1, 23);
+          tc_fence_after();
+          const uint32_t d = tmem_base + buf * 256;
+          uint32_t acc = 0;
+          for (int h = 0; h < 2; ++h) {
+            for (int s = 0; s < LT_SLABS; ++s) {
+              mbar_wait(&bars->b_full[st], ph, 24);
+              tc_fence_after();
+              const uint64_t bh = b0 + (uint64_t)((st * LT_B_STAGE) >> 4), bl = bh + (uint64_t)(LT_B_HALF >> 4);
+#pragma unroll
+              for (int j = 0; j < LT_KS / 8; ++j) {
+                const uint64_t ao = (uint64_t)((((s * (LT_KS / 4) + 2 * j) * LT_A_LBO) + h * 16) >> 4);
+                const uint64_t bo = (uint64_t)((2 * j * LT_B_LBO) >> 4);
+                umma_tf32(d, a_lo0 + ao, bh + bo, idesc, acc);
+                umma_tf32(d, a_hi0 + ao, bl + bo, idesc, 1);
+                umma_tf32(d, a_hi0 + ao, bh + bo, idesc, 1);
+                acc = 1;
+              }
+              umma_commit(&bars->b_empty[st]);
+              if (++st == LT_STAGES) { st = 0; ph ^= 1; }
+            }
+          }
+          umma_commit(&bars->tmem_full[buf]);
+        }
+        umma_commit(&bars->a_free);  // every MMA that reads this tile's chunk rows has completed
+      }
+    }
+  } else if (warp < 6) {
+    // ===== epilogue: one thread per frame =====
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    uint32_t g = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const long long R = (long long)tile * 128 + r;
+      const int b = (int)(R / RP), t = (int)(R - (long long)b * RP);
+      const bool valid = R < total_rows && t < T_valid;
+      float* orow = out + ((long long)b * T_out + t) * n_mels;
+      const int n_rep = (valid && t == T_valid - 1) ? (T_out - T_valid) : 0;  // np.pad(..., "edge") rows
+      float cur = 0.f, nxt = 0.f;
+      int j_cur = 0;
+      auto emit = [&](int m, float v) {
+        if (valid && m >= 0 && m < n_mels) {
+          const float l = logf(v + eps);
+          orow[m] = l;
+          for (int q = 1; q <= n_rep; ++q) orow[(long long)q * n_mels + m] = l;
+        }
+      };
+      for (int c = 0; c < n_chunks; ++c, ++g) {
+        const uint32_t buf = g & 1;
+        mbar_wait(&bars->tmem_full[buf], (g >> 1) & 1, 25);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256;
+#pragma unroll 1
+        for (int j0 = 0; j0 < LT_NBC; j0 += 8) {
+          uint32_t re[8], im[8];
+          tmem_ld8_issue(taddr + (uint32_t)j0, re);
+          tmem_ld8_issue(taddr + (uint32_t)(LT_NBC + j0), im);
+          lt_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const int k = c * LT_NBC + j0 + q;
+            const float x = __uint_as_float(re[q]), y = __uint_as_float(im[q]);
+            const float mag = sqrtf(fmaf(x, x, y * y));
+            const int jk = sj[k];
+            while (j_cur < jk) {  // uniform across the CTA: filter j_cur - 1 is complete
+              emit(j_cur - 1, cur);
+              cur = nxt;
+              nxt = 0.f;
+              ++j_cur;
+            }
+            const float2 w = sw[k];
+            cur = fmaf(w.x, mag, cur);
+            nxt = fmaf(w.y, mag, nxt);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+      }
+      while (j_cur <= n_mels) {
+        emit(j_cur - 1, cur);
+        cur = nxt;
+        nxt = 0.f;
+        ++j_cur;
+      }
+    }
+  } else {
+    // ===== chunk-row stager (128 threads) =====
+    const int sidx = (int)threadIdx.x - 192;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      mbar_wait(&bars->a_free, (uint32_t)((it & 1) ^ 1), 26);
+      const long long R0 = (long long)tile * 128;
+      constexpr int TOT = 129 * LT_HOP;
+#pragma unroll 1
+      for (int e0 = sidx; e0 < TOT; e0 += 4 * 128) {
+        float x[4];
+        int off[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int e = e0 + u * 128;
+          x[u] = 0.f;
+          off[u] = -1;
+          if (e < TOT) {
+            const int rr = e / LT_HOP, k = e - rr * LT_HOP;
+            const long long R = R0 + rr;
+            const int b = (int)(R / RP), t = (int)(R - (long long)b * RP);
+            const int s = (t - 1) * LT_HOP + k;
+            if (R < total_rows && t >= 1 && s < n_samples) x[u] = wave[(long long)b * wave_ld + s];
+            off[u] = (k >> 2) * LT_A_LBO + rr * 16 + (k & 3) * 4;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (off[u] >= 0) {
+            const uint32_t hi = tf32_rna(x[u]);
+            const uint32_t lo = tf32_rna(x[u] - __uint_as_float(hi));
+            *(uint32_t*)(smem + off[u]) = hi;
+            *(uint32_t*)(smem + LT_A_STRIDE + off[u]) = lo;
+          }
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(&bars->a_full);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+static inline float host_tf32_rna(float x) {
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  u = (u + 0x1000u) & 0xFFFFE000u;
+  float r;
+  memcpy(&r, &u, 4);
+  return r;
+}
+
+}  // namespace asf
+
+using namespace asf;
+
+extern "C" {
+
+int asf_logmel_tc_supported(int n_fft, int win, int hop) {
+  return (win == 2 * LT_HOP && hop == LT_HOP && n_fft >= win && (n_fft / 2 + 1 + LT_NBC - 1) / LT_NBC * LT_NBC <= LT_MAX_BINS)
+             ? 1 : 0;
+}
+
+long long asf_logmel_tc_btab_floats(int n_fft) {
+  const int n_chunks = (n_fft / 2 + 1 + LT_NBC - 1) / LT_NBC;
+  return (long long)n_chunks * 2 * LT_SLABS * (LT_B_STAGE / 4);
+}
+
+int asf_logmel_tc_tables(float* btab, float* melw, int32_t* melj, int sr, int n_fft, int win, int hop, int n_mels,
+                         void* stream) {
+  ASF_CHECK_ARG(btab && melw && melj && sr > 0 && n_mels > 0, "asf_logmel_tc_tables: bad arguments");
+  ASF_CHECK_ARG(asf_logmel_tc_supported(n_fft, win, hop), "asf_logmel_tc_tables: only win = 240, hop = 120, n_fft <= 2048");
+  const int n_bins = n_fft / 2 + 1;
+  const int n_chunks = (n_bins + LT_NBC - 1) / LT_NBC, nbp = n_chunks * LT_NBC;
+  const int lpad = (n_fft - win) / 2;
+  const double PI = 3.14159265358979323846;
+  std::vector<float> hb((size_t)asf_logmel_tc_btab_floats(n_fft), 0.f);
+  for (int c = 0; c < n_chunks; ++c)
+    for (int h = 0; h < 2; ++h)
+      for (int s = 0; s < LT_SLABS; ++s) {
+        float* stage = hb.data() + (size_t)((c * 2 + h) * LT_SLABS + s) * (LT_B_STAGE / 4);
+        for (int kl = 0; kl < LT_KS; ++kl) {
+          const int j = h * LT_HOP + s * LT_KS + kl;  // sample inside the window
+          const double w = 0.5 - 0.5 * cos(2.0 * PI * (double)j / (double)win);  // periodic Hann
+          for (int n = 0; n < LT_NCOL; ++n) {
+            const int bin = c * LT_NBC + (n % LT_NBC);
+            float v = 0.f;
+            if (bin < n_bins) {
+              const int64_t phs = ((int64_t)bin * (lpad + j)) % n_fft;  // exact phase reduction
+              const double ang = 2.0 * PI * (double)phs / (double)n_fft;
+              v = (n < LT_NBC) ? (float)(w * cos(ang)) : (float)(-w * sin(ang));
+            }
+            const float hi = host_tf32_rna(v), lo = host_tf32_rna(v - hi);
+            const size_t idx = ((size_t)(kl >> 2) * LT_NCOL + n) * 4 + (kl & 3);
+            stage[idx] = hi;
+            stage[LT_B_HALF / 4 + idx] = lo;
+          }
+        }
+      }
+  // librosa.filters.mel(htk=True, norm=None) as a per-bin pair of adjacent filters
+  const double mel_max = 2595.0 * log10(1.0 + (0.5 * sr) / 700.0);
+  std::vector<double> mel_f(n_mels + 2);
+  for (int i = 0; i < n_mels + 2; ++i) {
+    double m = (i == n_mels + 1) ? mel_max : (mel_max / (double)(n_mels + 1)) * (double)i;
+    mel_f[i] = 700.0 * (pow(10.0, m / 2595.0) - 1.0);
+  }
+  std::vector<float> hw((size_t)nbp * 2, 0.f);
+  std::vector<int32_t> hj((size_t)nbp, 0);
+  int jprev = 0;
+  for (int k = 0; k < nbp; ++k) {
+    if (k >= n_bins) {
+      hj[k] = jprev;
+      continue;
+    }
+    const double fk = (double)k * (double)sr / (double)n_fft;
+    int j = -1;
+    for (int i = 0; i < n_mels + 2; ++i)
+      if (mel_f[i] <= fk) j = i;
+    if (j < 0) j = 0;
+    if (j > n_mels) j = n_mels;
+    if (j < jprev) j = jprev;
+    for (int m = 0; m < n_mels; ++m) {
+      const double lower = (fk - mel_f[m]) / (mel_f[m + 1] - mel_f[m]);
+      const double upper = (mel_f[m + 2] - fk) / (mel_f[m + 2] - mel_f[m + 1]);
+      double v = lower < upper ? lower : upper;
+      if (v < 0.0) v = 0.0;
+      const float vf = (float)v;
+      if (m == j - 1) hw[2 * k] = vf;
+      else if (m == j) hw[2 * k + 1] = vf;
+      else
+        ASF_CHECK_ARG(vf == 0.f, "asf_logmel_tc_tables: bin %d touches mel filter %d outside its adjacent pair (%d, %d)",
+                      k, m, j - 1, j);
+    }
+    hj[k] = j;
+    jprev = j;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  ASF_CUDA(cudaMemcpyAsync(btab, hb.data(), hb.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+  ASF_CUDA(cudaMemcpyAsync(melw, hw.data(), hw.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+  ASF_CUDA(cudaMemcpyAsync(melj, hj.data(), hj.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  ASF_CUDA(cudaStreamSynchronize(st));  // host staging vectors die at return
+  return 0;
+}
+
+int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, int n_fft, int win, int hop,
+                      int n_mels, float eps, const float* btab, const float* melw, const int32_t* melj, float* fast,
+                      int T_out, void* stream) {
+  ASF_CHECK_ARG(wave && btab && melw && melj && fast, "asf_logmel_fwd_tc: null pointer");
+  ASF_CHECK_ARG(asf_logmel_tc_supported(n_fft, win, hop), "asf_logmel_fwd_tc: only win = 240, hop = 120, n_fft <= 2048");
+  ASF_CHECK_ARG(B > 0 && n_samples >= 0 && n_mels > 0 && wave_ld >= n_samples, "asf_logmel_fwd_tc: bad sizes");
+  const int T_valid = 1 + n_samples / hop;
+  if (T_out <= 0) T_out = T_valid;
+  ASF_CHECK_ARG(T_out >= T_valid, "asf_logmel_fwd_tc: T_out (%d) smaller than the %d frames of the clip (no truncation)",
+                T_out, T_valid);
+  const int n_chunks = (n_fft / 2 + 1 + LT_NBC - 1) / LT_NBC;
+  const long long total_rows = (long long)B * (T_valid + 1);
+  const long long n_tiles = cdiv(total_rows, 128);
+  ASF_CHECK_ARG(n_tiles < (1ll << 30), "asf_logmel_fwd_tc: batch too large");
+  static bool attr_set = false;
+  if (!attr_set) {
+    ASF_CUDA(cudaFuncSetAttribute(logmel_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LT_SMEM));
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = (int)(n_tiles < sms ? n_tiles : sms);
+  ASF_CUDA(launch_pdl(logmel_tc_kernel, dim3(grid), dim3(LT_THREADS), (size_t)LT_SMEM, (cudaStream_t)stream, wave,
+                      (long long)wave_ld, n_samples, T_valid, T_out, n_chunks, n_mels, eps, btab, (const float2*)melw,
+                      (const int*)melj, fast, total_rows, (int)n_tiles));
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -165,6 +165,8 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
   pdl_wait();  // everything above touched only shared memory, TMEM and kernel parameters
+  Probe pb{p.dbg, 0}, pb_all{p.dbg, 0};
+  if (threadIdx.x == 0) pb_all.begin();
 
   if (warp == 0 || warp == 10) {
     // ===== TMA producers: warp 0 streams the activation boxes, warp 10 the weight boxes.  One thread issuing both
@@ -193,7 +195,9 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
                     c4 = b4 + p.a_off[tap][3];
           const int wt = p.b_tap[tap];
           for (int kc = 0; kc < p.kchunks; ++kc) {
+            if (act) pb.begin();
             mbar_wait(&sh->empty[s], ph ^ 1, 1);
+            if (act) pb.end(1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
             if (act) {
               mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
@@ -222,13 +226,17 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
       int it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
+        pb.begin();
         mbar_wait(&sh->tmem_empty[buf], ((it >> 1) & 1) ^ 1, 2);
+        pb.end(3);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 256);
         uint32_t acc = 0;
         int kc = 0;
         for (int ki = 0; ki < kiters; ++ki) {
+          pb.begin();
           mbar_wait(&sh->full[s], ph, 3);
+          pb.end(2);
           tc_fence_after();
           const uint64_t adesc = adesc0 + dstage * (uint64_t)s, bdesc = bdesc0 + dstage * (uint64_t)s;
           if (full4 || kc + 1 < p.kchunks) {
@@ -320,7 +328,9 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         for (int i = t; i < p.block_n; i += 128) s_shift[i] = (n0 + i < p.N) ? g_shift[n0 + i] : 0.f;
       }
       named_bar(bar_id, 128);  // s_shift visible to the group
+      if (leader) pb.begin();
       mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
+      if (leader) { pb.end(4); pb.begin(); }
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
       for (int s = 0; s < nslab; ++s, ++gs) {
@@ -331,7 +341,10 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           // operands of the following slab (possibly of the next tile) into the other buffer: its last reader was
           // slab gs-1, and every thread has passed that slab's closing barrier
           if (n_ops > 0) prefetch_next();
-          bulk_wait_read<1>();  // the store that last read out_buf[b] (two slabs ago) has drained it
+          Probe pw{p.dbg, 0};
+          pw.begin();
+          bulk_wait_read<1>();
+          pw.end(6);  // the store that last read out_buf[b] (two slabs ago) has drained it
         }
         tmem_ld_wait();
         if (s == nslab - 1) {  // accumulators are in registers: hand the TMEM buffer back to the MMA warp
@@ -378,11 +391,20 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         }
         __syncwarp();
       }
+      if (leader) pb.end(5);  // tmem_full seen -> last slab of the tile handed to the store engine
     }
-    if (leader) bulk_wait_all();
+    if (leader) {
+      pb.begin();
+      bulk_wait_all();
+      pb.end(7);
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) {
+    pb_all.end(0);
+    if (p.dbg) atomicAdd(p.dbg + 8, 1ull);
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);

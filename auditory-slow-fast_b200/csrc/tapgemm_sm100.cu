@@ -17,158 +17,9 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace asf {
-
-// ------------------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() {
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.b32 %0, 1, 0, p;\n}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Bounded wait: a lost arrival turns into a trap (reported as a launch failure) instead of a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) {
-      printf("asf tapgemm: mbarrier wait timeout tag=%d block=%d thread=%d parity=%u\n", tag, (int)blockIdx.x,
-             (int)threadIdx.x, parity);
-      __trap();
-    }
-  }
-}
-
-__device__ __forceinline__ void tma_load(const CUtensorMap* tm, uint64_t* bar, void* dst, int rank, int c0, int c1,
-                                         int c2, int c3, int c4) {
-  const uint32_t d = smem_u32(dst), b = smem_u32(bar);
-  const uint64_t t = (uint64_t)tm;
-  switch (rank) {
-    case 2:
-      asm volatile(
-          "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1) : "memory");
-      break;
-    case 3:
-      asm volatile(
-          "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2) : "memory");
-      break;
-    case 4:
-      asm volatile(
-          "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-      break;
-    default:
-      asm volatile(
-          "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-          ::"r"(d), "l"(t), "r"(b), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
-      break;
-  }
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)tm) : "memory");
-}
-
-// TMA store of one smem box to global (bulk async-group completion); OOB parts of the box are clipped
-__device__ __forceinline__ void tma_store(const CUtensorMap* tm, const void* src, int rank, int c0, int c1, int c2,
-                                          int c3) {
-  const uint32_t s = smem_u32(src);
-  const uint64_t t = (uint64_t)tm;
-  switch (rank) {
-    case 2:
-      asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(t), "r"(s),
-                   "r"(c0), "r"(c1) : "memory");
-      break;
-    case 3:
-      asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(t), "r"(s),
-                   "r"(c0), "r"(c1), "r"(c2) : "memory");
-      break;
-    default:
-      asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(t),
-                   "r"(s), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-      break;
-  }
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-// generic-proxy smem writes -> visible to the async proxy (TMA store source)
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void named_bar(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
-               "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// arrives on `bar` once every tcgen05.mma issued so far by this thread has completed
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// shared-memory matrix descriptor, 128B swizzle (layout_type 2), descriptor version 1 (Blackwell)
-__device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
-  return d;
-}
-// instruction descriptor: D fp32, A/B bf16, M x N, majors (0 = K-major, 1 = MN-major)
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
-         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
 
 // ------------------------------------------------------------------------------------------------ parameters
 constexpr int TG_MAX_STAGES = 8;
@@ -206,6 +57,15 @@ struct TgParams {
   float* dwp;
   int ntaps_w, ksplit, c_tiles, r_tiles;
   int wg_ny, wg_nx, wg_halves, wg_tn, wg_tmem_cols;  // second-generation wgrad tile (tapgemm_wgrad.cuh)
+  unsigned long long* dbg;  // diagnostic stall counters (asf_tapgemm_probe), normally NULL
+};
+
+// stall probe: cycles a role spent inside a wait, summed over CTAs into dbg[slot]
+struct Probe {
+  unsigned long long* d;
+  long long t;
+  __device__ __forceinline__ void begin() { if (d) t = clock64(); }
+  __device__ __forceinline__ void end(int slot) { if (d) atomicAdd(d + slot, (unsigned long long)(clock64() - t)); }
 };
 
 struct TgShared {
@@ -651,6 +511,7 @@ static void prof_end(ProfRec* r, cudaStream_t st) {
   if (r) cudaEventRecord(r->e1, st);
 }
 
+static unsigned long long* g_probe = nullptr;
 static int g_debug_sync = -1;
 static int debug_sync(cudaStream_t st) {
   if (g_debug_sync < 0) {
@@ -713,6 +574,11 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
 
 using namespace asf;
 
+extern "C" int asf_tapgemm_probe(unsigned long long* dev_counters) {
+  g_probe = dev_counters;
+  return 0;
+}
+
 extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   ASF_CHECK_ARG(q && (mode == 0 || mode == 1), "asf_tapgemm: bad mode");
   ASF_CHECK_ARG(q->a && q->nd >= 1 && q->nd <= 4 && q->K > 0 && q->K % 8 == 0 && q->N > 0,
@@ -720,6 +586,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   ASF_CHECK_ARG(q->ntaps >= 1 && q->ntaps <= ASF_MAX_TAPS && q->ntaps_w >= 1, "asf_tapgemm: bad tap count");
   static TgParams p;  // large POD; filled per call (the launch copies it)
   memset(&p, 0, sizeof(p));
+  p.dbg = g_probe;
   int box_a[4] = {1, 1, 1, 1}, box_y[4] = {1, 1, 1, 1};
   int prod = 1, last = 0;
   p.m_tiles_total = 1;

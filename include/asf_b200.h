@@ -76,6 +76,22 @@ int asf_logmel_fwd(const float* wave, int64_t wave_ld, int B, int n_samples, int
                    int n_mels, float eps, const float* basisT, const float* melT, const int32_t* mel_range,
                    int n_bins_pad, float* fast, int T_out, void* stream);
 
+/* Tensor-core (tcgen05 / TMEM, 3-term TF32 split = fp32-grade accuracy) version of asf_logmel_fwd for the shipped
+ * configuration win = 240, hop = 120 (= win / 2), n_fft <= 2048: same inputs, same output, same padding rules.
+ *   asf_logmel_tc_supported   1 when (n_fft, win, hop) can run on this path
+ *   asf_logmel_tc_btab_floats number of floats of the pre-split basis image for n_fft
+ *   asf_logmel_tc_tables      fills btab [asf_logmel_tc_btab_floats], melw [nbp][2] (descending / ascending weight of
+ *                             the two mel filters a bin touches) and melj [nbp] (index of the ascending filter), with
+ *                             nbp = ceil((n_fft/2+1) / 104) * 104; fails if a bin touches non-adjacent filters
+ *   asf_logmel_fwd_tc         wave [B][wave_ld] fp32 -> fast [B][T_out][n_mels] fp32 */
+int asf_logmel_tc_supported(int n_fft, int win, int hop);
+long long asf_logmel_tc_btab_floats(int n_fft);
+int asf_logmel_tc_tables(float* btab, float* melw, int32_t* melj, int sr, int n_fft, int win, int hop, int n_mels,
+                         void* stream);
+int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, int n_fft, int win, int hop,
+                      int n_mels, float eps, const float* btab, const float* melw, const int32_t* melj, float* fast,
+                      int T_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Convolution family.  Replaces every nn.Conv2d (+ the BatchNorm2d / ReLU / residual add / torch.cat
  * that follow it) of
@@ -174,6 +190,11 @@ typedef struct {
 } asf_tapgemm_t;
 
 int asf_tapgemm(const asf_tapgemm_t* p, int mode, void* stream);
+/* Diagnostic: device array of >= 16 uint64 counters that later mode-0 launches add stall cycles to (summed over
+ * CTAs): [0] kernel body, [1] producer waiting for a free stage, [2] MMA waiting for operands, [3] MMA waiting for
+ * a free accumulator, [4] epilogue waiting for accumulators, [5] epilogue busy per tile, [6] epilogue waiting for
+ * its store buffer, [7] final store drain, [8] CTAs.  NULL switches the probe off (default). */
+int asf_tapgemm_probe(unsigned long long* dev_counters);
 /* the ksplit asf_tapgemm(p, 1, ...) uses when p->ksplit == 0 (>= 1), or a negative error code */
 int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* p);
 

@@ -34,6 +34,8 @@ class Harness(Engine):
         self.two_stream = False
         self.sm_split = (0, 0)
         self._side = None
+        self._wg = [None, None]
+        self.wgrad_streams = False
 
 
 def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, in_scale=1.0):

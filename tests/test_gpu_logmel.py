@@ -21,12 +21,12 @@ def _cfg():
     return epic_slowfast_cfg()
 
 
-def _gpu_logmel(w, num_frames=None):
+def _gpu_logmel(w, num_frames=None, impl=None):
     from asf_b200.datasets.audio_loader_epic import logmel_cuda
     x = torch.from_numpy(np.ascontiguousarray(w)).cuda()
     if x.dim() == 1:
         x = x[None]
-    return logmel_cuda(x, num_frames=num_frames).cpu().numpy()
+    return logmel_cuda(x, num_frames=num_frames, impl=impl).cpu().numpy()
 
 
 CASES = ["noise0", "noise1", "sine1k", "zeros", "len48000", "len23975", "len5000", "len119"]
@@ -46,10 +46,11 @@ def _inputs():
     }
 
 
+@pytest.mark.parametrize("impl", ["tc", "simt"])  # tcgen05 3xTF32 kernel (the default) / fp32 CUDA-core kernel
 @pytest.mark.parametrize("name", CASES)
-def test_logmel_matches_oracle_and_golden(golden_dir, name):
+def test_logmel_matches_oracle_and_golden(golden_dir, name, impl):
     w = _inputs()[name]
-    out = _gpu_logmel(w)[0, 0]
+    out = _gpu_logmel(w, impl=impl)[0, 0]
     ref = OL.log_specgram(w)
     gold = np.load(os.path.join(golden_dir, "logmel.npz"))[name]
     assert out.shape == ref.shape == gold.shape
@@ -93,6 +94,31 @@ def test_extract_sound_feature_and_batched_pack():
     assert slow.shape == (3, 1, 100, 128) and fast.shape == (3, 1, 400, 128)
     idx = torch.from_numpy(OL.slow_indices(400, 4)).cuda()
     assert torch.equal(slow, fast[:, :, idx, :])
+
+
+def test_tc_tiles_straddle_clips_and_edge_padding():
+    """The tensor-core kernel tiles the flattened (clip, frame) space in 128-row tiles: clips of 42 frames put three
+    clip boundaries inside one tile; num_frames > T adds the np.pad(..., "edge") rows; both must agree with the
+    per-clip oracle and with the CUDA-core kernel."""
+    wav = OL.synthetic_waveforms(37, 5000, 21)
+    tc = _gpu_logmel(wav, num_frames=50, impl="tc")
+    simt = _gpu_logmel(wav, num_frames=50, impl="simt")
+    assert tc.shape == simt.shape == (37, 1, 50, 128)
+    for b in (0, 1, 2, 3, 17, 36):
+        ref = OL.extract_sound_feature(wav[b], num_frames=50)[0]
+        for out in (tc, simt):
+            rel_log, rel_lin, _ = OL.logmel_parity(ref, out[b, 0])
+            assert rel_log <= TOL_LOG and rel_lin <= TOL_LIN, (b, rel_log, rel_lin)
+    assert np.array_equal(tc[:, 0, 41], tc[:, 0, 49])
+    # loud / quiet / DC-offset clips in one batch: per-clip independence of the shared accumulators
+    mix = OL.synthetic_waveforms(5, 47975, 22)
+    mix[1] *= 1e-3
+    mix[2] = 0.0
+    mix[3] += 0.25
+    out = _gpu_logmel(mix, impl="tc")
+    for b in range(5):
+        rel_log, rel_lin, _ = OL.logmel_parity(OL.log_specgram(mix[b]), out[b, 0])
+        assert rel_log <= TOL_LOG and rel_lin <= TOL_LIN, (b, rel_log, rel_lin)
 
 
 def test_full_batch_properties():

@@ -44,9 +44,13 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3):
         ts(w, lab)
     torch.cuda.synchronize()
-evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
-evs.sort(key=lambda e: e.time_range.start)
-rows = [(e.name, e.time_range.start, e.time_range.end) for e in evs]
+kin = prof.profiler.kineto_results.events()
+rows = []
+for e in kin:
+    if e.device_type() == torch.autograd.DeviceType.CUDA:
+        s0 = e.start_ns() / 1e3
+        rows.append((e.name(), s0, s0 + e.duration_ns() / 1e3, e.device_resource_id()))
+rows.sort(key=lambda r: r[1])
 # split into steps at the log-mel kernel
 starts = [i for i, r in enumerate(rows) if "logmel" in r[0]]
 print("cuda events", len(rows), "steps", len(starts))
@@ -57,9 +61,10 @@ if len(starts) >= 2:
     busy = collections.defaultdict(lambda: [0, 0.0])
     gaps = collections.defaultdict(lambda: [0, 0.0])
     prev_end = step[0][1]
+    per_stream = collections.defaultdict(lambda: [0, 0.0, 1e18, 0.0])
     tot_busy = tot_gap = 0.0
     with open(prefix + "_events.csv", "w") as f:
-        for name, s, e in step:
+        for name, s, e, sid in step:
             short = name.split("(")[0].replace("void ", "")[:60]
             gap = max(0.0, s - prev_end)
             busy[short][0] += 1
@@ -68,13 +73,19 @@ if len(starts) >= 2:
             gaps[short][1] += gap
             tot_busy += e - s
             tot_gap += gap
-            f.write("%s,%.3f,%.3f,%.3f\n" % (short, s - step[0][1], e - s, gap))
+            f.write("%s,%.3f,%.3f,%.3f,%d\n" % (short, s - step[0][1], e - s, gap, sid))
+            per_stream[sid][0] += 1
+            per_stream[sid][1] += e - s
+            per_stream[sid][2] = min(per_stream[sid][2], s - step[0][1])
+            per_stream[sid][3] = max(per_stream[sid][3], e - step[0][1])
             prev_end = max(prev_end, e)
     with open(prefix + "_summary.txt", "w") as f:
         def out(*a):
             print(*a)
             print(*a, file=f)
         out("step span %.1f us, kernels %d, sum busy %.1f us, sum gaps %.1f us" % (span, len(step), tot_busy, tot_gap))
+        for sid, v in sorted(per_stream.items()):
+            out("stream %d: %d kernels, busy %.1f us, first start %.1f, last end %.1f" % (sid, v[0], v[1], v[2], v[3]))
         out("%-62s %5s %10s %8s %10s" % ("kernel", "n", "busy_us", "avg", "gap_before"))
         for k, v in sorted(busy.items(), key=lambda x: -x[1][1]):
             out("%-62s %5d %10.1f %8.2f %10.1f" % (k, v[0], v[1], v[1] / v[0], gaps[k][1]))
