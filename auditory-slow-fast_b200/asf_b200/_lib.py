@@ -152,13 +152,20 @@ def call(name, *args):
     return rc
 
 
+_SM100_OK = set()
+
+
 def require_cuda_sm100():
     if not torch.cuda.is_available():
         raise RuntimeError("asf_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    dev = torch.cuda.current_device()
+    if dev in _SM100_OK:
+        return
     l = lib()
     ok = l.asf_device_is_sm100()
     if ok != 1:
         raise RuntimeError("asf_b200 kernels are built for sm_100a only; current device is not sm_100")
+    _SM100_OK.add(dev)
 
 
 def dtype_code(dt):

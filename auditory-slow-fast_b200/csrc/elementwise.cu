@@ -609,11 +609,10 @@ int asf_version(void) { return 101; }
 long long asf_launch_count(void) { return __atomic_load_n(&asf::g_launches, __ATOMIC_RELAXED); }
 
 int asf_device_is_sm100(void) {
-  int dev = 0;
-  cudaDeviceProp prop;
+  int dev = 0, major = 0;  // (cudaGetDeviceProperties costs milliseconds; this is called on every public entry)
   ASF_CUDA(cudaGetDevice(&dev));
-  ASF_CUDA(cudaGetDeviceProperties(&prop, dev));
-  return prop.major == 10 ? 1 : 0;
+  ASF_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  return major == 10 ? 1 : 0;
 }
 
 int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream) {

@@ -23,6 +23,7 @@
 //               filter j-1 and the ascending side of filter j), log, store -- one thread per frame
 //   warps 6-9   stage the next tile's chunk rows: coalesced loads, hi/lo split, conflict-free smem stores
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -36,7 +37,8 @@ constexpr int LT_HOP = 120;
 constexpr int LT_K4H = LT_HOP / 4;         // 16-byte K groups per half
 constexpr int LT_NBC = 104;                // bins per chunk
 constexpr int LT_NCOL = 2 * LT_NBC;        // accumulator columns: re | im
-constexpr int LT_KS = 24;                  // K floats per pipeline slab (3 MMA K-steps)
+constexpr int LT_KS = 24;                  // K floats per pipeline slab (3 MMA K-steps; a tcgen05.commit costs a ~200-cycle
+                                           // bubble of the tensor pipe, so slabs are as large as shared memory allows)
 constexpr int LT_SLABS = LT_HOP / LT_KS;   // 5 per half
 constexpr int LT_NR = 137;                 // padded row count of the A image (row pitch 16 B, K-group pitch 137*16)
 constexpr int LT_A_LBO = LT_NR * 16;       // 2192 B between K groups: 548 words = 4 (mod 32) -> conflict-free staging
@@ -51,7 +53,7 @@ constexpr int LT_OFF_B = 2 * LT_A_STRIDE;
 constexpr int LT_OFF_W = LT_OFF_B + LT_STAGES * LT_B_STAGE;
 constexpr int LT_OFF_J = LT_OFF_W + LT_MAX_BINS * 8;
 constexpr int LT_OFF_BAR = LT_OFF_J + LT_MAX_BINS * 4;
-constexpr int LT_SMEM = LT_OFF_BAR + 16 * 8;
+constexpr int LT_SMEM = LT_OFF_BAR + 24 * 8;
 constexpr int LT_THREADS = 320;
 static_assert(LT_A_BYTES <= LT_A_STRIDE && LT_SMEM <= 227 * 1024, "log-mel tile does not fit in shared memory");
 
@@ -61,7 +63,7 @@ struct LtBars {
   uint64_t tmem_full[2], tmem_empty[2];
   uint32_t tmem_base;
 };
-static_assert(sizeof(LtBars) <= 16 * 8, "barrier block");
+static_assert(sizeof(LtBars) <= 24 * 8, "barrier block");
 
 // no-swizzle K-major operand: core matrices (8 rows x 16 B) LBO bytes apart along K, SBO bytes apart along M/N
 __device__ __forceinline__ uint64_t lt_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
@@ -87,6 +89,32 @@ __device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* r) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "r"(taddr));
 }
+// One lane polls (with back-off), the warp follows: 128 threads spinning on one mbarrier word keep the shared-memory
+// pipe busy that the MMA operand reads, the epilogue's table loads and the stager's stores all need.
+__device__ __forceinline__ void lt_wait_warp(uint64_t* bar, uint32_t parity, int tag, unsigned sleep_ns) {
+  if ((threadIdx.x & 31) == 0) {
+    if (!mbar_try_wait(bar, parity)) {
+      const long long t0 = clock64();
+      while (!mbar_try_wait(bar, parity)) {
+        if (sleep_ns) __nanosleep(sleep_ns);
+        if (clock64() - t0 > 4000000000LL) {
+          printf("asf logmel_tc: mbarrier wait timeout tag=%d block=%d warp=%d parity=%u\n", tag, (int)blockIdx.x,
+                 (int)(threadIdx.x >> 5), parity);
+          __trap();
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+// a finished mel band of one frame: log, store (and the np.pad(..., "edge") copies of the clip's last frame)
+__device__ __noinline__ void lt_emit(float* orow, int m, float v, float eps, bool ok, int n_rep, int n_mels) {
+  if (ok) {
+    const float l = logf(v + eps);
+    orow[m] = l;
+    for (int q = 1; q <= n_rep; ++q) orow[(long long)q * n_mels + m] = l;
+  }
+}
 __device__ __forceinline__ void lt_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ uint32_t tf32_rna(float x) {
   uint32_t u;
@@ -98,7 +126,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
 logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_samples, int T_valid, int T_out,
                  int n_chunks, int n_mels, float eps, const float* __restrict__ btab,
                  const float2* __restrict__ melw, const int* __restrict__ melj, float* __restrict__ out,
-                 long long total_rows, int n_tiles) {
+                 long long total_rows, int n_tiles, int dbg, unsigned long long* probe) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_trigger();
   LtBars* bars = (LtBars*)(smem + LT_OFF_BAR);
@@ -129,6 +157,10 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   pdl_wait();
+  long long pt = 0;
+#define LT_PB() do { if (probe) pt = clock64(); } while (0)
+#define LT_PE(slot) do { if (probe) atomicAdd(probe + (slot), (unsigned long long)(clock64() - pt)); } while (0)
+  const long long t_start = clock64();
 
   if (warp == 0) {
     // ===== basis producer =====
@@ -138,9 +170,12 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint8_t* src = (const uint8_t*)btab;
         for (int i = 0; i < n_chunks * 2 * LT_SLABS; ++i) {
+          LT_PB();
           mbar_wait(&bars->b_empty[st], ph ^ 1, 21);
-          mbar_expect_tx(&bars->b_full[st], LT_B_STAGE);
-          bulk_g2s(smem + LT_OFF_B + st * LT_B_STAGE, src, LT_B_STAGE, &bars->b_full[st]);
+          LT_PE(1);
+          const uint32_t nbytes = (dbg & 1) ? 16u : (uint32_t)LT_B_STAGE;  // dbg bit 0: no basis traffic (wrong results)
+          mbar_expect_tx(&bars->b_full[st], nbytes);
+          bulk_g2s(smem + LT_OFF_B + st * LT_B_STAGE, src, nbytes, &bars->b_full[st]);
           src += LT_B_STAGE;
           if (++st == LT_STAGES) { st = 0; ph ^= 1; }
         }
@@ -158,17 +193,23 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
       uint32_t g = 0;  // accumulator use counter
       int it = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        LT_PB();
         mbar_wait(&bars->a_full, (uint32_t)(it & 1), 22);
+        LT_PE(2);
         tc_fence_after();
         for (int c = 0; c < n_chunks; ++c, ++g) {
           const uint32_t buf = g & 1;
+          LT_PB();
           mbar_wait(&bars->tmem_empty[buf], ((g >> 1) & 1) ^ 1, 23);
+          LT_PE(3);
           tc_fence_after();
           const uint32_t d = tmem_base + buf * 256;
           uint32_t acc = 0;
           for (int h = 0; h < 2; ++h) {
             for (int s = 0; s < LT_SLABS; ++s) {
+              LT_PB();
               mbar_wait(&bars->b_full[st], ph, 24);
+              LT_PE(4);
               tc_fence_after();
               const uint64_t bh = b0 + (uint64_t)((st * LT_B_STAGE) >> 4), bl = bh + (uint64_t)(LT_B_HALF >> 4);
 #pragma unroll
@@ -195,51 +236,71 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
     const int r = quarter * 32 + lane;
     uint32_t g = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-      const long long R = (long long)tile * 128 + r;
-      const int b = (int)(R / RP), t = (int)(R - (long long)b * RP);
-      const bool valid = R < total_rows && t < T_valid;
+      const int R = tile * 128 + r;
+      const int b = R / RP, t = R - b * RP;
+      const bool valid = (long long)R < total_rows && t < T_valid;
       float* orow = out + ((long long)b * T_out + t) * n_mels;
       const int n_rep = (valid && t == T_valid - 1) ? (T_out - T_valid) : 0;  // np.pad(..., "edge") rows
       float cur = 0.f, nxt = 0.f;
       int j_cur = 0;
-      auto emit = [&](int m, float v) {
-        if (valid && m >= 0 && m < n_mels) {
-          const float l = logf(v + eps);
-          orow[m] = l;
-          for (int q = 1; q <= n_rep; ++q) orow[(long long)q * n_mels + m] = l;
-        }
-      };
+      auto emit = [&](int m, float v) { lt_emit(orow, m, v, eps, valid && m >= 0 && m < n_mels, n_rep, n_mels); };
       for (int c = 0; c < n_chunks; ++c, ++g) {
         const uint32_t buf = g & 1;
-        mbar_wait(&bars->tmem_full[buf], (g >> 1) & 1, 25);
+        if (threadIdx.x == 64) LT_PB();
+        lt_wait_warp(&bars->tmem_full[buf], (g >> 1) & 1, 25, 0);
+        if (threadIdx.x == 64) { LT_PE(5); LT_PB(); }
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256;
 #pragma unroll 1
-        for (int j0 = 0; j0 < LT_NBC; j0 += 8) {
+        for (int j0 = 0; j0 < ((dbg & 2) ? 8 : LT_NBC); j0 += 8) {  // dbg bit 1: epilogue touches one column group
           uint32_t re[8], im[8];
           tmem_ld8_issue(taddr + (uint32_t)j0, re);
           tmem_ld8_issue(taddr + (uint32_t)(LT_NBC + j0), im);
+          const int k0 = c * LT_NBC + j0;
+          // tables of the eight bins (independent of the accumulators: issued under the TMEM load latency)
+          const int4 ja = *(const int4*)(sj + k0), jb = *(const int4*)(sj + k0 + 4);
+          const float4 wa = *(const float4*)(sw + k0), wb = *(const float4*)(sw + k0 + 2),
+                       wc = *(const float4*)(sw + k0 + 4), wd = *(const float4*)(sw + k0 + 6);
+          const int jk[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
+          const float wdn[8] = {wa.x, wa.z, wb.x, wb.z, wc.x, wc.z, wd.x, wd.z};
+          const float wup[8] = {wa.y, wa.w, wb.y, wb.w, wc.y, wc.w, wd.y, wd.w};
           lt_ld_wait();
+          // magnitudes, branch-free and independent of each other: s * rsqrt(s) + one Newton step (~1 ulp)
+          float mag[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
-            const int k = c * LT_NBC + j0 + q;
             const float x = __uint_as_float(re[q]), y = __uint_as_float(im[q]);
-            const float mag = sqrtf(fmaf(x, x, y * y));
-            const int jk = sj[k];
-            while (j_cur < jk) {  // uniform across the CTA: filter j_cur - 1 is complete
-              emit(j_cur - 1, cur);
-              cur = nxt;
-              nxt = 0.f;
-              ++j_cur;
+            const float s2 = fmaf(x, x, y * y);
+            float rs;
+            asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(s2));
+            const float m0 = s2 * rs;
+            const float m1 = fmaf(fmaf(-m0, m0, s2), 0.5f * rs, m0);
+            mag[q] = s2 >= 1e-36f ? m1 : 0.f;
+          }
+          if (jk[7] == j_cur) {  // no filter boundary inside the group (uniform): two short FMA chains
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              cur = fmaf(wdn[q], mag[q], cur);
+              nxt = fmaf(wup[q], mag[q], nxt);
             }
-            const float2 w = sw[k];
-            cur = fmaf(w.x, mag, cur);
-            nxt = fmaf(w.y, mag, nxt);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              while (j_cur < jk[q]) {  // uniform across the CTA: filter j_cur - 1 is complete
+                emit(j_cur - 1, cur);
+                cur = nxt;
+                nxt = 0.f;
+                ++j_cur;
+              }
+              cur = fmaf(wdn[q], mag[q], cur);
+              nxt = fmaf(wup[q], mag[q], nxt);
+            }
           }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+        if (threadIdx.x == 64) LT_PE(6);
       }
       while (j_cur <= n_mels) {
         emit(j_cur - 1, cur);
@@ -250,50 +311,77 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
     }
   } else {
     // ===== chunk-row stager (128 threads) =====
+    // Warp w of the stagers owns chunk rows w, w + 4, ... (33 at most); a lane holds samples lane, lane + 32, ... of
+    // each row.  The NEXT tile's samples are loaded into registers while the current tile computes, so that once the
+    // MMAs release the image only the hi/lo split and the (bank-conflict-free) stores remain.
     const int sidx = (int)threadIdx.x - 192;
+    const int sw_ = (int)(threadIdx.x >> 5) - 6;
+    constexpr int LT_RPW = 33;
+    float xr[LT_RPW][4];
+    auto load_tile = [&](int tile) {
+      const int row0 = tile * 128;  // < 2^31 (checked by the launcher)
+#pragma unroll
+      for (int i = 0; i < LT_RPW; ++i) {
+        const int r2 = sw_ + 4 * i;
+        const int R = row0 + r2;
+        const int b = R / RP, t = R - b * RP;
+        const bool row_ok = tile < n_tiles && r2 < 129 && (long long)R < total_rows && t >= 1;
+        const float* src = wave + (long long)b * wave_ld + (long long)(t - 1) * LT_HOP;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int k = lane + 32 * u;
+          xr[i][u] = (row_ok && k < LT_HOP && (t - 1) * LT_HOP + k < n_samples) ? src[k] : 0.f;
+        }
+      }
+    };
+    load_tile(blockIdx.x);
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      mbar_wait(&bars->a_free, (uint32_t)((it & 1) ^ 1), 26);
-      const long long R0 = (long long)tile * 128;
-      constexpr int TOT = 129 * LT_HOP;
-#pragma unroll 1
-      for (int e0 = sidx; e0 < TOT; e0 += 4 * 128) {
-        float x[4];
-        int off[4];
+      if (sidx == 0) LT_PB();
+      lt_wait_warp(&bars->a_free, (uint32_t)((it & 1) ^ 1), 26, 256);
+      if (sidx == 0) { LT_PE(7); LT_PB(); }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int e = e0 + u * 128;
-          x[u] = 0.f;
-          off[u] = -1;
-          if (e < TOT) {
-            const int rr = e / LT_HOP, k = e - rr * LT_HOP;
-            const long long R = R0 + rr;
-            const int b = (int)(R / RP), t = (int)(R - (long long)b * RP);
-            const int s = (t - 1) * LT_HOP + k;
-            if (R < total_rows && t >= 1 && s < n_samples) x[u] = wave[(long long)b * wave_ld + s];
-            off[u] = (k >> 2) * LT_A_LBO + rr * 16 + (k & 3) * 4;
-          }
-        }
+      for (int i = 0; i < LT_RPW; ++i) {
+        const int r2 = sw_ + 4 * i;
+        if (r2 < 129) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (off[u] >= 0) {
-            const uint32_t hi = tf32_rna(x[u]);
-            const uint32_t lo = tf32_rna(x[u] - __uint_as_float(hi));
-            *(uint32_t*)(smem + off[u]) = hi;
-            *(uint32_t*)(smem + LT_A_STRIDE + off[u]) = lo;
+          for (int u = 0; u < 4; ++u) {
+            const int k = lane + 32 * u;
+            if (k < LT_HOP) {
+              const uint32_t hi = tf32_rna(xr[i][u]);
+              const uint32_t lo = tf32_rna(xr[i][u] - __uint_as_float(hi));
+              const int off = (k >> 2) * LT_A_LBO + r2 * 16 + (k & 3) * 4;
+              *(uint32_t*)(smem + off) = hi;
+              *(uint32_t*)(smem + LT_A_STRIDE + off) = lo;
+            }
           }
         }
       }
       fence_proxy_async();
       mbar_arrive(&bars->a_full);
+      if (sidx == 0) LT_PE(8);
+      load_tile(tile + (int)gridDim.x);
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (probe && threadIdx.x == 0) {
+    atomicAdd(probe + 0, (unsigned long long)(clock64() - t_start));
+    atomicAdd(probe + 9, 1ull);
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+}
+
+static int lt_dbg() {  // ASF_LOGMEL_DBG: timing experiments only (bit 0 / bit 1 switch off basis traffic / epilogue)
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ASF_LOGMEL_DBG");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
 }
 
 static inline float host_tf32_rna(float x) {
@@ -410,7 +498,7 @@ int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, 
   const int n_chunks = (n_fft / 2 + 1 + LT_NBC - 1) / LT_NBC;
   const long long total_rows = (long long)B * (T_valid + 1);
   const long long n_tiles = cdiv(total_rows, 128);
-  ASF_CHECK_ARG(n_tiles < (1ll << 30), "asf_logmel_fwd_tc: batch too large");
+  ASF_CHECK_ARG(total_rows + 256 < (1ll << 31), "asf_logmel_fwd_tc: batch too large (B * frames must stay below 2^31)");
   static bool attr_set = false;
   if (!attr_set) {
     ASF_CUDA(cudaFuncSetAttribute(logmel_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LT_SMEM));
@@ -420,10 +508,27 @@ int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, 
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int grid = (int)(n_tiles < sms ? n_tiles : sms);
+  unsigned long long* probe = nullptr;
+  if (lt_dbg() & 32) {  // ASF_LOGMEL_DBG bit 5: print the stall counters of this launch (synchronises)
+    static unsigned long long* dprobe = nullptr;
+    if (!dprobe) ASF_CUDA(cudaMalloc(&dprobe, 16 * sizeof(unsigned long long)));
+    ASF_CUDA(cudaMemsetAsync(dprobe, 0, 16 * sizeof(unsigned long long), (cudaStream_t)stream));
+    probe = dprobe;
+  }
   ASF_CUDA(launch_pdl(logmel_tc_kernel, dim3(grid), dim3(LT_THREADS), (size_t)LT_SMEM, (cudaStream_t)stream, wave,
                       (long long)wave_ld, n_samples, T_valid, T_out, n_chunks, n_mels, eps, btab, (const float2*)melw,
-                      (const int*)melj, fast, total_rows, (int)n_tiles));
+                      (const int*)melj, fast, total_rows, (int)n_tiles, lt_dbg(), probe));
   ASF_LAUNCH_CHECK();
+  if (probe) {
+    unsigned long long h[16];
+    ASF_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    ASF_CUDA(cudaMemcpy(h, probe, sizeof(h), cudaMemcpyDeviceToHost));
+    const double n = h[9] ? (double)h[9] : 1.0;
+    fprintf(stderr, "logmel_tc probe (kcycles per CTA, %d tiles on %d CTAs): body %.1f | producer wait stage %.1f | mma wait A %.1f, "
+            "wait acc %.1f, wait basis %.1f | epilogue wait acc %.1f, busy %.1f | stager wait free %.1f, busy %.1f\n",
+            (int)n_tiles, grid, h[0] / n / 1e3, h[1] / n / 1e3, h[2] / n / 1e3, h[3] / n / 1e3, h[4] / n / 1e3, h[5] / n / 1e3,
+            h[6] / n / 1e3, h[7] / n / 1e3, h[8] / n / 1e3);
+  }
   return 0;
 }
 

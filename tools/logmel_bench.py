@@ -1,4 +1,4 @@
-"""GPU aid: log-mel kernels timed alone (CUDA events, L2 flushed between launches).  python tools/logmel_bench.py [B]"""
+"""GPU aid: log-mel kernels timed alone (CUDA events around 20 back-to-back launches).  python tools/logmel_bench.py [B]"""
 import os
 import sys
 
@@ -11,20 +11,18 @@ from asf_b200.datasets.audio_loader_epic import logmel_cuda
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 w = (0.1 * torch.randn(B, 47975, device="cuda")).clamp_(-1, 1)
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for impl in ("tc", "simt"):
     logmel_cuda(w, impl=impl)
     torch.cuda.synchronize()
-    tot = 0.0
-    for _ in range(10):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+    for _ in range(30):  # spin the clocks up
         logmel_cuda(w, impl=impl)
-        e1.record()
-        torch.cuda.synchronize()
-        tot += e0.elapsed_time(e1)
-    us = tot / 10 * 1e3
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        logmel_cuda(w, impl=impl)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / 20 * 1e3
     print("%-5s B=%d  %8.1f us  %8.0f clips/s  %6.2f TFLOP/s(dense fp32-equivalent)  %6.1f GB/s(alg)" %
           (impl, B, us, B / us * 1e6, B * 0.4986e9 / us / 1e6, B * 396700 / us / 1e3))
 a = logmel_cuda(w, impl="tc")
