@@ -89,24 +89,6 @@ __device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* r) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "r"(taddr));
 }
-// One lane polls (with back-off), the warp follows: 128 threads spinning on one mbarrier word keep the shared-memory
-// pipe busy that the MMA operand reads, the epilogue's table loads and the stager's stores all need.
-__device__ __forceinline__ void lt_wait_warp(uint64_t* bar, uint32_t parity, int tag, unsigned sleep_ns) {
-  if ((threadIdx.x & 31) == 0) {
-    if (!mbar_try_wait(bar, parity)) {
-      const long long t0 = clock64();
-      while (!mbar_try_wait(bar, parity)) {
-        if (sleep_ns) __nanosleep(sleep_ns);
-        if (clock64() - t0 > 4000000000LL) {
-          printf("asf logmel_tc: mbarrier wait timeout tag=%d block=%d warp=%d parity=%u\n", tag, (int)blockIdx.x,
-                 (int)(threadIdx.x >> 5), parity);
-          __trap();
-        }
-      }
-    }
-  }
-  __syncwarp();
-}
 // a finished mel band of one frame: log, store (and the np.pad(..., "edge") copies of the clip's last frame)
 __device__ __noinline__ void lt_emit(float* orow, int m, float v, float eps, bool ok, int n_rep, int n_mels) {
   if (ok) {
@@ -247,7 +229,7 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
       for (int c = 0; c < n_chunks; ++c, ++g) {
         const uint32_t buf = g & 1;
         if (threadIdx.x == 64) LT_PB();
-        lt_wait_warp(&bars->tmem_full[buf], (g >> 1) & 1, 25, 0);
+        mbar_wait_warp(&bars->tmem_full[buf], (g >> 1) & 1, 25, 0);
         if (threadIdx.x == 64) { LT_PE(5); LT_PB(); }
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256;
@@ -338,7 +320,7 @@ logmel_tc_kernel(const float* __restrict__ wave, long long wave_ld, int n_sample
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       if (sidx == 0) LT_PB();
-      lt_wait_warp(&bars->a_free, (uint32_t)((it & 1) ^ 1), 26, 256);
+      mbar_wait_warp(&bars->a_free, (uint32_t)((it & 1) ^ 1), 26, 256);
       if (sidx == 0) { LT_PE(7); LT_PB(); }
 #pragma unroll
       for (int i = 0; i < LT_RPW; ++i) {

@@ -44,6 +44,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
   }
 }
 
+// Whole-warp wait: lane 0 polls (optionally backing off), the warp follows through __syncwarp.  Many threads spinning
+// on one mbarrier word keep the shared-memory pipe busy that the tensor core's operand reads and the TMA writes need.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity, int tag, unsigned sleep_ns = 0) {
+  if ((threadIdx.x & 31) == 0) {
+    if (!mbar_try_wait(bar, parity)) {
+      const long long t0 = clock64();
+      while (!mbar_try_wait(bar, parity)) {
+        if (sleep_ns) __nanosleep(sleep_ns);
+        if (clock64() - t0 > 4000000000LL) {
+          printf("asf: mbarrier wait timeout tag=%d block=%d warp=%d parity=%u\n", tag, (int)blockIdx.x,
+                 (int)(threadIdx.x >> 5), parity);
+          __trap();
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
 __device__ __forceinline__ void tma_load(const CUtensorMap* tm, uint64_t* bar, void* dst, int rank, int c0, int c1,
                                          int c2, int c3, int c4) {
   const uint32_t d = smem_u32(dst), b = smem_u32(bar);

@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
       }
       named_bar(bar_id, 128);  // s_shift visible to the group
       if (leader) pb.begin();
-      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
+      mbar_wait_warp(&sh->tmem_full[buf], (it >> 1) & 1, 4);
       if (leader) { pb.end(4); pb.begin(); }
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           __syncwarp();
           if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
         }
-        if (n_ops > 0) mbar_wait(&sh->op_full[group][b], (gs >> 1) & 1, 5);
+        if (n_ops > 0) mbar_wait_warp(&sh->op_full[group][b], (gs >> 1) & 1, 5);
         named_bar(bar_id, 128);  // out_buf[b] is free for everybody
         uint8_t* ob = out_buf + b * EPI_SLAB_BYTES;
         const uint8_t* op0 = op_buf + b * EPI_SLAB_BYTES;

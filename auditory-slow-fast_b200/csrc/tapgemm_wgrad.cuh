@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(WG2_THREADS, 1) tapgemm_wgrad2_kernel(const __
     const int half = (warp - 2) >> 2;
     const int quarter = warp & 3;
     if (half < p.wg_halves) {
-      mbar_wait(&sh->tmem_full[0], 0, 13);
+      mbar_wait_warp(&sh->tmem_full[0], 0, 13, 128);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * TN);
       const int wt = p.b_tap[tap];
