@@ -121,8 +121,8 @@ SIGNATURES = {
     "asf_bn_bwd_reduce": [_P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P],
     "asf_bn_bwd_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _D, _P, _P, _I, _P],
     "asf_relu_bwd": [_P, _L, _P, _L, _P, _L, _P, _L, _I, _L, _I, _P],
-    "asf_bn_relu_maxpool_fwd": [_P, _P, _L, _I, _I, _I, _I, _I, _P, _P, _P],
-    "asf_bn_relu_maxpool_bwd": [_P, _P, _L, _P, _I, _I, _I, _I, _I, _P, _P, _P],
+    "asf_bn_relu_maxpool_fwd": [_P, _P, _L, _I, _I, _I, _I, _I, _P, _P, _P, _P],
+    "asf_bn_relu_maxpool_bwd": [_P, _P, _L, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P],
     "asf_avgpool_fwd": [_P, _I, _I, _I, _I, _P, _L, _I, _P],
     "asf_avgpool_bwd": [_P, _L, _I, _P, _P, _I, _I, _I, _I, _P],
     "asf_sgemm": [_P, _P, _P, _I, _I, _I, _I, _I, _L, _L, _L, _F, _F, _P, _P],

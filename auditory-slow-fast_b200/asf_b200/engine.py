@@ -287,6 +287,9 @@ class Engine:
             u = ConvUnit("s1.pathway%d_stem" % p, conv, st.bn, xin, raw, relu=False)
             u.bn_name = "s1.pathway%d_stem.bn" % p
             u.pooled = pooled
+            # arg-max codes of the stem max-pool (written by the forward, read by the backward): bf16 vector path only
+            u.pool_argmax = (torch.empty((B, Tp, Fp, conv.out_channels // 8), dtype=torch.int32, device=dev)
+                             if dt == torch.bfloat16 and conv.out_channels % 8 == 0 else None)
             u.is_stem = True
             u.path = p
             plan.stems.append(u)
@@ -751,7 +754,7 @@ class Engine:
                            L.ptr(u.stats), st)
                     self._bn_forward(u, u.y, None, None, False, training, st)
                 L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld,
-                       u.y.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+                       u.y.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.pool_argmax), st)
         # stages.  Two-stream mode: laterals and fast blocks run ahead on the side stream; the slow blocks of a stage
         # wait for that stage's lateral (which writes the lateral channels of the buffer they read).
         ev_fuse = None
@@ -948,7 +951,8 @@ class Engine:
                 pooled = u.pooled
                 dz = u.y.grad
                 L.call("asf_bn_relu_maxpool_bwd", C.c_void_p(u.y.ptr), C.c_void_p(pooled.grad.ptr), pooled.grad.ld,
-                       C.c_void_p(dz.ptr), dz.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), st)
+                       C.c_void_p(dz.ptr), dz.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift),
+                       L.ptr(u.pool_argmax), st)
                 if u.batch_mode:
                     u.raw = u.y  # the stem keeps its raw conv output in u.y
                 self._unit_backward(u, dz, False, False)

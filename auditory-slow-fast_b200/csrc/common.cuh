@@ -102,9 +102,9 @@ int relu_bwd_v8(const bf16* a, int64_t ld_a, const bf16* b, int64_t ld_b, const 
 int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* mask, bf16* dx, int B, int P, int C,
                    cudaStream_t st);
 int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, int F, int C, const float* scale,
-                           const float* shift, cudaStream_t st);
+                           const float* shift, uint32_t* argmax, cudaStream_t st);
 int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* dz, int B, int T, int F, int C,
-                           const float* scale, const float* shift, cudaStream_t st);
+                           const float* scale, const float* shift, const uint32_t* argmax, cudaStream_t st);
 int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st);
 int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st);
 

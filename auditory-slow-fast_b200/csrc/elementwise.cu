@@ -719,11 +719,12 @@ int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const
 }
 
 int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int B, int T, int F, int C,
-                            const float* scale, const float* shift, void* stream) {
+                            const float* scale, const float* shift, uint32_t* argmax, void* stream) {
   ASF_CHECK_ARG(x && y && scale && shift && B > 0 && T > 0 && F > 0 && C > 0, "asf_bn_relu_maxpool_fwd: bad arguments");
   int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
   if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_y) && al16(x) && al16(y))
-    return bn_relu_maxpool_fwd_v8((const bf16*)x, (bf16*)y, ld_y, B, T, F, C, scale, shift, (cudaStream_t)stream);
+    return bn_relu_maxpool_fwd_v8((const bf16*)x, (bf16*)y, ld_y, B, T, F, C, scale, shift, argmax, (cudaStream_t)stream);
+  ASF_CHECK_ARG(!argmax, "asf_bn_relu_maxpool_fwd: arg-max codes need the bf16 vector path (C %% 8 == 0, aligned)");
   ASF_DISPATCH_DTYPE(dtype, Tt, {
     bn_relu_maxpool_fwd_kernel<Tt><<<ew_grid((int64_t)B * To * Fo * C), 256, 0, (cudaStream_t)stream>>>(
         (const Tt*)x, (Tt*)y, ld_y, B, T, F, C, To, Fo, scale, shift);
@@ -733,13 +734,14 @@ int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int
 }
 
 int asf_bn_relu_maxpool_bwd(const void* x, const void* dy, int64_t ld_dy, void* dz, int dtype, int B, int T, int F,
-                            int C, const float* scale, const float* shift, void* stream) {
-  ASF_CHECK_ARG(x && dy && dz && scale && shift && B > 0 && T > 0 && F > 0 && C > 0,
+                            int C, const float* scale, const float* shift, const uint32_t* argmax, void* stream) {
+  ASF_CHECK_ARG(dy && dz && (argmax || (x && scale && shift)) && B > 0 && T > 0 && F > 0 && C > 0,
                 "asf_bn_relu_maxpool_bwd: bad arguments");
   int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
-  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dy) && al16(x) && al16(dy) && al16(dz))
-    return bn_relu_maxpool_bwd_v8((const bf16*)x, (const bf16*)dy, ld_dy, (bf16*)dz, B, T, F, C, scale, shift,
+  if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dy) && (argmax || al16(x)) && al16(dy) && al16(dz))
+    return bn_relu_maxpool_bwd_v8((const bf16*)x, (const bf16*)dy, ld_dy, (bf16*)dz, B, T, F, C, scale, shift, argmax,
                                   (cudaStream_t)stream);
+  ASF_CHECK_ARG(!argmax, "asf_bn_relu_maxpool_bwd: arg-max codes need the bf16 vector path (C %% 8 == 0, aligned)");
   ASF_DISPATCH_DTYPE(dtype, Tt, {
     bn_relu_maxpool_bwd_kernel<Tt><<<ew_grid((int64_t)B * T * F * C), 256, 0, (cudaStream_t)stream>>>(
         (const Tt*)x, (const Tt*)dy, ld_dy, (Tt*)dz, B, T, F, C, To, Fo, scale, shift);

@@ -448,10 +448,14 @@ int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* m
 
 // ------------------------------------------------------------------------------------------- stem max-pool
 // y[b,to,fo,c] = max over the 3x3 / stride 2 / pad 1 window of relu(x*scale + shift)
+// argmax != NULL: also records, per (window, 8-channel group), one nibble per channel = position (dt+1)*3 + (df+1) of the
+// FIRST strict maximum of the positive values in scan order (15: none positive, nothing flows back through the ReLU);
+// the backward then never re-reads x.
 __global__ void __launch_bounds__(256) bn_relu_maxpool_fwd_v8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
                                                                      int64_t ld_y, int64_t nvec, int Tn, int F, int CV,
                                                                      int To, int Fo, const float* __restrict__ scale,
-                                                                     const float* __restrict__ shift) {
+                                                                     const float* __restrict__ shift,
+                                                                     uint32_t* __restrict__ argmax) {
   pdl_trigger();
   pdl_wait();
   const int C = CV * 8;
@@ -467,26 +471,37 @@ __global__ void __launch_bounds__(256) bn_relu_maxpool_fwd_v8_kernel(const bf16*
     F8 m;
 #pragma unroll
     for (int j = 0; j < 8; ++j) m.v[j] = 0.f;  // relu output is >= 0 and every window holds a valid element
+    uint32_t code = 0xffffffffu;
+#pragma unroll
     for (int dt = -1; dt <= 1; ++dt) {
       const int t = 2 * to + dt;
       if (t < 0 || t >= Tn) continue;
+#pragma unroll
       for (int df = -1; df <= 1; ++df) {
         const int f = 2 * fo + df;
         if (f < 0 || f >= F) continue;
         const F8 v = unpack8(*(const uint4*)(x + (((int64_t)b * Tn + t) * F + f) * C + c));
+        const uint32_t pos = (uint32_t)((dt + 1) * 3 + (df + 1));
 #pragma unroll
-        for (int j = 0; j < 8; ++j) m.v[j] = fmaxf(m.v[j], fmaf(v.v[j], sc.v[j], sh.v[j]));
+        for (int j = 0; j < 8; ++j) {
+          const float a = fmaf(v.v[j], sc.v[j], sh.v[j]);
+          if (a > m.v[j]) {
+            m.v[j] = a;
+            code = (code & ~(15u << (4 * j))) | (pos << (4 * j));
+          }
+        }
       }
     }
     *(uint4*)(y + orow * ld_y + c) = pack8(m);
+    if (argmax) argmax[i] = code;
   }
 }
 
 int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, int F, int C, const float* scale,
-                           const float* shift, cudaStream_t st) {
+                           const float* shift, uint32_t* argmax, cudaStream_t st) {
   const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
   const int64_t nvec = (int64_t)B * To * Fo * (C / 8);
-  ASF_CUDA(launch_pdl(bn_relu_maxpool_fwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, x, y, ld_y, nvec, T, F, C / 8, To, Fo, scale, shift));
+  ASF_CUDA(launch_pdl(bn_relu_maxpool_fwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, x, y, ld_y, nvec, T, F, C / 8, To, Fo, scale, shift, argmax));
   ASF_LAUNCH_CHECK();
   return 0;
 }
@@ -557,10 +572,61 @@ __global__ void __launch_bounds__(256) bn_relu_maxpool_bwd_v8_kernel(const bf16*
   }
 }
 
+// Backward from the forward's arg-max codes: dz[b,t,f,c] = sum of dy over the (<= 4) windows whose code names (t,f).
+__global__ void __launch_bounds__(256) maxpool_bwd_argmax_v8_kernel(const uint32_t* __restrict__ argmax,
+                                                                    const bf16* __restrict__ dy, int64_t ld_dy,
+                                                                    bf16* __restrict__ dz, int64_t nvec, int Tn, int F,
+                                                                    int CV, int To, int Fo) {
+  pdl_trigger();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % CV);
+    int64_t r = i / CV;
+    const int f = (int)(r % F);
+    r /= F;
+    const int t = (int)(r % Tn);
+    const int b = (int)(r / Tn);
+    // windows containing t: to in {t/2} if t even, {(t-1)/2, (t+1)/2} if odd (same along f)
+    const int to0 = t >> 1, nto = (t & 1) ? 2 : 1;
+    const int fo0 = f >> 1, nfo = (f & 1) ? 2 : 1;
+    uint32_t code[4];
+    uint4 dv[4];
+    uint32_t pos[4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int to = to0 + a, fo = fo0 + q;
+        const bool ok = a < nto && q < nfo && to < To && fo < Fo;
+        const int64_t w = ((int64_t)b * To + to) * Fo + fo;
+        code[a * 2 + q] = ok ? argmax[w * CV + cv] : 0xffffffffu;
+        dv[a * 2 + q] = ok ? *(const uint4*)(dy + w * ld_dy + cv * 8) : make_uint4(0, 0, 0, 0);
+        pos[a * 2 + q] = (uint32_t)((t - (2 * to - 1)) * 3 + (f - (2 * fo - 1)));
+      }
+    F8 g;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g.v[j] = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const F8 d = unpack8(dv[w]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (((code[w] >> (4 * j)) & 15u) == pos[w]) g.v[j] += d.v[j];
+    }
+    *(uint4*)(dz + i * 8) = pack8(g);
+  }
+}
+
 int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* dz, int B, int T, int F, int C,
-                           const float* scale, const float* shift, cudaStream_t st) {
+                           const float* scale, const float* shift, const uint32_t* argmax, cudaStream_t st) {
   const int To = (T + 2 - 3) / 2 + 1, Fo = (F + 2 - 3) / 2 + 1;
   const int64_t nvec = (int64_t)B * T * F * (C / 8);
+  if (argmax) {
+    ASF_CUDA(launch_pdl(maxpool_bwd_argmax_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, argmax, dy, ld_dy, dz, nvec, T, F,
+                        C / 8, To, Fo));
+    ASF_LAUNCH_CHECK();
+    return 0;
+  }
   ASF_CUDA(launch_pdl(bn_relu_maxpool_bwd_v8_kernel, dim3(vgrid(nvec)), dim3(256), 0, st, x, dy, ld_dy, dz, nvec, T, F, C / 8, To, Fo, scale, shift));
   ASF_LAUNCH_CHECK();
   return 0;

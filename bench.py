@@ -113,7 +113,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
-def _cpu_step_fn(batch, workload):
+def _cpu_step_fn(batch, workload, bn_freeze=True):
     """The oracle's CPU implementation of one step on `batch` clips (numpy log-mel + functional torch model)."""
     import numpy as np
     import torch
@@ -124,7 +124,7 @@ def _cpu_step_fn(batch, workload):
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    ocfg = M.epic_cfg(dropout=0.5, bn_freeze=False)
+    ocfg = M.epic_cfg(dropout=0.5, bn_freeze=bool(bn_freeze))
     sd = M.init_state_dict(ocfg, 0)
     wav = OL.synthetic_waveforms(batch, N_SAMPLES, 1234)
     labels = M.synthetic_labels(ocfg, batch)
@@ -161,7 +161,7 @@ def run_reference(args):
     if rank != 0:
         return
     sample = args.ref_batch
-    step, cores = _cpu_step_fn(sample, args.workload)
+    step, cores = _cpu_step_fn(sample, args.workload, args.bn_freeze)
     for _ in range(max(1, min(args.warmup, 2))):
         step()
     t0 = time.perf_counter()
@@ -190,7 +190,10 @@ def _config(args, B, n):
                                   "(BASELINE configs[1])" % args.batch,
                          "logmel": "log-mel extraction 2 s clips, batch %d/GPU (BASELINE configs[4])" % args.batch}[args.workload],
             "global_batch": args.batch * n, "clip_samples": N_SAMPLES, "frames": 400, "mels": 128,
-            "bn_freeze": bool(args.bn_freeze), "parallelism": "dp%d" % n, "cuda_graph": not args.no_graph,
+            "bn_freeze": bool(args.bn_freeze),
+            "bn_recipe": ("BN.FREEZE True as in the reference's EPIC yamls (SLOWFAST_R50.yaml:44): frozen statistics + affine "
+                          "except stems / s1_fuse" if args.bn_freeze else "all BatchNorm layers in training mode"),
+            "parallelism": "dp%d" % n, "cuda_graph": not args.no_graph,
             "l2": "inputs rotate over %d distinct batches; activations + weights + gradients of one step (> 2 GB) exceed "
                   "the 126 MB L2, so nothing survives between steps" % args.rotate}
 
@@ -357,7 +360,7 @@ def run_ours(args):
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same step on the host cores
     cpu = None
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
-        cstep, cores = _cpu_step_fn(args.ref_batch, args.workload)
+        cstep, cores = _cpu_step_fn(args.ref_batch, args.workload, args.bn_freeze)
         cstep()
         t0 = time.perf_counter()
         n = 0
@@ -403,8 +406,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="train", choices=["train", "infer", "logmel"])
     ap.add_argument("--batch", type=int, default=None, help="clips per GPU (default 64 train, 256 infer/logmel)")
-    ap.add_argument("--bn-freeze", type=int, default=0, help="1 = the EPIC fine-tuning recipe (BN.FREEZE True); "
-                    "default 0 = every BatchNorm in training mode (the harder case, SURVEY.md 8d)")
+    ap.add_argument("--bn-freeze", type=int, default=1, help="default 1 = BN.FREEZE True, the recipe of every EPIC-KITCHENS "
+                    "yaml the reference ships (models/asf/config/SLOWFAST_R50.yaml:44; train_net.py:79-80, :709-710: all "
+                    "BatchNorm layers but the stems' and s1_fuse's run on running statistics with frozen affine); "
+                    "0 = every BatchNorm in training mode (from-scratch training, BASELINE configs[3])")
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through")
     ap.add_argument("--ref-batch", type=int, default=8, help="clips per step of the CPU reference arm / baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")

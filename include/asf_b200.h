@@ -289,12 +289,16 @@ int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const
  * Pools and head.  nn.MaxPool2d([3,3],[2,2],[1,1]) of stem_helper.py:161; nn.AvgPool2d + cat + Dropout +
  * Linear (+ Softmax + mean) of audio_slowfast/models/head_helper.py:70-109.
  * ---------------------------------------------------------------------------------------------- */
-/* y[b,tp,fp,c] = max over the 3x3/s2/p1 window of relu(x*scale+shift);  x [B][T][F][C], y [B][To][Fo][C] */
+/* y[b,tp,fp,c] = max over the 3x3/s2/p1 window of relu(x*scale+shift);  x [B][T][F][C], y [B][To][Fo][C].
+ * argmax (optional, bf16 with C % 8 == 0 only): [B][To][Fo][C/8] uint32, one nibble per channel = position
+ * (dt+1)*3 + (df+1) of the window's first positive maximum (15 = none) -- what torch's MaxPool2d keeps as indices. */
 int asf_bn_relu_maxpool_fwd(const void* x, void* y, int64_t ld_y, int dtype, int B, int T, int F, int C,
-                            const float* scale, const float* shift, void* stream);
-/* dz[b,t,f,c] = (a>0) * sum over windows whose (first) argmax is (t,f) of dy;  a = relu(x*scale+shift) */
+                            const float* scale, const float* shift, uint32_t* argmax, void* stream);
+/* dz[b,t,f,c] = (a>0) * sum over windows whose (first) argmax is (t,f) of dy;  a = relu(x*scale+shift).
+ * With the forward's argmax codes the kernel reads only the codes and dy (x, scale, shift are not touched);
+ * argmax == NULL recomputes the windows from x. */
 int asf_bn_relu_maxpool_bwd(const void* x, const void* dy, int64_t ld_dy, void* dz, int dtype, int B, int T, int F,
-                            int C, const float* scale, const float* shift, void* stream);
+                            int C, const float* scale, const float* shift, const uint32_t* argmax, void* stream);
 /* feat[b][c_off + c] = mean over P positions of x[b][p][c]   (fp32 out, row pitch ld_feat) */
 int asf_avgpool_fwd(const void* x, int dtype, int B, int P, int C, float* feat, int64_t ld_feat, int c_off,
                     void* stream);

@@ -231,15 +231,26 @@ def test_stem_pool_forward_backward(dtype):
     y = torch.empty(B, To, Fo, Cn, dtype=dtype, device="cuda")
     st = L.stream_ptr()
     code = L.dtype_code(dtype)
-    L.call("asf_bn_relu_maxpool_fwd", L.ptr(xa), L.ptr(y), Cn, code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift), st)
+    L.call("asf_bn_relu_maxpool_fwd", L.ptr(xa), L.ptr(y), Cn, code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift), None, st)
     xs = nchw(xa.float()).requires_grad_(True)
     ref = F.max_pool2d(F.relu(xs * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)), 3, 2, 1)
     assert rel_err(nchw(y.float()), ref) < (1e-6 if dtype == torch.float32 else 4e-3)
     dy = torch.randn(B, To, Fo, Cn, generator=g).cuda().to(dtype)
     dz = torch.empty_like(xa)
-    L.call("asf_bn_relu_maxpool_bwd", L.ptr(xa), L.ptr(dy), Cn, L.ptr(dz), code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift), st)
+    L.call("asf_bn_relu_maxpool_bwd", L.ptr(xa), L.ptr(dy), Cn, L.ptr(dz), code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift),
+           None, st)
     torch.cuda.synchronize()
     ref.backward(nchw(dy.float()))
+    if dtype == torch.bfloat16:
+        # the production path: arg-max codes written by the forward, the backward reads only codes + dy -- bit-equal
+        # to the recomputing kernel (same first-maximum rule)
+        am = torch.empty(B, To, Fo, Cn // 8, dtype=torch.int32, device="cuda")
+        y2, dz2 = torch.empty_like(y), torch.empty_like(dz)
+        L.call("asf_bn_relu_maxpool_fwd", L.ptr(xa), L.ptr(y2), Cn, code, B, T, Fq, Cn, L.ptr(scale), L.ptr(shift),
+               L.ptr(am), st)
+        L.call("asf_bn_relu_maxpool_bwd", None, L.ptr(dy), Cn, L.ptr(dz2), code, B, T, Fq, Cn, None, None, L.ptr(am), st)
+        torch.cuda.synchronize()
+        assert torch.equal(y2, y) and torch.equal(dz2, dz)
     # dz is the gradient w.r.t. the BN output (before the scale): compare with grad_x / scale
     refdz = xs.grad / scale.view(1, -1, 1, 1)
     assert rel_err(nchw(dz.float()), refdz) < (1e-5 if dtype == torch.float32 else 1e-2)
