@@ -55,6 +55,12 @@ class TapGemm(C.Structure):
     ]
 
 
+class UnpackDesc(C.Structure):
+    _fields_ = [("dwp", C.c_void_p), ("dw", C.c_void_p), ("rscale", C.c_void_p),
+                ("O", C.c_int32), ("I", C.c_int32), ("taps", C.c_int32), ("ksplit", C.c_int32),
+                ("accumulate", C.c_int32), ("pad_", C.c_int32), ("chunk0", C.c_int64)]
+
+
 class PackDesc(C.Structure):
     _fields_ = [("w", C.c_void_p), ("packed", C.c_void_p), ("packed_t", C.c_void_p), ("rscale", C.c_void_p),
                 ("O", C.c_int32), ("I", C.c_int32), ("taps", C.c_int32), ("dtype", C.c_int32), ("chunk0", C.c_int64)]
@@ -112,6 +118,7 @@ SIGNATURES = {
     "asf_pack_weights_multi": [_P, _I, C.c_longlong, _P],
     "asf_sgd_multi": [_P, _I, C.c_longlong, _P, _F, _F, _I, _I, _P],
     "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _I, _P],
+    "asf_unpack_wgrad_multi": [_P, _I, C.c_longlong, _P],
     "asf_tapgemm_wgrad_ksplit": [C.POINTER(TapGemm)],
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],

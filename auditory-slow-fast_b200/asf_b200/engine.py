@@ -239,6 +239,8 @@ class Engine:
         self._side = None
         self._wg = [None, None]  # weight-gradient streams (one per pathway), off the dz -> dgrad critical chain
         self.wgrad_streams = os.environ.get("ASF_WGRAD_STREAMS", "1") != "0"
+        self.defer_unpack = os.environ.get("ASF_DEFER_UNPACK", "1") != "0"
+        self._pending_unpack = []
 
     # ------------------------------------------------------------------------------------------ plan
     def invalidate_weights(self):
@@ -602,10 +604,49 @@ class Engine:
             if ks < 1:
                 raise RuntimeError("asf_tapgemm_wgrad_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
             u.wg_ksplit, u.wg_ksplit_cap = ks, tg.max_ctas
+        if self._defer_unpack():
+            # own workspace per layer; the split-K reduction of a whole backward segment is ONE launch (_flush_unpacks)
+            ws = getattr(u, "wg_ws", None)
+            if ws is None or ws.numel() < ks * u.Cout * u.taps * u.Cin:
+                ws = u.wg_ws = torch.empty(ks * u.Cout * u.taps * u.Cin, dtype=torch.float32, device=self.device)
+            tg.dwp, tg.ksplit = ws.data_ptr(), ks
+            L.call("asf_tapgemm", C.byref(tg), 1, st)
+            self._pending_unpack.append((u, gview, rscale, bool(accumulate), ks))
+            return
         ws = self._wgrad_ws(ks * u.Cout * u.taps * u.Cin)
         tg.dwp, tg.ksplit = ws.data_ptr(), ks
         L.call("asf_tapgemm", C.byref(tg), 1, st)
         L.call("asf_unpack_wgrad", L.ptr(ws), L.ptr(gview), u.Cout, u.Cin, u.taps, L.ptr(rscale), int(accumulate), ks, st)
+
+    def _defer_unpack(self):
+        return self._ts() and self.wgrad_streams and self.defer_unpack
+
+    def _flush_unpacks(self):
+        """Split-K reduction + OIHW re-layout of every weight gradient computed since the last flush, in one launch
+        on the current stream (which the caller has ordered after the weight-gradient streams)."""
+        pend = self._pending_unpack
+        if not pend:
+            return
+        self._pending_unpack = []
+        key = tuple((u.name, u.wg_ws.data_ptr(), g.data_ptr(), rs.data_ptr() if rs is not None else 0, acc, ks)
+                    for u, g, rs, acc, ks in pend)
+        cache = self.__dict__.setdefault("_unpack_tables", {})
+        ent = cache.get(key)
+        if ent is None:
+            arr = (L.UnpackDesc * len(pend))()
+            chunk = 0
+            for i, (u, g, rs, acc, ks) in enumerate(pend):
+                d = arr[i]
+                d.dwp, d.dw = u.wg_ws.data_ptr(), g.data_ptr()
+                d.rscale = rs.data_ptr() if rs is not None else None
+                d.O, d.I, d.taps, d.ksplit, d.accumulate = u.Cout, u.Cin, u.taps, ks, int(acc)
+                d.chunk0 = chunk
+                chunk += -(-(u.Cout * u.Cin * u.taps) // 64)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            if len(cache) > 64:
+                cache.clear()
+            ent = cache[key] = (host.to(self.device), len(pend), chunk)
+        L.call("asf_unpack_wgrad_multi", L.ptr(ent[0]), ent[1], ent[2], L.stream_ptr())
 
     # ------------------------------------------------------------------------------------------ grads
     def _ensure_grad_buffers(self):
@@ -848,6 +889,7 @@ class Engine:
         plan, m = self.plan, self.model
         st = L.stream_ptr()
         B = plan.B
+        self._pending_unpack = []
         plan.red_flat.zero_()
         # ---- head
         plan.dfeat.zero_()
@@ -961,26 +1003,30 @@ class Engine:
             for wg in self._wg:
                 if wg is not None:
                     main.wait_stream(wg)
+        self._flush_unpacks()
         self._notify(pending + ["stems"])
 
     def _notify_joined(self, names):
-        """Two-stream mode: gradient-ready notification issued where the current (side) stream is ordered after
-        everything both pathway streams have been given so far.  The weight gradients live on the wgrad streams, so
-        the hook runs on one of those after it has been ordered behind the other and behind the current stream --
-        nothing on the dz -> dgrad chain waits."""
-        if self.grad_hook is None:
+        """Two-stream mode: gradient-ready point, issued where the current (side) stream is ordered after everything
+        both pathway streams have been given so far.  The weight gradients live on the wgrad streams, so the deferred
+        split-K reductions and the hook run on one of those after it has been ordered behind the other and behind the
+        current stream -- nothing on the dz -> dgrad chain waits."""
+        if not self.wgrad_streams:
+            if self.grad_hook is not None:
+                self.grad_hook(self, names)
+            return
+        if self.grad_hook is None and not self._pending_unpack:
             return
         cur = torch.cuda.current_stream(self.device)
-        if not self.wgrad_streams:
-            self.grad_hook(self, names)
-            return
         j = self._wg_stream(1)
         ev = torch.cuda.Event()
         ev.record(cur)
         j.wait_event(ev)
         j.wait_stream(self._wg_stream(0))
         with torch.cuda.stream(j):
-            self.grad_hook(self, names)
+            self._flush_unpacks()
+            if self.grad_hook is not None:
+                self.grad_hook(self, names)
 
     def _notify(self, names):
         if self.grad_hook is not None:

@@ -541,6 +541,50 @@ __global__ void __launch_bounds__(256) unpack_wgrad_kernel(const float* __restri
   }
 }
 
+// The same reduction for MANY layers in one launch (the engine defers the unpack of a backward segment: ~100 small
+// launches on the weight-gradient streams become a handful).  Block b owns 64 consecutive elements of the layer whose
+// chunk range contains b; four split lanes per element.
+__global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpack_desc_t* __restrict__ d, int n) {
+  __shared__ float part[256];
+  pdl_trigger();
+  int lo = 0, hi = n - 1;
+  const long long b = blockIdx.x;
+  pdl_wait();
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (d[mid].chunk0 <= b) lo = mid; else hi = mid - 1;
+  }
+  const asf_unpack_desc_t u = d[lo];
+  const int el = threadIdx.x & 63, sl = threadIdx.x >> 6;
+  const int64_t E = (int64_t)u.O * u.taps * u.I;
+  const int64_t e = (b - u.chunk0) * 64 + el;
+  float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+  if (e < E) {
+    const float* src = u.dwp + e;
+    int k = sl;
+    for (; k + 12 < u.ksplit; k += 16) {
+      v0 += src[(int64_t)k * E];
+      v1 += src[(int64_t)(k + 4) * E];
+      v2 += src[(int64_t)(k + 8) * E];
+      v3 += src[(int64_t)(k + 12) * E];
+    }
+    for (; k < u.ksplit; k += 4) v0 += src[(int64_t)k * E];
+  }
+  float v = (v0 + v1) + (v2 + v3);
+  part[threadIdx.x] = v;
+  __syncthreads();
+  if (sl == 0 && e < E) {
+    v = ((v + part[64 + el]) + part[128 + el]) + part[192 + el];
+    const int c = (int)(e % u.I);
+    const int64_t ot = e / u.I;
+    const int tp = (int)(ot % u.taps), o = (int)(ot / u.taps);
+    if (u.rscale) v *= u.rscale[o];
+    const int64_t dst = ((int64_t)o * u.I + c) * u.taps + tp;
+    if (u.accumulate) v += u.dw[dst];
+    u.dw[dst] = v;
+  }
+}
+
 // Stem weight gradient (C_in = 1): dw[n][tap] = sum_rows dout[row][n] * in[row shifted by tap].
 // block = 256 threads = RL row-lanes x Cout channels; each thread keeps all taps (<= 35) in registers while it
 // streams its rows (dout coalesced along n, the input sample is a warp broadcast); row-lanes are folded in smem
@@ -872,6 +916,13 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_
     ASF_LAUNCH_CHECK();
     return 0;
   });
+}
+
+int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long total_chunks, void* stream) {
+  ASF_CHECK_ARG(descs_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_unpack_wgrad_multi: bad arguments");
+  ASF_CUDA(launch_pdl(unpack_wgrad_multi_kernel, dim3((unsigned)total_chunks), dim3(256), 0, (cudaStream_t)stream, descs_dev, n));
+  ASF_LAUNCH_CHECK();
+  return 0;
 }
 
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,

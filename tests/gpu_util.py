@@ -36,6 +36,8 @@ class Harness(Engine):
         self._side = None
         self._wg = [None, None]
         self.wgrad_streams = False
+        self.defer_unpack = False
+        self._pending_unpack = []
 
 
 def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, in_scale=1.0):
