@@ -237,7 +237,9 @@ class Engine:
         split = os.environ.get("ASF_SM_SPLIT", "0,0").split(",")  # 0 = no cap: CTAs of both streams share all SMs
         self.sm_split = (int(split[0]), int(split[1]))
         self._side = None
-        self._wg = [None, None]  # weight-gradient streams (one per pathway), off the dz -> dgrad critical chain
+        self._wg = {}  # weight-gradient streams (wg_per_path per pathway, round robin), off the dz -> dgrad chain
+        self.wg_per_path = max(1, int(os.environ.get("ASF_WG_PER_PATH", "2")))
+        self._wg_rr = [0, 0]
         self.wgrad_streams = os.environ.get("ASF_WGRAD_STREAMS", "1") != "0"
         self.defer_unpack = os.environ.get("ASF_DEFER_UNPACK", "1") != "0"
         self._pending_unpack = []
@@ -483,11 +485,15 @@ class Engine:
             self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_SIDE_PRIO", "0")))
         return self._side
 
-    def _wg_stream(self, path):
-        if self._wg[path] is None:
-            # lower priority than the pathway streams: dgrad / BN backward feed the next layer, wgrad feeds nobody
-            self._wg[path] = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_WG_PRIO", "0")))
-        return self._wg[path]
+    def _wg_stream(self, path, advance=False):
+        """Weight-gradient stream of a pathway (round robin over wg_per_path streams when ``advance``)."""
+        idx = self._wg_rr[path]
+        if advance:
+            self._wg_rr[path] = (idx + 1) % self.wg_per_path
+        key = (path, idx)
+        if key not in self._wg:
+            self._wg[key] = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_WG_PRIO", "0")))
+        return self._wg[key]
 
     def _on(self, path):
         """Context that issues work of pathway ``path`` on its stream (fast pathway -> side stream)."""
@@ -641,7 +647,7 @@ class Engine:
                 d.rscale = rs.data_ptr() if rs is not None else None
                 d.O, d.I, d.taps, d.ksplit, d.accumulate = u.Cout, u.Cin, u.taps, ks, int(acc)
                 d.chunk0 = chunk
-                chunk += -(-(u.Cout * u.Cin * u.taps) // 64)
+                chunk += -(-(u.Cout * u.Cin * u.taps) // 1024)  # ASF_UNPACK_CHUNK
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             if len(cache) > 64:
                 cache.clear()
@@ -687,7 +693,7 @@ class Engine:
         by asf_unpack_wgrad on the same stream): one grow-only buffer per stream, shared by the layers issued on it."""
         cur = torch.cuda.current_stream(self.device)  # one workspace per issuing stream
         key = 0
-        for i, s_ in enumerate((self._side, self._wg[0], self._wg[1])):
+        for i, s_ in enumerate([self._side] + [self._wg[k] for k in sorted(self._wg)]):
             if s_ is not None and cur == s_:
                 key = i + 1
         ws = self._ws.get(key)
@@ -874,7 +880,7 @@ class Engine:
         if gview is not None:
             if self._ts() and self.wgrad_streams and not u.is_stem:
                 # dW needs dconv and the saved input only; nothing downstream in this pass reads it
-                wg = self._wg_stream(u.path)
+                wg = self._wg_stream(u.path, advance=True)
                 ev = torch.cuda.Event()
                 ev.record(torch.cuda.current_stream(self.device))
                 wg.wait_event(ev)
@@ -1000,9 +1006,8 @@ class Engine:
                 self._unit_backward(u, dz, False, False)
         if ts:
             main.wait_stream(side)  # join
-            for wg in self._wg:
-                if wg is not None:
-                    main.wait_stream(wg)
+            for wg in self._wg.values():
+                main.wait_stream(wg)
         self._flush_unpacks()
         self._notify(pending + ["stems"])
 
@@ -1022,7 +1027,9 @@ class Engine:
         ev = torch.cuda.Event()
         ev.record(cur)
         j.wait_event(ev)
-        j.wait_stream(self._wg_stream(0))
+        for wg in self._wg.values():
+            if wg is not j:
+                j.wait_stream(wg)
         with torch.cuda.stream(j):
             self._flush_unpacks()
             if self.grad_hook is not None:

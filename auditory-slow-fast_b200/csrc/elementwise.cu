@@ -542,10 +542,11 @@ __global__ void __launch_bounds__(256) unpack_wgrad_kernel(const float* __restri
 }
 
 // The same reduction for MANY layers in one launch (the engine defers the unpack of a backward segment: ~100 small
-// launches on the weight-gradient streams become a handful).  Block b owns 64 consecutive elements of the layer whose
-// chunk range contains b; four split lanes per element.
+// launches on the weight-gradient streams become a handful).  Block b owns ASF_UNPACK_CHUNK (1024) consecutive elements
+// of the layer whose chunk range contains b: 64 lanes x float4 per pass, four split lanes per element group (lane j
+// adds partial tiles j, j + 4, ... in ascending order, then the lanes are folded in a fixed order).
 __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpack_desc_t* __restrict__ d, int n) {
-  __shared__ float part[256];
+  __shared__ float4 part[256];
   pdl_trigger();
   int lo = 0, hi = n - 1;
   const long long b = blockIdx.x;
@@ -557,31 +558,48 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpac
   const asf_unpack_desc_t u = d[lo];
   const int el = threadIdx.x & 63, sl = threadIdx.x >> 6;
   const int64_t E = (int64_t)u.O * u.taps * u.I;
-  const int64_t e = (b - u.chunk0) * 64 + el;
-  float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
-  if (e < E) {
-    const float* src = u.dwp + e;
-    int k = sl;
-    for (; k + 12 < u.ksplit; k += 16) {
-      v0 += src[(int64_t)k * E];
-      v1 += src[(int64_t)(k + 4) * E];
-      v2 += src[(int64_t)(k + 8) * E];
-      v3 += src[(int64_t)(k + 12) * E];
+  const int64_t e0 = (b - u.chunk0) * ASF_UNPACK_CHUNK;
+#pragma unroll 1
+  for (int pass = 0; pass < ASF_UNPACK_CHUNK / 256; ++pass) {
+    const int64_t e = e0 + pass * 256 + el * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f), w = v;
+    if (e < E) {
+      const float* src = u.dwp + e;
+      int k = sl;
+      for (; k + 4 < u.ksplit; k += 8) {
+        const float4 a = *(const float4*)(src + (int64_t)k * E);
+        const float4 c = *(const float4*)(src + (int64_t)(k + 4) * E);
+        v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+        w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w;
+      }
+      if (k < u.ksplit) {
+        const float4 a = *(const float4*)(src + (int64_t)k * E);
+        v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+      }
+      v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
     }
-    for (; k < u.ksplit; k += 4) v0 += src[(int64_t)k * E];
-  }
-  float v = (v0 + v1) + (v2 + v3);
-  part[threadIdx.x] = v;
-  __syncthreads();
-  if (sl == 0 && e < E) {
-    v = ((v + part[64 + el]) + part[128 + el]) + part[192 + el];
-    const int c = (int)(e % u.I);
-    const int64_t ot = e / u.I;
-    const int tp = (int)(ot % u.taps), o = (int)(ot / u.taps);
-    if (u.rscale) v *= u.rscale[o];
-    const int64_t dst = ((int64_t)o * u.I + c) * u.taps + tp;
-    if (u.accumulate) v += u.dw[dst];
-    u.dw[dst] = v;
+    if (pass) __syncthreads();  // the previous pass has finished reading `part`
+    part[threadIdx.x] = v;
+    __syncthreads();
+    if (sl == 0 && e < E) {
+      float r[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 1; j < 4; ++j) {
+        const float4 q = part[j * 64 + el];
+        r[0] += q.x; r[1] += q.y; r[2] += q.z; r[3] += q.w;
+      }
+      const int c = (int)(e % u.I);  // I % 4 == 0: the four elements share (o, tap)
+      const int64_t ot = e / u.I;
+      const int tp = (int)(ot % u.taps), o = (int)(ot / u.taps);
+      const float sc = u.rscale ? u.rscale[o] : 1.f;
+      float* dst = u.dw + ((int64_t)o * u.I + c) * u.taps + tp;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float x = r[j] * sc;
+        if (u.accumulate) x += dst[(int64_t)j * u.taps];
+        dst[(int64_t)j * u.taps] = x;
+      }
+    }
   }
 }
 
@@ -920,6 +938,7 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_
 
 int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long total_chunks, void* stream) {
   ASF_CHECK_ARG(descs_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_unpack_wgrad_multi: bad arguments");
+  // (every layer: I % 4 == 0 and 16-byte aligned dwp -- the tap-GEMM wgrad already requires I % 8 == 0)
   ASF_CUDA(launch_pdl(unpack_wgrad_multi_kernel, dim3((unsigned)total_chunks), dim3(256), 0, (cudaStream_t)stream, descs_dev, n));
   ASF_LAUNCH_CHECK();
   return 0;

@@ -249,7 +249,8 @@ int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
                      int accumulate, int ksplit, void* stream);
 /* The same for many layers in one launch.  descs_dev: DEVICE array of n descriptors sorted by chunk0, where unit i owns
- * the blocks [chunk0_i, chunk0_{i+1}) of 64 destination elements each (chunks_i = ceil(O*I*taps / 64)). */
+ * the blocks [chunk0_i, chunk0_{i+1}) of ASF_UNPACK_CHUNK destination elements each (chunks_i = ceil(O*I*taps /
+ * ASF_UNPACK_CHUNK)); I % 4 == 0 and dwp 16-byte aligned. */
 typedef struct {
   const float* dwp;    /* [ksplit][O][taps][I] partial tiles */
   float* dw;           /* OIHW fp32 gradient */
@@ -257,7 +258,7 @@ typedef struct {
   int32_t O, I, taps, ksplit, accumulate, pad_;
   int64_t chunk0;
 } asf_unpack_desc_t;
-#define ASF_UNPACK_CHUNK 64
+#define ASF_UNPACK_CHUNK 1024
 int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long total_chunks, void* stream);
 
 /* ------------------------------------------------------------------------------------------------

@@ -34,7 +34,9 @@ class Harness(Engine):
         self.two_stream = False
         self.sm_split = (0, 0)
         self._side = None
-        self._wg = [None, None]
+        self._wg = {}
+        self.wg_per_path = 1
+        self._wg_rr = [0, 0]
         self.wgrad_streams = False
         self.defer_unpack = False
         self._pending_unpack = []
