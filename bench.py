@@ -55,6 +55,18 @@ def _peaks():
     return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
 
 
+def _ncu_traffic(kernel, bn_freeze):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu pass of one training
+    step (profiles/r01_dram_traffic.json, written by tools/ncu_traffic.py); None when no capture matches this workload."""
+    path = os.path.join(ROOT, "profiles", "r01_dram_traffic.json")
+    if not os.path.exists(path) or bn_freeze is None:
+        return None
+    with open(path) as f:
+        d = json.load(f)
+    ent = d.get("bn_freeze_%d" % int(bn_freeze), {}).get(kernel)
+    return ent["dram_bytes_per_launch"] if ent else None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -332,6 +344,12 @@ def run_ours(args):
     roof = None
     if args.workload != "logmel":
         psteps = min(args.steps, 5)
+        # per-launch events need every launch alone on its stream: the instrumented passes run the engine single-stream
+        # (the timed runs above use the two-stream / weight-gradient-stream schedule, where launches overlap)
+        eng = getattr(net, "engine", None)
+        saved_ts = getattr(eng, "two_stream", None)
+        if eng is not None:
+            eng.two_stream = False
         L.call("asf_prof_start", 4096 * psteps)
         for i in range(psteps):
             if train:
@@ -342,11 +360,14 @@ def run_ours(args):
         torch.cuda.synchronize()
         pms, pfl, pn = (C.c_double * 2)(), (C.c_double * 2)(), (C.c_longlong * 2)()
         L.call("asf_prof_stop", pms, pfl, pn)
+        if eng is not None:
+            eng.two_stream = saved_ts
         if pn[0] > 0:
             ach = pfl[0] / (pms[0] * 1e-3) / 1e12
-            roof = {"bound": "tensor", "kernel": "tapgemm_fwd_kernel (tcgen05 implicit-GEMM conv forward + dgrad)",
+            roof = {"bound": "tensor", "kernel": "tapgemm_fwd_tma_kernel (tcgen05 implicit-GEMM conv forward + dgrad)",
                     "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s", "frac": ach / peaks["bf16_sustained"],
-                    "peak_source": peaks["source"] + " sustained bf16 (kernel timed inside a long step)", "traffic": None,
+                    "peak_source": peaks["source"] + " sustained bf16 (kernel timed inside a long step)",
+                    "traffic": _ncu_traffic("tapgemm_fwd_tma_kernel", bool(args.bn_freeze) if train else None),
                     "launches_per_step": pn[0] / psteps, "kernel_ms_per_step": pms[0] / psteps,
                     "wgrad_kernel": {"achieved": (pfl[1] / (pms[1] * 1e-3) / 1e12) if pn[1] else None,
                                      "launches_per_step": pn[1] / psteps, "kernel_ms_per_step": pms[1] / psteps},

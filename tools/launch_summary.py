@@ -7,12 +7,14 @@ rows = list(csv.reader(open(sys.argv[1])))
 hdr = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
 h = rows[hdr]
 ki, vi = h.index("Kernel Name"), h.index("Metric Value")
+mi, ui = h.index("Metric Name"), h.index("Metric Unit")
+SCALE = {"ns": 1.0, "nsecond": 1.0, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6}
 d = collections.defaultdict(lambda: [0, 0.0])
 for r in rows[hdr + 1:]:
-    if len(r) <= vi:
+    if len(r) <= vi or not r[mi].startswith("gpu__time_duration"):
         continue
     try:
-        v = float(r[vi].replace(",", ""))
+        v = float(r[vi].replace(",", "")) * SCALE.get(r[ui], 1.0)
     except ValueError:
         continue
     name = r[ki].split("(")[0].replace("void ", "")[:70]
