@@ -237,6 +237,7 @@ class Engine:
         split = os.environ.get("ASF_SM_SPLIT", "0,0").split(",")  # 0 = no cap: CTAs of both streams share all SMs
         self.sm_split = (int(split[0]), int(split[1]))
         self._side = None
+        self._slow = None
         self._wg = {}  # weight-gradient streams (wg_per_path per pathway, round robin), off the dz -> dgrad chain
         self.wg_per_path = max(1, int(os.environ.get("ASF_WG_PER_PATH", "2")))
         self._wg_rr = [0, 0]
@@ -482,8 +483,15 @@ class Engine:
 
     def _side_stream(self):
         if self._side is None:
-            self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_SIDE_PRIO", "0")))
+            self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_PATH_PRIO", "0")))
         return self._side
+
+    def _slow_stream(self):
+        """The slow pathway's stream.  Both pathway streams outrank the weight-gradient streams, so that when an SM
+        frees up the next dgrad / forward CTA (which the following layer waits for) is placed before a wgrad CTA."""
+        if self._slow is None:
+            self._slow = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_PATH_PRIO", "0")))
+        return self._slow
 
     def _wg_stream(self, path, advance=False):
         """Weight-gradient stream of a pathway (round robin over wg_per_path streams when ``advance``)."""
@@ -497,8 +505,8 @@ class Engine:
 
     def _on(self, path):
         """Context that issues work of pathway ``path`` on its stream (fast pathway -> side stream)."""
-        if path == 1 and self._ts():
-            return torch.cuda.stream(self._side_stream())
+        if self._ts():
+            return torch.cuda.stream(self._side_stream() if path == 1 else self._slow_stream())
         return contextlib.nullcontext()
 
     def _cap(self, u):
@@ -693,7 +701,7 @@ class Engine:
         by asf_unpack_wgrad on the same stream): one grow-only buffer per stream, shared by the layers issued on it."""
         cur = torch.cuda.current_stream(self.device)  # one workspace per issuing stream
         key = 0
-        for i, s_ in enumerate([self._side] + [self._wg[k] for k in sorted(self._wg)]):
+        for i, s_ in enumerate([self._side, self._slow] + [self._wg[k] for k in sorted(self._wg)]):
             if s_ is not None and cur == s_:
                 key = i + 1
         ws = self._ws.get(key)
@@ -780,10 +788,12 @@ class Engine:
             plan.stats_flat.zero_()
         self._prepare_all(training)
         ts = self._ts()
-        main = torch.cuda.current_stream(self.device)
-        side = self._side_stream() if ts else None
+        cur = torch.cuda.current_stream(self.device)
+        main = self._slow_stream() if ts else cur   # the slow pathway's stream
+        side = self._side_stream() if ts else None  # the fast pathway's stream
         if ts:
-            side.wait_stream(main)  # fork: inputs, zeroed statistics and refreshed weights are ready on `main`
+            main.wait_stream(cur)  # fork: inputs, zeroed statistics and refreshed weights are ready on `cur`
+            side.wait_stream(cur)
         # stems
         for p, u in enumerate(plan.stems):
             with self._on(p):
@@ -823,7 +833,8 @@ class Engine:
                     self._unit_forward(item["b"], training, True)
                     self._unit_forward(item["c"], training, True)
         if ts:
-            main.wait_stream(side)  # join
+            cur.wait_stream(main)  # join
+            cur.wait_stream(side)
         st = L.stream_ptr()
         # head
         head = m.head
@@ -939,10 +950,12 @@ class Engine:
             return fresh
 
         ts = self._ts()
-        main = torch.cuda.current_stream(self.device)
+        cur = torch.cuda.current_stream(self.device)
+        main = self._slow_stream() if ts else cur
         side = self._side_stream() if ts else None
         if ts:
-            side.wait_stream(main)  # fork: head gradients / pooled gradients of both pathways are on `main`
+            main.wait_stream(cur)  # fork: head gradients / pooled gradients of both pathways are on `cur`
+            side.wait_stream(cur)
         pending = []  # two-stream mode: units finished since the last point where both streams were ordered
         for kind, item in reversed(plan.order):
             if kind == "fuse":
@@ -1005,9 +1018,10 @@ class Engine:
                     u.raw = u.y  # the stem keeps its raw conv output in u.y
                 self._unit_backward(u, dz, False, False)
         if ts:
-            main.wait_stream(side)  # join
+            cur.wait_stream(main)  # join
+            cur.wait_stream(side)
             for wg in self._wg.values():
-                main.wait_stream(wg)
+                cur.wait_stream(wg)
         self._flush_unpacks()
         self._notify(pending + ["stems"])
 

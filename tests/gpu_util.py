@@ -34,6 +34,7 @@ class Harness(Engine):
         self.two_stream = False
         self.sm_split = (0, 0)
         self._side = None
+        self._slow = None
         self._wg = {}
         self.wg_per_path = 1
         self._wg_rr = [0, 0]
