@@ -123,6 +123,8 @@ template <bool STATS>
 __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const __grid_constant__ TgParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   pdl_trigger();
+  unsigned long long gt_entry = 0;
+  if (p.dbg && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt_entry));
   uint8_t* smem = smem_raw;  // 1024-byte aligned (128B-swizzle atoms); checked below
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int b_bytes = p.block_n * 128;
@@ -167,6 +169,12 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   pdl_wait();  // everything above touched only shared memory, TMEM and kernel parameters
   Probe pb{p.dbg, 0}, pb_all{p.dbg, 0};
   if (threadIdx.x == 0) pb_all.begin();
+  if (p.dbg && threadIdx.x == 0) {
+    unsigned long long g1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1));
+    atomicAdd(p.dbg + 9, g1 - gt_entry);
+    atomicMin(p.dbg + 11, gt_entry);
+  }
 
   if (warp == 0 || warp == 10) {
     // ===== TMA producers: warp 0 streams the activation boxes, warp 10 the weight boxes.  One thread issuing both
@@ -408,6 +416,11 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
+  }
+  if (p.dbg && threadIdx.x == 0) {
+    unsigned long long g3;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g3));
+    atomicMax(p.dbg + 12, g3);
   }
   if (stats_smem && threadIdx.x >= 64 && threadIdx.x < 320) {
     for (int i = (int)threadIdx.x - 64; i < p.N; i += 256) {

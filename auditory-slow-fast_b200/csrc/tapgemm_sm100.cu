@@ -522,13 +522,25 @@ static int debug_sync(cudaStream_t st) {
   return 0;
 }
 
+#include "narrow_wgrad.cuh"
+
 // wgrad tiling: 64-row boxes (half of the 128-row M tile, split on its slowest boxed dim), output-channel tile of one
 // or two 128-row halves, input-channel tile <= 256, split-K so that about one wave of CTAs is in flight.
 struct WgPlan {
   int box[3];
   int halves, tn, ny, nx, r_tiles, c_tiles, tmem_cols, stages, ksplit, m_tiles;
+  int narrow, narrow_rows;  // CUDA-core path for the narrow layers (narrow_wgrad.cuh): ksplit = its CTA count
 };
 static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
+  w->narrow = 0;
+  {
+    int ks = 0, rpc = 0;  // a caller-chosen ksplit other than the plan's keeps the layer on the tensor-core kernel
+    if (narrow_wgrad_plan(q, &ks, &rpc) && (q->ksplit <= 0 || q->ksplit == ks)) {
+      w->narrow = 1;
+      w->narrow_rows = rpc;
+      w->ksplit = ks;
+    }
+  }
   int prod = 1;
   for (int j = 0; j < 3; ++j) {
     w->box[j] = q->m_box[j];
@@ -566,7 +578,7 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   int ks = (int)cdiv(sm_budget(q), base_tiles);
   if (ks > w->m_tiles / 4) ks = w->m_tiles / 4;  // at least four 64-row stages of MMA work per partial tile
   if (ks < 1) ks = 1;
-  w->ksplit = ks;
+  if (!w->narrow) w->ksplit = ks;
   return 0;
 }
 
@@ -768,6 +780,19 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   WgPlan wp;
   rc = wgrad_plan(q, &wp);
   if (rc) return rc;
+  if (wp.narrow) {
+    const double nflops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
+    ProfRec* npr = prof_begin(st, 1, nflops);
+    if (npr) {
+      npr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; npr->N = q->N; npr->K = q->K; npr->taps = q->ntaps;
+      npr->block_n = wp.ksplit; npr->grid = wp.ksplit;
+    }
+    rc = narrow_wgrad_launch(q, wp.ksplit, wp.narrow_rows, st);
+    if (rc) return rc;
+    prof_end(npr, st);
+    ASF_LAUNCH_CHECK();
+    return debug_sync(st);
+  }
   // re-tile the M-space with the 64-row boxes of the plan
   p.m_tiles_total = 1;
   for (int j = 0; j < 3; ++j) {

@@ -144,6 +144,42 @@ def test_tapgemm_wgrad(h_tc, case):
     assert rel_err(g, 2 * ref) < 5e-3
 
 
+# Narrow layers with >= 16384 output positions take the CUDA-core weight-gradient kernel (csrc/narrow_wgrad.cuh): same
+# entry point, same partial-tile workspace, every conv class of the fast pathway incl. strides, laterals and a
+# concat-slice input pitch.
+NARROW_CASES = [
+    ("1x3_c8", 8, 100, 32, 8, 8, (1, 3), (1, 1), (0, 1), None),
+    ("3x1_32to8", 8, 100, 32, 32, 8, (3, 1), (1, 1), (1, 0), None),
+    ("1x1_8to32", 8, 100, 32, 8, 32, (1, 1), (1, 1), (0, 0), None),
+    ("1x3_c16", 16, 100, 16, 16, 16, (1, 3), (1, 1), (0, 1), None),
+    ("1x1_64to16", 16, 100, 16, 64, 16, (1, 1), (1, 1), (0, 0), None),
+    ("3x1_16to32_pitch80", 16, 100, 16, 16, 32, (3, 1), (1, 1), (1, 0), 80),
+    ("1x1s2_32to64", 16, 100, 32, 32, 64, (1, 1), (1, 2), (0, 0), None),
+    ("1x3s2_c16", 12, 100, 32, 16, 16, (1, 3), (1, 2), (0, 1), None),
+    ("7x1s4_lat_8to16", 24, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0), None),
+]
+
+
+@pytest.mark.parametrize("case", NARROW_CASES, ids=[c[0] for c in NARROW_CASES])
+def test_narrow_wgrad(h_tc, case):
+    _, B, T, Fq, cin, cout, k, s, p, ld_in = case
+    u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=6, ld_in=ld_in)
+    dy = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+    dy.buf.copy_(torch.randn(dy.buf.shape, device="cuda"))
+    g = torch.zeros_like(w)
+    h_tc._conv_wgrad(u, dy, None, g, accumulate=False)
+    torch.cuda.synchronize()
+    rows = u.y.B * u.y.T * u.y.F
+    assert u.wg_ksplit == -(-rows // max(512, -(-rows // (2 * 148 * 128)) * 128)), \
+        "expected the CUDA-core narrow-layer kernel's CTA count as ksplit, got %d" % u.wg_ksplit
+    wr = w.clone().requires_grad_(True)
+    _ref_conv(x, wr, s, p).backward(nchw(dy.view().float()))
+    assert rel_err(g, wr.grad) < 5e-3, rel_err(g, wr.grad)
+    h_tc._conv_wgrad(u, dy, None, g, accumulate=True)
+    torch.cuda.synchronize()
+    assert rel_err(g, 2 * wr.grad) < 5e-3
+
+
 def test_tapgemm_concat_slice_output(h_tc):
     """the lateral conv writes into channels [64:80) of the slow buffer (no torch.cat)."""
     u, x, w = make_unit(h_tc, 2, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0), seed=5, ld_out=80)

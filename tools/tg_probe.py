@@ -69,13 +69,16 @@ def main():
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) / 5 * 1e3
             cnt.zero_()
+            cnt[11] = 2 ** 62
             L.call("asf_tapgemm_probe", L.ptr(cnt))
             fn()
             torch.cuda.synchronize()
             L.call("asf_tapgemm_probe", None)
             c = cnt.cpu().tolist()
             n = max(c[8], 1)
-            print("%-20s %-10s %7.1f | %s   (CTAs %d)" % (name, mode, us, " ".join("%15.1f" % (c[i] / n / 1e3) for i in range(8)), c[8]))
+            print("%-20s %-10s %7.1f | %s   (CTAs %d)  entry->body %.2f us, first entry->last exit %.2f us"
+                  % (name, mode, us, " ".join("%15.1f" % (c[i] / n / 1e3) for i in range(8)), c[8], c[9] / n / 1e3,
+                     (c[12] - c[11]) / 1e3))
 
 
 if __name__ == "__main__":
