@@ -147,6 +147,8 @@ def _declare(l):
         fn.restype = C.c_int
     l.asf_launch_count.argtypes = []
     l.asf_launch_count.restype = C.c_longlong
+    l.asf_narrow_conv_launches.argtypes = []
+    l.asf_narrow_conv_launches.restype = C.c_longlong
 
 
 def call(name, *args):

@@ -523,6 +523,7 @@ static int debug_sync(cudaStream_t st) {
 }
 
 #include "narrow_wgrad.cuh"
+#include "narrow_conv.cuh"
 
 // wgrad tiling: 64-row boxes (half of the 128-row M tile, split on its slowest boxed dim), output-channel tile of one
 // or two 128-row halves, input-channel tile <= 256, split-K so that about one wave of CTAs is in flight.
@@ -591,11 +592,15 @@ extern "C" int asf_tapgemm_probe(unsigned long long* dev_counters) {
   return 0;
 }
 
+extern "C" long long asf_narrow_conv_launches(void) { return g_narrow_conv_launches; }
+
 extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
   ASF_CHECK_ARG(q && (mode == 0 || mode == 1), "asf_tapgemm: bad mode");
   ASF_CHECK_ARG(q->a && q->nd >= 1 && q->nd <= 4 && q->K > 0 && q->K % 8 == 0 && q->N > 0,
                 "asf_tapgemm: bad A description (nd %d, K %d, N %d)", q->nd, q->K, q->N);
   ASF_CHECK_ARG(q->ntaps >= 1 && q->ntaps <= ASF_MAX_TAPS && q->ntaps_w >= 1, "asf_tapgemm: bad tap count");
+  if (mode == 0 && q->bw && q->out && q->ld_out >= q->N && narrow_conv_ok(q))
+    return narrow_conv_launch(q, (cudaStream_t)stream);
   static TgParams p;  // large POD; filled per call (the launch copies it)
   memset(&p, 0, sizeof(p));
   p.dbg = g_probe;

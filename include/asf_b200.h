@@ -158,6 +158,11 @@ int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout
  *         own tensor map (y_*).  The rows are split over `ksplit` groups of CTAs; group k WRITES (no atomics, no
  *         pre-zeroing) its partial sums to dwp[k][N][ntaps_w][K] at tap b_tap[tap]; asf_unpack_wgrad adds the
  *         groups.  ksplit = 0 lets the launcher choose -- query it first with asf_tapgemm_wgrad_ksplit to size dwp.
+ *
+ * Narrow layers (N, K powers of two in 8..64, >= 16384 output positions: the fast pathway) do not fill a 128-row MMA
+ * tile; both modes route them to CUDA-core kernels behind this same entry point (mode 0: csrc/narrow_conv.cuh when
+ * N*K*ntaps <= 8192 and the output is bf16; mode 1: csrc/narrow_wgrad.cuh, ksplit = its CTA count).
+ * asf_narrow_conv_launches() counts the mode-0 launches that took that route (tests use it to prove coverage).
  */
 typedef struct {
   const void* a;      /* bf16 */
@@ -195,6 +200,7 @@ int asf_tapgemm(const asf_tapgemm_t* p, int mode, void* stream);
  * a free accumulator, [4] epilogue waiting for accumulators, [5] epilogue busy per tile, [6] epilogue waiting for
  * its store buffer, [7] final store drain, [8] CTAs.  NULL switches the probe off (default). */
 int asf_tapgemm_probe(unsigned long long* dev_counters);
+long long asf_narrow_conv_launches(void);
 /* the ksplit asf_tapgemm(p, 1, ...) uses when p->ksplit == 0 (>= 1), or a negative error code */
 int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* p);
 

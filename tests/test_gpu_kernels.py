@@ -180,6 +180,82 @@ def test_narrow_wgrad(h_tc, case):
     assert rel_err(g, 2 * wr.grad) < 5e-3
 
 
+def _narrow_count():
+    from asf_b200 import _lib as L
+    return int(L.lib().asf_narrow_conv_launches())
+
+
+@pytest.mark.parametrize("case", NARROW_CASES, ids=[c[0] for c in NARROW_CASES])
+def test_narrow_conv_forward_and_dgrad(h_tc, case, monkeypatch):
+    """csrc/narrow_conv.cuh behind asf_tapgemm mode 0: fused-affine forward (+ residual, ReLU), batch-statistics
+    forward and dgrad (+ accumulate, ReLU mask) against torch, and against the tensor-core kernel on the same inputs
+    (both accumulate in fp32 and round once to bf16, so they agree to a bf16 ulp)."""
+    _, B, T, Fq, cin, cout, k, s, p, ld_in = case
+
+    def run_all(tag):
+        out = {}
+        u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=7, ld_in=ld_in)
+        u.bn.eval()
+        res = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+        res.buf.copy_(torch.randn(res.buf.shape, generator=torch.Generator("cuda").manual_seed(1), device="cuda"))
+        u.res = res
+        h_tc._unit_forward(u, training=False)
+        torch.cuda.synchronize()
+        out["fwd"] = nchw(u.y.view().float()).clone()
+        scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+        shift = u.bn.bias - u.bn.running_mean * scale
+        w_seen = (w * scale.view(-1, 1, 1, 1)).to(torch.bfloat16).float()
+        out["fwd_ref"] = F.relu(_ref_conv(x, w_seen, s, p) + shift.view(1, -1, 1, 1) + nchw(res.view().float()))
+        # dgrad with accumulate + mask
+        h_tc._prepare_unit(u, training=True)
+        dy = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+        dy.buf.copy_(torch.randn(dy.buf.shape, generator=torch.Generator("cuda").manual_seed(2), device="cuda"))
+        dx = u.x.grad
+        dx.buf.copy_(torch.randn(dx.buf.shape, generator=torch.Generator("cuda").manual_seed(3), device="cuda"))
+        prev = nchw(dx.view().float()).clone()
+        covered = not (k == (1, 1) and s != (1, 1))
+        h_tc._conv_dgrad(u, dy, dx, accumulate=True, mask=u.x if covered else None)
+        torch.cuda.synchronize()
+        out["dgrad"] = nchw(dx.view().float()).clone()
+        xr = x.clone().requires_grad_(True)
+        _ref_conv(xr, w_seen, s, p).backward(nchw(dy.view().float()))
+        ref = xr.grad + prev
+        out["dgrad_ref"] = ref * (x > 0) if covered else ref
+        # batch statistics
+        u2, x2, w2 = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=8, ld_in=ld_in)
+        u2.bn.train()
+        h_tc._unit_forward(u2, training=True)
+        torch.cuda.synchronize()
+        conv = _ref_conv(x2, w2.to(torch.bfloat16).float(), s, p)
+        out["mean"], out["invstd"] = u2.mean.clone(), u2.invstd.clone()
+        out["mean_ref"] = conv.mean((0, 2, 3))
+        out["invstd_ref"] = 1.0 / torch.sqrt(conv.var((0, 2, 3), unbiased=False) + u2.bn.eps)
+        out["bn"] = nchw(u2.y.view().float()).clone()
+        out["bn_ref"] = F.relu(F.batch_norm(conv, None, None, u2.bn.weight, u2.bn.bias, True, 0.1, u2.bn.eps))
+        out["amax"] = float(conv.abs().max())
+        return out
+
+    monkeypatch.setenv("ASF_NARROW_CONV", "1")
+    n0 = _narrow_count()
+    a = run_all("narrow")
+    taken = _narrow_count() - n0
+    assert taken >= 3, "forward, dgrad and batch-stat forward should take the CUDA-core narrow kernel (%d did)" % taken
+    monkeypatch.setenv("ASF_NARROW_CONV", "0")
+    n1 = _narrow_count()
+    b = run_all("tensor-core")
+    assert _narrow_count() == n1
+    assert rel_err(a["fwd"], a["fwd_ref"]) < 6e-3
+    assert max_err(a["fwd"], a["fwd_ref"]) <= 2e-2 * float(a["fwd_ref"].abs().max())
+    assert rel_err(a["dgrad"], a["dgrad_ref"]) < 1e-2
+    assert torch.allclose(a["mean"], a["mean_ref"], atol=2e-3 * a["amax"])
+    assert torch.allclose(a["invstd"], a["invstd_ref"], rtol=5e-3)
+    assert rel_err(a["bn"], a["bn_ref"]) < 1e-2
+    # the two kernels differ only in fp32 summation order before one bf16 rounding
+    for key in ("fwd", "dgrad", "bn"):
+        assert rel_err(a[key], b[key]) < 3e-3, (key, rel_err(a[key], b[key]))
+    assert torch.allclose(a["mean"], b["mean"], atol=1e-4 * a["amax"])
+
+
 def test_tapgemm_concat_slice_output(h_tc):
     """the lateral conv writes into channels [64:80) of the slow buffer (no torch.cat)."""
     u, x, w = make_unit(h_tc, 2, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0), seed=5, ld_out=80)
