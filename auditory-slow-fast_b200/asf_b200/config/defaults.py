@@ -149,6 +149,9 @@ _C.DIST_BACKEND = "nccl"
 # --- additive (not in the reference): knobs of the B200 engine -------------------------------------------
 _C.B200 = CfgNode()
 _C.B200.COMPUTE_DTYPE = "bfloat16"   # "bfloat16" (tcgen05 path) or "float32" (CUDA-core parity mode)
+# NUM_GPUS > 1: train-mode BatchNorm uses the statistics of the global batch, as the torch.nn.SyncBatchNorm the
+# reference converts every BatchNorm to (models/build.py:45-46).  False = per-replica statistics (no BN collectives).
+_C.B200.SYNC_BN = True
 
 
 def _assert_and_infer_cfg(cfg):

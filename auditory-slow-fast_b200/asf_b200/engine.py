@@ -29,6 +29,7 @@ import math
 import os
 
 import torch
+import torch.distributed as dist
 import torch.nn as nn
 
 from . import _lib as L
@@ -227,6 +228,10 @@ class Engine:
         self.plan = None
         self.grad_hook = None        # callable(engine, names_done) used by the data-parallel wrapper
         self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
+        # (process_group, world_size) set by the data-parallel wrapper: train-mode BatchNorm then normalises with the
+        # statistics of the GLOBAL batch, like the torch.nn.SyncBatchNorm the reference converts to when NUM_GPUS > 1
+        # (/root/reference/audio_slowfast/models/build.py:45-46)
+        self.sync_bn = None
         self._flat_grad = None
         self._grad_views = {}
         self._ws = {}
@@ -381,6 +386,7 @@ class Engine:
         flat = torch.empty(4 * tot, dtype=torch.float32, device=dev)
         plan.stats_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
         plan.red_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
+        plan.red_local = torch.zeros(2 * tot, dtype=torch.float32, device=dev)  # per-rank sums under SyncBN
         o = 0
         for u in allu:
             Cn = u.Cout
@@ -388,6 +394,7 @@ class Engine:
             u.mean, u.invstd = flat[4 * o + 2 * Cn:4 * o + 3 * Cn], flat[4 * o + 3 * Cn:4 * o + 4 * Cn]
             u.stats = plan.stats_flat[2 * o:2 * o + 2 * Cn]
             u.red = plan.red_flat[2 * o:2 * o + 2 * Cn]
+            u.red_local = plan.red_local[2 * o:2 * o + 2 * Cn]
             o += Cn
         return plan
 
@@ -755,10 +762,17 @@ class Engine:
         rows = raw.rows
         mom = bn.momentum if bn.momentum is not None else 0.1
         track = bn.track_running_stats
+        count = float(rows)
+        if self.sync_bn is not None:
+            # SyncBatchNorm forward: sum(x), sum(x^2) and the element count are summed over the replicas; mean, biased
+            # variance and the unbiased running-variance update then follow from the global count
+            group, world = self.sync_bn
+            dist.all_reduce(u.stats, group=group)
+            count *= world
         # statistics -> scale / shift / saved mean, invstd / running stats, and the normalise(+res)(+ReLU) pass: one launch
         L.call("asf_bn_train_fwd", C.c_void_p(raw.ptr), raw.ld, C.c_void_p(res.ptr) if res is not None else None,
                res.ld if res is not None else 0, C.c_void_p(out.ptr) if out is not None else None,
-               out.ld if out is not None else 0, raw.code, rows, u.Cout, L.ptr(u.stats), C.c_double(rows),
+               out.ld if out is not None else 0, raw.code, rows, u.Cout, L.ptr(u.stats), C.c_double(count),
                L.ptr(bn.weight), L.ptr(bn.bias), C.c_float(bn.eps), C.c_float(mom),
                L.ptr(bn.running_mean) if track else None, L.ptr(bn.running_var) if track else None,
                L.ptr(bn.num_batches_tracked) if track else None, L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.mean),
@@ -876,9 +890,23 @@ class Engine:
             if (gw is not None) and (gb is not None) and acc_w != acc_b:
                 raise RuntimeError("%s: BN weight and bias gradients must both exist or both be unset" % u.name)
             dconv = u.raw.grad
+            count = float(rows)
+            pg_w, pg_b = gw, gb
+            if self.sync_bn is not None:
+                # SyncBatchNorm backward: dx uses sum(dz), sum(dz * xhat) of the GLOBAL batch; dgamma / dbeta stay the
+                # per-rank sums (the gradient all-reduce averages them like every other parameter gradient)
+                group, world = self.sync_bn
+                u.red_local.copy_(u.red)
+                dist.all_reduce(u.red, group=group)
+                count *= world
+                pg_w = pg_b = None
             L.call("asf_bn_bwd_apply", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld,
                    C.c_void_p(dconv.ptr), dconv.ld, dz.code, rows, u.Cout, L.ptr(bn.weight), L.ptr(u.mean),
-                   L.ptr(u.invstd), L.ptr(u.red), C.c_double(rows), L.ptr(gw), L.ptr(gb), int(acc_w or acc_b), st)
+                   L.ptr(u.invstd), L.ptr(u.red), C.c_double(count), L.ptr(pg_w), L.ptr(pg_b), int(acc_w or acc_b), st)
+            if self.sync_bn is not None:
+                for g_, acc_, src in ((gb, acc_b, u.red_local[:u.Cout]), (gw, acc_w, u.red_local[u.Cout:])):
+                    if g_ is not None:
+                        g_.add_(src) if acc_ else g_.copy_(src)
             rscale = None
         else:
             dconv = dz

@@ -48,9 +48,9 @@ def build_model(cfg, gpu_id=None):
     (KeyError if unknown), device placement, and -- when NUM_GPUS > 1 -- a data-parallel wrapper whose
     ``.module`` is the model (callers reach through it: train_net.py:392, :710; checkpoint.py:111).
     Differences, both deliberate: the wrapper is asf_b200.parallel.DataParallel (bucketed NCCL all-reduce
-    issued from inside the fused backward, overlapping the remaining wgrads) instead of torch DDP, and
-    BatchNorm statistics stay per-replica unless cfg.B200.SYNC_BN is set (the reference force-converts to
-    SyncBatchNorm; per-GPU batch 64 makes local statistics sound -- DESIGN.md "multi-GPU").
+    issued from inside the fused backward, overlapping the remaining wgrads) instead of torch DDP, and the
+    SyncBatchNorm conversion (build.py:45-46) is a switch of the engine (global-batch statistics by all-reduce of
+    the per-channel sums, cfg.B200.SYNC_BN, default True) rather than a module swap, so module names stay put.
     """
     if torch.cuda.is_available():
         assert cfg.NUM_GPUS <= torch.cuda.device_count(), "Cannot use more GPU devices than available"
@@ -63,5 +63,5 @@ def build_model(cfg, gpu_id=None):
     if cfg.NUM_GPUS > 1:
         from ..parallel import DataParallel
 
-        model = DataParallel(model)
+        model = DataParallel(model, sync_bn=bool(getattr(getattr(cfg, "B200", None), "SYNC_BN", True)))
     return model

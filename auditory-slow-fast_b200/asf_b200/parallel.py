@@ -82,7 +82,11 @@ class GradBucketer:
 class DataParallel(nn.Module):
     """``DataParallel(model)``: data-parallel replica of an asf_b200 engine model (one process per GPU)."""
 
-    def __init__(self, module, process_group=None, bucket_bytes=16 << 20, broadcast_parameters=True):
+    def __init__(self, module, process_group=None, bucket_bytes=16 << 20, broadcast_parameters=True, sync_bn=True):
+        """``sync_bn``: train-mode BatchNorm layers normalise with the statistics of the global batch (two small
+        all-reduces per such layer and pass: sum(x), sum(x^2) forward; sum(dz), sum(dz * xhat) backward), which is
+        what the reference gets from ``torch.nn.SyncBatchNorm.convert_sync_batchnorm`` (models/build.py:45-46).
+        With the EPIC recipe (BN.FREEZE True) only the two stems and s1_fuse are in training mode."""
         super().__init__()
         if not dist.is_initialized():
             raise RuntimeError("asf_b200.parallel.DataParallel needs torch.distributed to be initialised "
@@ -97,6 +101,8 @@ class DataParallel(nn.Module):
                 for t in list(module.parameters()) + list(module.buffers()):
                     dist.broadcast(t, src=0, group=process_group)
         module.engine.grad_hook = self._on_grads
+        world = dist.get_world_size(process_group)
+        module.engine.sync_bn = (process_group, world) if (sync_bn and world > 1) else None
 
     def forward(self, x, bboxes=None):
         return self.module(x, bboxes)

@@ -241,7 +241,9 @@ static bool narrow_conv_ok(const asf_tapgemm_t* q) {
   const char* e = getenv("ASF_NARROW_CONV");  // read per call: the parity tests flip it between two launches
   if ((e && e[0] == '0') || q->max_ctas > 0) return false;
   const int N = q->N, K = q->K;
-  if (N < 8 || K < 8 || N > 64 || K > 64 || (N & (N - 1)) || (K & (K - 1))) return false;
+  // K up to 128: the dgrad of the fast pathway's 1x1 expansion convs (s4: 128 -> 32 channels) has 2.7 us of traffic and
+  // took 45..54 us on the tcgen05 kernel (profiles/r01_tapgemm_layers_v16.txt)
+  if (N < 8 || K < 8 || N > 64 || K > 128 || (N & (N - 1)) || (K & (K - 1))) return false;
   if ((long long)N * K * q->ntaps > NC_MAX_W) return false;
   if (q->out_dtype != ASF_BF16 || q->epi.scale) return false;
   const long long m_total = (long long)q->m_ext[0] * q->m_ext[1] * q->m_ext[2];

@@ -30,6 +30,7 @@ class Harness(Engine):
         self.device = torch.device("cuda", torch.cuda.current_device())
         self._ws = {}
         self.grad_hook = None
+        self.sync_bn = None
         self.plan = None
         self.two_stream = False
         self.sm_split = (0, 0)

@@ -256,6 +256,34 @@ def test_narrow_conv_forward_and_dgrad(h_tc, case, monkeypatch):
     assert torch.allclose(a["mean"], b["mean"], atol=1e-4 * a["amax"])
 
 
+def test_narrow_conv_dgrad_k128(h_tc, monkeypatch):
+    """dgrad of a 1x1 expansion conv 32 -> 128 channels (fast pathway s4, conv c): contraction over 128 channels into
+    32, the widest K the narrow kernel takes; against torch and against the tensor-core kernel."""
+    B, T, Fq, cin, cout = 16, 100, 16, 32, 128
+    got = {}
+    for tag, env in (("narrow", "1"), ("tc", "0")):
+        monkeypatch.setenv("ASF_NARROW_CONV", env)
+        u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, (1, 1), (1, 1), (0, 0), seed=9)
+        u.bn.eval()
+        h_tc._prepare_unit(u, training=True)
+        dy = Act(u.y.B, u.y.T, u.y.F, cout, h_tc.dtype, h_tc.device)
+        dy.buf.copy_(torch.randn(dy.buf.shape, generator=torch.Generator("cuda").manual_seed(2), device="cuda"))
+        dx = u.x.grad
+        n0 = _narrow_count()
+        h_tc._conv_dgrad(u, dy, dx, accumulate=False, mask=u.x)
+        torch.cuda.synchronize()
+        assert _narrow_count() - n0 == (1 if env == "1" else 0)
+        got[tag] = nchw(dx.view().float()).clone()
+        if tag == "narrow":
+            scale = u.bn.weight / torch.sqrt(u.bn.running_var + u.bn.eps)
+            w_seen = (w * scale.view(-1, 1, 1, 1)).to(torch.bfloat16).float()
+            xr = x.clone().requires_grad_(True)
+            _ref_conv(xr, w_seen, (1, 1), (0, 0)).backward(nchw(dy.view().float()))
+            ref = xr.grad * (x > 0)
+    assert rel_err(got["narrow"], ref) < 1e-2, rel_err(got["narrow"], ref)
+    assert rel_err(got["narrow"], got["tc"]) < 3e-3, rel_err(got["narrow"], got["tc"])
+
+
 def test_tapgemm_concat_slice_output(h_tc):
     """the lateral conv writes into channels [64:80) of the slow buffer (no torch.cat)."""
     u, x, w = make_unit(h_tc, 2, 100, 32, 8, 16, (7, 1), (4, 1), (3, 0), seed=5, ld_out=80)

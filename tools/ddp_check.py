@@ -1,5 +1,7 @@
 """GPU aid (2+ GPUs): gradients of asf_b200.parallel.DataParallel after backward == mean over ranks of the gradients
-each rank's batch gives on its own, with the two-stream / weight-gradient-stream engine, eager and inside a CUDA graph.
+each rank's batch gives on its own (per-replica BatchNorm statistics), and -- with cfg.B200.SYNC_BN, the default -- ==
+the gradients of ONE process on the concatenated batch (SyncBatchNorm semantics of the reference, build.py:45-46), with
+the two-stream / weight-gradient-stream engine.
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/ddp_check.py"""
 import os
 import sys
@@ -37,11 +39,18 @@ def grads_of(model, x, lab):
     return {n: p.grad.detach().clone() for n, p in net.named_parameters() if p.grad is not None}
 
 
-worst = 0.0
-for freeze in (True, False):
+def cat_batches():
+    xs, labs = zip(*(batch(r) for r in range(world)))
+    x = [torch.cat([b[i] for b in xs]) for i in range(2)]
+    lab = {k: torch.cat([l[k] for l in labs]) for k in labs[0]}
+    return x, lab
+
+
+for freeze, sync in ((True, False), (True, True), (False, False), (False, True)):
     cfg = epic_slowfast_cfg((97, 300), freeze)
     cfg.BN.FREEZE = freeze
     cfg.MODEL.DROPOUT_RATE = 0.0
+    cfg.B200.SYNC_BN = sync
     cfg.NUM_GPUS = 1
     torch.manual_seed(0)
     single = build_model(cfg)        # no wrapper: per-rank gradients
@@ -50,19 +59,28 @@ for freeze in (True, False):
     torch.manual_seed(0)
     ddp = build_model(cfg)           # wrapped in asf_b200.parallel.DataParallel (models/build.py)
     ddp.train()
+    assert (ddp.module.engine.sync_bn is not None) == sync
     if freeze:
         for m in (single, ddp.module):
             m.freeze_fn("bn_parameters")
             m.freeze_fn("bn_statistics")
     ddp.module.load_state_dict(single.state_dict())
-    ref = None
-    for r in range(world):
-        x, lab = batch(r)
-        g = grads_of(single, x, lab)
-        # BN running statistics must not drift between the per-rank passes of the reference model
-        single.load_state_dict(ddp.module.state_dict())
-        ref = g if ref is None else {k: ref[k] + g[k] for k in g}
-    ref = {k: v / world for k, v in ref.items()}
+    state0 = {k: v.clone() for k, v in single.state_dict().items()}
+    if sync:
+        # SyncBatchNorm: every train-mode BN sees the statistics of the global batch, so the averaged gradients (and
+        # the running statistics) equal those of ONE process running the concatenated batch
+        x, lab = cat_batches()
+        ref = grads_of(single, x, lab)
+        ref_state = {k: v.clone() for k, v in single.state_dict().items() if "running_" in k}
+    else:
+        ref = None
+        for r in range(world):
+            x, lab = batch(r)
+            g = grads_of(single, x, lab)
+            # BN running statistics must not drift between the per-rank passes of the reference model
+            single.load_state_dict(state0)
+            ref = g if ref is None else {k: ref[k] + g[k] for k in g}
+        ref = {k: v / world for k, v in ref.items()}
     x, lab = batch(rank)
     got = grads_of(ddp, x, lab)
     errs = sorted(((float((got[k] - ref[k]).norm() / (ref[k].norm() + 1e-12)), k) for k in ref), reverse=True)
@@ -74,8 +92,15 @@ for freeze in (True, False):
         assert worst < 2e-2, errs[:5]
     else:
         assert med < 1e-2 and worst < 0.15, (med, errs[:5])
+    stat = ""
+    if sync:
+        now = ddp.module.state_dict()
+        serr = max(float((now[k] - v).abs().max() / (v.abs().max() + 1e-6)) for k, v in ref_state.items())
+        assert serr < 2e-3, serr
+        stat = "; running statistics vs the single-process global batch: worst rel err %.1e" % serr
     if rank == 0:
-        print("freeze=%s: %d gradient tensors vs the mean over %d ranks: median rel err %.2e, worst %.2e (%s)"
-              % (freeze, len(ref), world, med, worst, errs[0][1]))
+        print("freeze=%s sync_bn=%s: %d gradient tensors vs %s: median rel err %.2e, worst %.2e (%s)%s"
+              % (freeze, sync, len(ref), "one process on the concatenated batch" if sync else
+                 "the mean over %d ranks" % world, med, worst, errs[0][1], stat))
 dist.barrier()
 dist.destroy_process_group()
