@@ -738,15 +738,116 @@ __global__ void __launch_bounds__(256) stem_wgrad_v8_kernel(const float* __restr
   for (int i = threadIdx.x; i < g.Cout * taps; i += 256) atomicAdd(dw + i, sacc[i]);
 }
 
+// Second generation: a WARP owns one (8-channel group, kernel row) and a slice of the block's output rows, lanes walk
+// consecutive rows (dout loads of a warp are contiguous, two rows per lane in flight, 32-bit index arithmetic), the
+// 8 x kf accumulators are folded by shuffles and only lane 0 touches the shared accumulators.  The v8 kernel spent its
+// time in 64-bit div/mod per row and in 51-way contended shared atomics (157 us for the fast stem, the last kernel of
+// the backward pass and therefore on the critical path of the step).
+__global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
+                                                            float* __restrict__ dw, asf_conv_geom_t g, int rows_per_block,
+                                                            int nslice) {
+  pdl_trigger();
+  pdl_wait();
+  extern __shared__ float sacc[];  // [Cout][taps]
+  const int taps = g.kt * g.kf, CG = g.Cout / 8;
+  const int ngroups = CG * g.kt;
+  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) sacc[i] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rows = g.B * g.Tout * g.Fout;
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, rows);
+  const int slice_rows = (rows_per_block + nslice - 1) / nslice;
+  const unsigned Fout = (unsigned)g.Fout, Tout = (unsigned)g.Tout;
+  for (int task = warp; task < ngroups * nslice; task += 8) {
+    const int grp = task % ngroups, sl = task / ngroups;
+    const int cg = grp % CG, it = grp / CG;
+    float acc[8][STEM_KF_MAX];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int k = 0; k < STEM_KF_MAX; ++k) acc[j][k] = 0.f;
+    const int s0 = r0 + sl * slice_rows, s1 = min(s0 + slice_rows, r1);
+    for (int base = s0 + lane; base < s1; base += 64) {
+      uint4 dq[2];
+      float xv[2][STEM_KF_MAX];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int row = base + 32 * h;
+        dq[h] = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int k = 0; k < STEM_KF_MAX; ++k) xv[h][k] = 0.f;
+        if (row < s1) {
+          const unsigned r2 = (unsigned)row / Fout;
+          const int fo = (int)((unsigned)row - r2 * Fout);
+          const unsigned b = r2 / Tout;
+          const int to = (int)(r2 - b * Tout);
+          const int t = to * g.st + it - g.pt;
+          if (t >= 0 && t < g.Tin) {
+            dq[h] = *(const uint4*)(dout + (int64_t)row * g.ld_out + cg * 8);
+            const float* ip = in + ((int64_t)b * g.Tin + t) * g.Fin;
+            const int f0 = fo * g.sf - g.pf;
+#pragma unroll
+            for (int k = 0; k < STEM_KF_MAX; ++k) {
+              const int f = f0 + k;
+              if (k < g.kf && f >= 0 && f < g.Fin) xv[h][k] = ip[f];
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const F8 d = unpack8(dq[h]);
+#pragma unroll
+        for (int k = 0; k < STEM_KF_MAX; ++k)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j][k] = fmaf(d.v[j], xv[h][k], acc[j][k]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int k = 0; k < STEM_KF_MAX; ++k) {
+        if (k < g.kf) {  // uniform across the warp
+          float v = acc[j][k];
+#pragma unroll
+          for (int sft = 16; sft >= 1; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
+          if (lane == 0) atomicAdd(&sacc[(cg * 8 + j) * taps + it * g.kf + k], v);
+        }
+      }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) atomicAdd(dw + i, sacc[i]);
+}
+
 int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st) {
   const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
   const int ngroups = (g->Cout / 8) * g->kt;
+  const size_t smem = sizeof(float) * (size_t)g->Cout * g->kt * g->kf;
+  static int use_v8 = -1;
+  if (use_v8 < 0) {
+    const char* e = getenv("ASF_STEM_WGRAD_V8");
+    use_v8 = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (!use_v8 && rows < (1LL << 31) && (int64_t)g->B * g->Tin * g->Fin < (1LL << 31)) {
+    // (group, slice) tasks are dealt round robin to the 8 warps of a block: the smallest slice count that balances them
+    int nslice = 1;
+    while ((ngroups * nslice) % 8) ++nslice;
+    int64_t blocks = 148 * 2;
+    int64_t rpb = cdiv(rows, blocks);
+    const int64_t min_rpb = 64LL * 4 * nslice;  // at least four double-row rounds per task
+    if (rpb < min_rpb) rpb = min_rpb;
+    blocks = cdiv(rows, rpb);
+    ASF_CUDA(launch_pdl(stem_wgrad_v9_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dw, *g, (int)rpb,
+                        nslice));
+    ASF_LAUNCH_CHECK();
+    return 0;
+  }
   const int RL = 256 / ngroups;
   int64_t blocks = 148 * 4;
   int64_t rpb = cdiv(rows, blocks);
   if (rpb < RL * 8) rpb = RL * 8;
   blocks = cdiv(rows, rpb);
-  const size_t smem = sizeof(float) * (size_t)g->Cout * g->kt * g->kf;
   ASF_CUDA(launch_pdl(stem_wgrad_v8_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dw, *g, rpb));
   ASF_LAUNCH_CHECK();
   return 0;

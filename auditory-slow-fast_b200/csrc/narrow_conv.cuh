@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
 // Which mode-0 launches take this kernel.  ASF_NARROW_CONV=0 sends everything back to the tensor-core kernel.
 static bool narrow_conv_ok(const asf_tapgemm_t* q) {
   const char* e = getenv("ASF_NARROW_CONV");  // read per call: the parity tests flip it between two launches
-  if ((e && e[0] == '0') || q->max_ctas > 0) return false;
+  if (e && e[0] == '0') return false;  // (an SM budget, max_ctas, does not apply: these CTAs share SMs with anything)
   const int N = q->N, K = q->K;
   // K up to 128: the dgrad of the fast pathway's 1x1 expansion convs (s4: 128 -> 32 channels) has 2.7 us of traffic and
   // took 45..54 us on the tcgen05 kernel (profiles/r01_tapgemm_layers_v16.txt)

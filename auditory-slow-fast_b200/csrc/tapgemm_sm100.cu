@@ -576,7 +576,19 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: wgrad stage does not fit twice in shared memory");
   w->stages = stages;
   const int64_t base_tiles = (int64_t)w->r_tiles * w->c_tiles * q->ntaps;
-  int ks = (int)cdiv(sm_budget(q), base_tiles);
+  // CTAs a weight-gradient launch aims for (ASF_WG_CTAS, 0 = every SM).  tcgen05 CTAs of two kernels never share an SM
+  // (each allocates its TMEM columns and most of the shared memory), so a wgrad grid over all 148 SMs makes the dgrad
+  // chain beside it on the pathway stream queue behind it.  A quarter of the chip per wgrad launch -- four of them run
+  // on the four weight-gradient streams -- leaves the rest to the critical chain and cuts the split-K partial traffic
+  // 4x: measured 5.95 -> 5.35 ms per step (148: 5.95, 96: 5.60, 64: 5.47, 48: 5.36, 32: 5.35, 24: 5.42, 16: 5.47).
+  static int wg_ctas = -1;
+  if (wg_ctas < 0) {
+    const char* e = getenv("ASF_WG_CTAS");
+    wg_ctas = e ? atoi(e) : 32;
+  }
+  int budget = sm_budget(q);
+  if (wg_ctas > 0 && wg_ctas < budget) budget = wg_ctas;
+  int ks = (int)cdiv(budget, base_tiles);
   if (ks > w->m_tiles / 4) ks = w->m_tiles / 4;  // at least four 64-row stages of MMA work per partial tile
   if (ks < 1) ks = 1;
   if (!w->narrow) w->ksplit = ks;

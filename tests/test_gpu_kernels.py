@@ -396,6 +396,33 @@ def test_stem_pool_forward_backward(dtype):
     assert rel_err(nchw(dz.float()), refdz) < (1e-5 if dtype == torch.float32 else 1e-2)
 
 
+@pytest.mark.parametrize("name,T,cout,k,s,p", [("slow", 100, 64, (1, 7), (2, 2), (0, 3)),
+                                               ("fast", 400, 8, (5, 7), (2, 2), (2, 3)),
+                                               ("ragged", 37, 16, (3, 5), (2, 2), (1, 2))])
+def test_stem_wgrad(name, T, cout, k, s, p):
+    """asf_stem_wgrad (C_in = 1 stems, stem_helper.py:150-157) against torch's conv weight gradient, overwrite and
+    accumulate; 'ragged' has row counts that do not divide the warp / slice tiling."""
+    B, Fq = 3, 128 if name != "ragged" else 50
+    torch.manual_seed(3)
+    x = torch.randn(B, 1, T, Fq, device="cuda")
+    To, Fo = (T + 2 * p[0] - k[0]) // s[0] + 1, (Fq + 2 * p[1] - k[1]) // s[1] + 1
+    dy = torch.randn(B, To, Fo, cout, device="cuda").to(torch.bfloat16)
+    g = L.ConvGeom()
+    g.B, g.Tin, g.Fin, g.Cin, g.Tout, g.Fout, g.Cout = B, T, Fq, 1, To, Fo, cout
+    g.kt, g.kf, g.st, g.sf, g.pt, g.pf = k[0], k[1], s[0], s[1], p[0], p[1]
+    g.ld_in, g.ld_out = 1, cout
+    dw = torch.full((cout, 1, k[0], k[1]), 7.0, device="cuda")
+    st = L.stream_ptr()
+    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dw), C.byref(g), 0, st)
+    torch.cuda.synchronize()
+    w = torch.zeros(cout, 1, k[0], k[1], device="cuda", requires_grad=True)
+    F.conv2d(x, w, stride=s, padding=p).backward(nchw(dy.float()))
+    assert rel_err(dw, w.grad) < 1e-4, rel_err(dw, w.grad)
+    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dw), C.byref(g), 1, st)
+    torch.cuda.synchronize()
+    assert rel_err(dw, 2 * w.grad) < 1e-4
+
+
 def test_head_kernels():
     B, P, Cn = 4, 100, 256
     g = torch.Generator().manual_seed(2)
