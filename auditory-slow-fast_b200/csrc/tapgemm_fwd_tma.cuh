@@ -285,10 +285,35 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     // Operand prefetch runs one slab ahead of the math ACROSS tile boundaries (leader thread only): the sequence of
     // (tile, slab) pairs of a group is known up front, and for narrow layers (one slab per tile) the TMA latency of
     // the residual / mask slab would otherwise sit in every tile's critical path.
-    int pf_tile = blockIdx.x + group * gridDim.x, pf_s = 0;
+    // The epilogue of a CTA's LAST tile has nothing to overlap with (no next mainloop), and most launches of this
+    // network are 1..3 tiles per CTA: there the group that does not own the tile's TMEM buffer takes the upper half of
+    // its slabs, so the exposed tail is half as long.  seg(): the slab range [s0, s1) of tile `it_` for this group.
+    const int n_it = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    auto seg = [&](int it_, int nslab_, int& s0, int& s1) -> bool {
+      const bool owner = (it_ & 1) == group;
+      if (!(p.epi_split && it_ == n_it - 1 && nslab_ >= 2)) {
+        s0 = 0;
+        s1 = nslab_;
+        return owner;
+      }
+      const int h = (nslab_ + 1) >> 1;
+      s0 = owner ? 0 : h;
+      s1 = owner ? h : nslab_;
+      return true;
+    };
+    int pf_it = -1, pf_s = 0, pf_s1 = 0;
     uint32_t pf_gs = 0;
+    auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs
+      for (++pf_it; pf_it < n_it; ++pf_it) {
+        const int n0_ = ((blockIdx.x + pf_it * gridDim.x) % p.n_tiles) * p.block_n;
+        const int nslab_ = (min(p.block_n, p.N - n0_) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
+        if (seg(pf_it, nslab_, pf_s, pf_s1)) return;
+      }
+    };
+    pf_seek();
     auto prefetch_next = [&]() {
-      if (pf_tile >= total_tiles) return;
+      if (pf_it >= n_it) return;
+      const int pf_tile = blockIdx.x + pf_it * gridDim.x;
       const int n_tile = pf_tile % p.n_tiles, m_tile = pf_tile / p.n_tiles;
       int st[3];
       tile_coords(p, m_tile, st);
@@ -301,24 +326,24 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         o3 = d == 3 ? st[j] : o3;
       }
       const int n0 = n_tile * p.block_n;
-      const int nslab = (min(p.block_n, p.N - n0) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
       const int b = pf_gs & 1;
       uint64_t* bar = &sh->op_full[group][b];
       mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
       for (int o = 0; o < n_ops; ++o)
         tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + b) * EPI_SLAB_BYTES, p.rank_o, n0 + pf_s * 32, o1, o2, o3, 0);
       ++pf_gs;
-      if (++pf_s == nslab) {
-        pf_s = 0;
-        pf_tile += 2 * gridDim.x;
-      }
+      if (++pf_s == pf_s1) pf_seek();
     };
-    if (leader && n_ops > 0) prefetch_next();  // slab 0 of this group's first tile
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      if ((it & 1) != group) continue;
-      const int buf = group;
+    if (leader && n_ops > 0) prefetch_next();  // first slab of this group's first segment
+    for (int it = 0; it < n_it; ++it) {
+      const int tile = blockIdx.x + it * gridDim.x;
+      const int buf = it & 1;
       const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+      const int n0 = n_tile * p.block_n;
+      const int nslab = (min(p.block_n, p.N - n0) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
+      int s0, s1;
+      if (!seg(it, nslab, s0, s1)) continue;
+      const bool owner = buf == group;
       int st[3];
       tile_coords(p, m_tile, st);
       int o1 = 0, o2 = 0, o3 = 0;
@@ -330,8 +355,6 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         o3 = d == 3 ? st[j] : o3;
       }
       const bool valid = (st[0] + r1 < p.m_ext[0]) && (st[1] + r2 < p.m_ext[1]) && (st[2] + r3 < p.m_ext[2]);
-      const int n0 = n_tile * p.block_n;
-      const int nslab = (min(p.block_n, p.N - n0) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
       if (g_shift) {
         for (int i = t; i < p.block_n; i += 128) s_shift[i] = (n0 + i < p.N) ? g_shift[n0 + i] : 0.f;
       }
@@ -341,7 +364,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
       if (leader) { pb.end(4); pb.begin(); }
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
-      for (int s = 0; s < nslab; ++s, ++gs) {
+      for (int s = s0; s < s1; ++s, ++gs) {
         const int b = gs & 1;
         uint32_t raw[32];
         tmem_ld32_issue(taddr0 + (uint32_t)(s * 32), raw);
@@ -355,7 +378,9 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           pw.end(6);  // the store that last read out_buf[b] (two slabs ago) has drained it
         }
         tmem_ld_wait();
-        if (s == nslab - 1) {  // accumulators are in registers: hand the TMEM buffer back to the MMA warp
+        // accumulators are in registers: the owning group hands the TMEM buffer back to the MMA warp (on a shared last
+        // tile the other group may still be reading it, but no mainloop follows the last tile)
+        if (s == s1 - 1 && owner) {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);

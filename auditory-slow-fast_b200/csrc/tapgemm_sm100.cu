@@ -53,6 +53,7 @@ struct TgParams {
   int o_dim[3];          // M-dim j -> coordinate slot (1..3) of the output maps, 0 = unmapped
   int n_add, has_mask;   // operands: n_add in {0,1} additive, has_mask in {0,1}
   int epi_smem_off;      // byte offset of the epilogue staging region inside dynamic smem
+  int epi_split;         // both epilogue groups share the slabs of a CTA's LAST tile (nothing left to overlap it with)
   // mode 1
   float* dwp;
   int ntaps_w, ksplit, c_tiles, r_tiles;
@@ -716,6 +717,14 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       p.n_add = n_add;
       p.has_mask = has_mask;
       p.epi_smem_off = stages * stage_bytes;
+      {
+        static int split = -1;
+        if (split < 0) {
+          const char* e = getenv("ASF_EPI_SPLIT");
+          split = (e && e[0] == '0') ? 0 : 1;
+        }
+        p.epi_split = split;
+      }
       // output-space tensor maps: dim 0 = channels, then every M dim that moves the output row
       int64_t oext[3], ostr_rows[3];
       int obox[3], nd_o = 0;
