@@ -131,7 +131,8 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   const int stage_bytes = TG_A_BYTES + b_bytes;
   const int n_ops = p.n_add + p.has_mask;
   uint8_t* epi_base = smem + p.epi_smem_off;
-  const int group_bytes = (2 + 2 * n_ops) * EPI_SLAB_BYTES;
+  const int OD = p.op_depth;  // operand ring depth
+  const int group_bytes = (2 + OD * n_ops) * EPI_SLAB_BYTES;
   float* shift_base = (float*)(epi_base + 2 * group_bytes);
   TgShared* sh = (TgShared*)(shift_base + 2 * EPI_SHIFT_FLOATS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -150,8 +151,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     for (int i = 0; i < 2; ++i) {
       mbar_init(&sh->tmem_full[i], 1);
       mbar_init(&sh->tmem_empty[i], 4);
-      mbar_init(&sh->op_full[i][0], 1);
-      mbar_init(&sh->op_full[i][1], 1);
+      for (int j = 0; j < 4; ++j) mbar_init(&sh->op_full[i][j], 1);
     }
     fence_barrier_init();
   }
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     const int bar_id = 1 + group;
     uint8_t* gbase = epi_base + group * group_bytes;
     uint8_t* out_buf = gbase;                             // [2] slabs
-    uint8_t* op_buf = gbase + 2 * EPI_SLAB_BYTES;         // [n_ops][2] slabs
+    uint8_t* op_buf = gbase + 2 * EPI_SLAB_BYTES;         // [n_ops][OD] slabs
     float* s_shift = shift_base + group * EPI_SHIFT_FLOATS;
     const float* g_shift = p.epi.shift;
     const int variant = (g_shift ? 8 : 0) | (p.n_add ? 4 : 0) | (p.has_mask ? 2 : 0) | (p.epi.relu ? 1 : 0);
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
       return true;
     };
     int pf_it = -1, pf_s = 0, pf_s1 = 0;
-    uint32_t pf_gs = 0;
+    int pf_ob = 0;  // operand ring slot of the next prefetch
     auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs
       for (++pf_it; pf_it < n_it; ++pf_it) {
         const int n0_ = ((blockIdx.x + pf_it * gridDim.x) % p.n_tiles) * p.block_n;
@@ -326,15 +326,17 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         o3 = d == 3 ? st[j] : o3;
       }
       const int n0 = n_tile * p.block_n;
-      const int b = pf_gs & 1;
-      uint64_t* bar = &sh->op_full[group][b];
+      uint64_t* bar = &sh->op_full[group][pf_ob];
       mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
       for (int o = 0; o < n_ops; ++o)
-        tma_load(&p.tm_op[o], bar, op_buf + (o * 2 + b) * EPI_SLAB_BYTES, p.rank_o, n0 + pf_s * 32, o1, o2, o3, 0);
-      ++pf_gs;
+        tma_load(&p.tm_op[o], bar, op_buf + (o * OD + pf_ob) * EPI_SLAB_BYTES, p.rank_o, n0 + pf_s * 32, o1, o2, o3, 0);
+      if (++pf_ob == OD) pf_ob = 0;
       if (++pf_s == pf_s1) pf_seek();
     };
-    if (leader && n_ops > 0) prefetch_next();  // first slab of this group's first segment
+    if (leader && n_ops > 0)
+      for (int i = 0; i < OD - 1; ++i) prefetch_next();  // the first OD - 1 slabs of this group's sequence
+    int oslot = 0;     // operand ring slot of the slab being processed
+    uint32_t oph = 0;  // its mbarrier parity
     for (int it = 0; it < n_it; ++it) {
       const int tile = blockIdx.x + it * gridDim.x;
       const int buf = it & 1;
@@ -369,8 +371,8 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         uint32_t raw[32];
         tmem_ld32_issue(taddr0 + (uint32_t)(s * 32), raw);
         if (leader) {
-          // operands of the following slab (possibly of the next tile) into the other buffer: its last reader was
-          // slab gs-1, and every thread has passed that slab's closing barrier
+          // operands of slab gs + OD - 1 (possibly of a later tile) into the ring slot that slab gs - 1 used: every
+          // thread has passed that slab's closing barrier
           if (n_ops > 0) prefetch_next();
           Probe pw{p.dbg, 0};
           pw.begin();
@@ -385,11 +387,15 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           __syncwarp();
           if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
         }
-        if (n_ops > 0) mbar_wait_warp(&sh->op_full[group][b], (gs >> 1) & 1, 5);
+        if (n_ops > 0) mbar_wait_warp(&sh->op_full[group][oslot], oph, 5);
         named_bar(bar_id, 128);  // out_buf[b] is free for everybody
         uint8_t* ob = out_buf + b * EPI_SLAB_BYTES;
-        const uint8_t* op0 = op_buf + b * EPI_SLAB_BYTES;
-        const uint8_t* op1 = op_buf + (2 + b) * EPI_SLAB_BYTES;
+        const uint8_t* op0 = op_buf + oslot * EPI_SLAB_BYTES;
+        const uint8_t* op1 = op_buf + (OD + oslot) * EPI_SLAB_BYTES;
+        if (++oslot == OD) {
+          oslot = 0;
+          oph ^= 1;
+        }
         const float* ss = s_shift + s * 32;
         const bool zero = STATS && !valid;
         switch (variant) {

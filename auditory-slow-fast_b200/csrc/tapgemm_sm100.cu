@@ -53,6 +53,7 @@ struct TgParams {
   int o_dim[3];          // M-dim j -> coordinate slot (1..3) of the output maps, 0 = unmapped
   int n_add, has_mask;   // operands: n_add in {0,1} additive, has_mask in {0,1}
   int epi_smem_off;      // byte offset of the epilogue staging region inside dynamic smem
+  int op_depth;          // residual / mask slabs in flight per epilogue group (2..4): op_depth - 1 slabs of TMA prefetch
   int epi_split;         // both epilogue groups share the slabs of a CTA's LAST tile (nothing left to overlap it with)
   // mode 1
   float* dwp;
@@ -74,7 +75,7 @@ struct TgShared {
   uint64_t empty[TG_MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t op_full[2][2];  // [epilogue group][operand buffer]
+  uint64_t op_full[2][4];  // [epilogue group][operand buffer] (TgParams::op_depth of them in use)
   uint32_t tmem_base;
 };
 
@@ -670,7 +671,18 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     }
     const bool use_tma = vec && !q->epi.scale && !(q->epi.res && q->epi.accumulate) && !force_direct;
     const int n_add = (q->epi.res || q->epi.accumulate) ? 1 : 0, has_mask = q->epi.mask ? 1 : 0;
-    const int group_bytes = (2 + 2 * (n_add + has_mask)) * EPI_SLAB_BYTES;
+    // Operand slabs (residual / mask) arrive by TMA ahead of the math through a ring of op_depth slabs per operand and
+    // epilogue group.  Measured on the training step (ASF_OP_DEPTH): 2 -> 5.21 ms, 3 -> 5.22 ms, 4 -> 5.75 ms -- every
+    // extra slab of lookahead costs 16..32 KB of shared memory, i.e. a mainloop stage or half the N tile, which loses
+    // more than the operand latency it hides.  Default 2.
+    static int op_depth_env = -1;
+    if (op_depth_env < 0) {
+      const char* e = getenv("ASF_OP_DEPTH");
+      op_depth_env = e ? atoi(e) : 0;
+    }
+    int op_depth = 2;
+    if (op_depth_env >= 2 && op_depth_env <= 4) op_depth = op_depth_env;
+    const int group_bytes = (2 + op_depth * (n_add + has_mask)) * EPI_SLAB_BYTES;
     const int tma_fixed = 2 * group_bytes + 2 * EPI_SHIFT_FLOATS * 4 + (int)sizeof(TgShared);
     const int smem_cap = 227 * 1024;
     int bn = q->block_n;
@@ -717,6 +729,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       p.n_add = n_add;
       p.has_mask = has_mask;
       p.epi_smem_off = stages * stage_bytes;
+      p.op_depth = op_depth;
       {
         static int split = -1;
         if (split < 0) {
