@@ -94,6 +94,10 @@ class FusedSGD(torch.optim.Optimizer):
         first = int(self._steps == 0 and g0["dampening"] != 0)
         L.call("asf_sgd_multi", L.ptr(self._table[0]), self._table[1], self._table[2], L.ptr(self._lr_dev),
                C.c_float(g0["momentum"]), C.c_float(g0["dampening"]), int(bool(g0["nesterov"])), first, L.stream_ptr())
+        # The kernel wrote through raw pointers: tell autograd's version counters, which is what the engine keys its
+        # packed bf16 weight copies on (Engine._prepare_all) -- without this the next forward would keep using the
+        # weights from before the update.
+        torch.autograd.graph.increment_version([p for p, _, _, _ in items])
         self._steps += 1
         return loss
 
