@@ -483,6 +483,36 @@ class Engine:
             cache[tkey] = ent
         L.call("asf_pack_weights_multi", L.ptr(ent[0]), ent[1], ent[2], st)
 
+    def refresh_weights(self, training=True, stream=None, after=None):
+        """Re-packs the stale bf16 weight copies now, on ``stream`` (forked from and joined back to the current stream),
+        instead of at the start of the next forward: the training step calls this before the log-mel extraction, so
+        the HBM-bound re-layout of the 26.9 M parameters that the optimiser just changed runs beside the tensor-core
+        log-mel kernel instead of in front of the stems.  No-op until the first forward has built the plan."""
+        if self.plan is None:
+            return
+        cur = torch.cuda.current_stream(self.device)
+        if stream is None:
+            if getattr(self, "_pack_stream", None) is None:
+                self._pack_stream = torch.cuda.Stream(device=self.device)
+            stream = self._pack_stream
+        # ``after``: an event recorded on the current stream BEFORE the work this refresh is meant to run beside (the
+        # caller launches that work first, so its CTAs are resident when the short pack blocks arrive)
+        if after is not None:
+            stream.wait_event(after)
+        else:
+            stream.wait_stream(cur)
+        with torch.cuda.stream(stream):
+            self._prepare_all(training)
+        cur_done = torch.cuda.Event()
+        cur_done.record(stream)
+        self._pack_join = cur_done
+
+    def join_refresh(self):
+        ev = getattr(self, "_pack_join", None)
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            self._pack_join = None
+
     # ------------------------------------------------------------------------------------------ conv launches
     # ------------------------------------------------------------------------------------------ streams
     def _ts(self):
@@ -800,6 +830,7 @@ class Engine:
         st = L.stream_ptr()
         if training:
             plan.stats_flat.zero_()
+        self.join_refresh()
         self._prepare_all(training)
         ts = self._ts()
         cur = torch.cuda.current_stream(self.device)

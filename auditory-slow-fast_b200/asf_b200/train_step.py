@@ -51,7 +51,15 @@ class TrainStep:
         self._calls = 0
 
     def _body(self):
+        net = self.model.module if hasattr(self.model, "module") else self.model
+        fork = torch.cuda.Event()
+        fork.record(torch.cuda.current_stream(self.device))
         x = logmel_batch(self.cfg, self.wave)
+        if hasattr(net, "engine"):
+            # the optimiser step of the previous iteration left every packed weight copy stale: refresh them on a side
+            # stream forked BEFORE the log-mel kernel but launched after it, so the HBM-bound re-layout runs beside the
+            # tensor-core kernel (the forward joins that stream before its first launch)
+            net.engine.refresh_weights(net.training, after=fork)
         self.opt.zero_grad(set_to_none=True)
         preds = self.model(x)
         loss, _, _ = compute_loss(preds, self.labels)

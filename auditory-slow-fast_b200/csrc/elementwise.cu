@@ -403,7 +403,15 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ 
 // All convs of the network in ONE launch: block b handles PACK_CHUNK destination indices of the unit whose chunk range
 // contains b (binary search over the descriptor table), for both the [O][taps][I] and the [I][taps][O] copy.
 constexpr int PACK_CHUNK = 2048;
+constexpr int PACK_TILE = 32;      // output channels x input channels per shared-memory tile
+constexpr int PACK_MAX_TAPS = 7;   // tiled path; more taps (the 5x7 stems, C_in = 1) take the element-wise loop
+// A block owns the tiles t = b - chunk0, + nb, ... of its unit (nb = the unit's chunk count, as laid out by the caller).
+// The OIHW master is read in whole rows (I x taps contiguous floats per output channel, scaled by the folded BN
+// factor), staged in shared memory, and leaves as 64-byte runs of both packed layouts.  The first version gathered
+// every destination element on its own (4-byte reads at a stride of I*taps floats for the transposed copy): 176 us
+// for the 26.9 M parameters, in front of the stems of every training step.
 __global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_desc_t* __restrict__ d, int n) {
+  __shared__ float tile[PACK_TILE][PACK_TILE * PACK_MAX_TAPS + 1];
   int lo = 0, hi = n - 1;
   const long long b = blockIdx.x;
   while (lo < hi) {
@@ -412,26 +420,67 @@ __global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_
   }
   const asf_pack_desc_t u = d[lo];
   const long long total = (long long)u.O * u.I * u.taps;
-  const long long i0 = (b - u.chunk0) * PACK_CHUNK;
-  for (int k = threadIdx.x; k < PACK_CHUNK; k += 256) {
-    const long long i = i0 + k;
-    if (i >= total) break;
-    {  // [O][taps][I]
-      const int c = (int)(i % u.I);
-      const long long r = i / u.I;
-      const int tp = (int)(r % u.taps), o = (int)(r / u.taps);
-      float v = u.w[((long long)o * u.I + c) * u.taps + tp];
-      if (u.rscale) v *= u.rscale[o];
-      if (u.dtype == ASF_BF16) ((bf16*)u.packed)[i] = __float2bfloat16_rn(v); else ((float*)u.packed)[i] = v;
+  const int nb = (int)((total + PACK_CHUNK - 1) / PACK_CHUNK);
+  const int bl = (int)(b - u.chunk0);
+  const bool bf = u.dtype == ASF_BF16;
+  if (u.taps > PACK_MAX_TAPS) {
+    const long long i0 = (long long)bl * PACK_CHUNK;
+    for (int k = threadIdx.x; k < PACK_CHUNK; k += 256) {
+      const long long i = i0 + k;
+      if (i >= total) break;
+      {  // [O][taps][I]
+        const int c = (int)(i % u.I);
+        const long long r = i / u.I;
+        const int tp = (int)(r % u.taps), o = (int)(r / u.taps);
+        float v = u.w[((long long)o * u.I + c) * u.taps + tp];
+        if (u.rscale) v *= u.rscale[o];
+        if (bf) ((bf16*)u.packed)[i] = __float2bfloat16_rn(v); else ((float*)u.packed)[i] = v;
+      }
+      if (u.packed_t) {  // [I][taps][O]
+        const int o = (int)(i % u.O);
+        const long long r = i / u.O;
+        const int tp = (int)(r % u.taps), c = (int)(r / u.taps);
+        float v = u.w[((long long)o * u.I + c) * u.taps + tp];
+        if (u.rscale) v *= u.rscale[o];
+        if (bf) ((bf16*)u.packed_t)[i] = __float2bfloat16_rn(v); else ((float*)u.packed_t)[i] = v;
+      }
     }
-    if (u.packed_t) {  // [I][taps][O]
-      const int o = (int)(i % u.O);
-      const long long r = i / u.O;
-      const int tp = (int)(r % u.taps), c = (int)(r / u.taps);
-      float v = u.w[((long long)o * u.I + c) * u.taps + tp];
-      if (u.rscale) v *= u.rscale[o];
-      if (u.dtype == ASF_BF16) ((bf16*)u.packed_t)[i] = __float2bfloat16_rn(v); else ((float*)u.packed_t)[i] = v;
+    return;
+  }
+  const int O = u.O, I = u.I, taps = u.taps;
+  const int itl = (I + PACK_TILE - 1) / PACK_TILE, nt = ((O + PACK_TILE - 1) / PACK_TILE) * itl;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int t = bl; t < nt; t += nb) {
+    const int o0 = (t / itl) * PACK_TILE, i0 = (t % itl) * PACK_TILE;
+    const int ow = min(PACK_TILE, O - o0), iw = min(PACK_TILE, I - i0);
+    const int seg = iw * taps;
+    for (int o = warp; o < ow; o += 8) {
+      const float* src = u.w + ((long long)(o0 + o) * I + i0) * taps;
+      const float sc = u.rscale ? u.rscale[o0 + o] : 1.f;
+      for (int k = lane; k < seg; k += 32) tile[o][k] = src[k] * sc;
     }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < ow * taps * PACK_TILE; idx += 256) {  // [O][taps][I]: lanes along I
+      const int i = idx & 31, r = idx >> 5;
+      const int tp = r % taps, o = r / taps;
+      if (i < iw) {
+        const float v = tile[o][i * taps + tp];
+        const long long dst = ((long long)(o0 + o) * taps + tp) * I + i0 + i;
+        if (bf) ((bf16*)u.packed)[dst] = __float2bfloat16_rn(v); else ((float*)u.packed)[dst] = v;
+      }
+    }
+    if (u.packed_t) {
+      for (int idx = threadIdx.x; idx < iw * taps * PACK_TILE; idx += 256) {  // [I][taps][O]: lanes along O
+        const int o = idx & 31, r = idx >> 5;
+        const int tp = r % taps, i = r / taps;
+        if (o < ow) {
+          const float v = tile[o][i * taps + tp];
+          const long long dst = ((long long)(i0 + i) * taps + tp) * O + o0 + o;
+          if (bf) ((bf16*)u.packed_t)[dst] = __float2bfloat16_rn(v); else ((float*)u.packed_t)[dst] = v;
+        }
+      }
+    }
+    __syncthreads();
   }
 }
 

