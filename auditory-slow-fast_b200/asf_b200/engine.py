@@ -459,6 +459,22 @@ class Engine:
                 u.w_key = key
         if not stale:
             return
+        # Two launches: everything the first millisecond of the forward needs (stems, laterals, the whole fast pathway,
+        # slow s2 / s3: 6 % of the parameters) and the slow pathway's s4 / s5 (94 %).  When the refresh runs on a side
+        # stream (refresh_weights) the forward joins the first before the stems and the second only before the first
+        # slow s4 block, so the big re-layout hides beside the early layers.
+        late = [u for u in stale if u.name.startswith(("s4.pathway0", "s5.pathway0"))]
+        early = [u for u in stale if not u.name.startswith(("s4.pathway0", "s5.pathway0"))]
+        if early:
+            self._pack_launch(early, st)
+        if self._pack_record:
+            self._pack_join = torch.cuda.Event()
+            self._pack_join.record(torch.cuda.current_stream(self.device))
+        if late:
+            self._pack_launch(late, st)
+
+    def _pack_launch(self, stale, st):
+        plan = self.plan
         tkey = tuple((u.name, u.conv.weight.data_ptr(), u.batch_mode) for u in stale)
         cache = getattr(plan, "_pack_tables", None)
         if cache is None:
@@ -483,6 +499,10 @@ class Engine:
             cache[tkey] = ent
         L.call("asf_pack_weights_multi", L.ptr(ent[0]), ent[1], ent[2], st)
 
+    _pack_record = False
+    _pack_join = None
+    _pack_join_late = None
+
     def refresh_weights(self, training=True, stream=None, after=None):
         """Re-packs the stale bf16 weight copies now, on ``stream`` (forked from and joined back to the current stream),
         instead of at the start of the next forward: the training step calls this before the log-mel extraction, so
@@ -501,17 +521,28 @@ class Engine:
             stream.wait_event(after)
         else:
             stream.wait_stream(cur)
+        self._pack_join = None
         with torch.cuda.stream(stream):
-            self._prepare_all(training)
-        cur_done = torch.cuda.Event()
-        cur_done.record(stream)
-        self._pack_join = cur_done
+            self._pack_record = True
+            try:
+                self._prepare_all(training)
+            finally:
+                self._pack_record = False
+            done = torch.cuda.Event()
+            done.record(stream)
+        if self._pack_join is None:
+            self._pack_join = done
+        self._pack_join_late = done
 
-    def join_refresh(self):
-        ev = getattr(self, "_pack_join", None)
+    def join_refresh(self, late=False):
+        """Makes the current stream wait for the side-stream weight refresh: the early group (before the first launch of
+        the forward) or, ``late``, everything (before the first slow s4 block and at the end of the forward)."""
+        if late:
+            ev, self._pack_join_late = self._pack_join_late, None
+        else:
+            ev, self._pack_join = self._pack_join, None
         if ev is not None:
             torch.cuda.current_stream(self.device).wait_event(ev)
-            self._pack_join = None
 
     # ------------------------------------------------------------------------------------------ conv launches
     # ------------------------------------------------------------------------------------------ streams
@@ -872,6 +903,8 @@ class Engine:
                     main.wait_event(ev_fuse)
                     ev_fuse = None
                 with self._on(item["path"]):
+                    if self._pack_join_late is not None and item["name"].startswith(("s4.pathway0", "s5.pathway0")):
+                        self.join_refresh(late=True)
                     if "b1" in item:
                         self._unit_forward(item["b1"], training, True)
                     self._unit_forward(item["a"], training, True)
@@ -880,6 +913,8 @@ class Engine:
         if ts:
             cur.wait_stream(main)  # join
             cur.wait_stream(side)
+        if self._pack_join_late is not None:
+            self.join_refresh(late=True)
         st = L.stream_ptr()
         # head
         head = m.head
