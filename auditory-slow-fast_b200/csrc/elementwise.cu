@@ -460,6 +460,38 @@ __global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_
       for (int k = lane; k < seg; k += 32) tile[o][k] = src[k] * sc;
     }
     __syncthreads();
+    // bf16 with 4-aligned tile widths (every conv but the stems): 8-byte stores of four consecutive channels, a warp
+    // covers four 64-byte runs per instruction
+    const bool v4 = bf && !(iw & 3) && !(ow & 3) && !(I & 3) && !(O & 3);
+    if (v4) {
+      for (int idx = threadIdx.x; idx < ow * taps * 8; idx += 256) {  // [O][taps][I]: 8 lanes x 4 channels along I
+        const int i = (idx & 7) * 4, r = idx >> 3;
+        const int tp = r % taps, o = r / taps;
+        if (i < iw) {
+          const float* tr = &tile[o][i * taps + tp];
+          __nv_bfloat162 lo2 = __floats2bfloat162_rn(tr[0], tr[taps]), hi2 = __floats2bfloat162_rn(tr[2 * taps], tr[3 * taps]);
+          uint2 q;
+          q.x = *(const uint32_t*)&lo2;
+          q.y = *(const uint32_t*)&hi2;
+          *(uint2*)((bf16*)u.packed + ((long long)(o0 + o) * taps + tp) * I + i0 + i) = q;
+        }
+      }
+      if (u.packed_t) {
+        for (int idx = threadIdx.x; idx < iw * taps * 8; idx += 256) {  // [I][taps][O]: 8 lanes x 4 channels along O
+          const int o = (idx & 7) * 4, r = idx >> 3;
+          const int tp = r % taps, i = r / taps;
+          if (o < ow) {
+            const int k = i * taps + tp;
+            __nv_bfloat162 lo2 = __floats2bfloat162_rn(tile[o][k], tile[o + 1][k]),
+                           hi2 = __floats2bfloat162_rn(tile[o + 2][k], tile[o + 3][k]);
+            uint2 q;
+            q.x = *(const uint32_t*)&lo2;
+            q.y = *(const uint32_t*)&hi2;
+            *(uint2*)((bf16*)u.packed_t + ((long long)(i0 + i) * taps + tp) * O + o0 + o) = q;
+          }
+        }
+      }
+    } else {
     for (int idx = threadIdx.x; idx < ow * taps * PACK_TILE; idx += 256) {  // [O][taps][I]: lanes along I
       const int i = idx & 31, r = idx >> 5;
       const int tp = r % taps, o = r / taps;
@@ -479,6 +511,7 @@ __global__ void __launch_bounds__(256) pack_weights_multi_kernel(const asf_pack_
           if (bf) ((bf16*)u.packed_t)[dst] = __float2bfloat16_rn(v); else ((float*)u.packed_t)[dst] = v;
         }
       }
+    }
     }
     __syncthreads();
   }
