@@ -26,6 +26,13 @@ def test_cfg_defaults_and_merge():
     e.merge_from_list(["MODEL.DROPOUT_RATE", 0.0])
     assert e.MODEL.DROPOUT_RATE == 0.0
     assert int(round(e.AUDIO_DATA.SAMPLING_RATE * e.AUDIO_DATA.CLIP_SECS)) == 47976
+    # the reference converts every BatchNorm to SyncBatchNorm when NUM_GPUS > 1 (models/build.py:45-46): same default
+    # here, as a switch of the data-parallel wrapper rather than a module swap
+    import inspect
+
+    from asf_b200.parallel import DataParallel
+    assert e.B200.SYNC_BN is True
+    assert inspect.signature(DataParallel.__init__).parameters["sync_bn"].default is True
 
 
 def test_registry_and_build_model_contract():
