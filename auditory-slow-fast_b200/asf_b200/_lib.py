@@ -24,7 +24,16 @@ class Epilogue(C.Structure):
         ("mask", C.c_void_p), ("ld_mask", C.c_int64),
         ("stats", C.c_void_p), ("stats_stride", C.c_int32),
         ("relu", C.c_int32), ("accumulate", C.c_int32),
+        ("stats_ws", C.c_void_p), ("stats_ticket", C.c_void_p),
     ]
+
+
+STATS_TICKETS = 128
+
+
+def stats_ws_floats(channels):
+    """ASF_STATS_WS_FLOATS(C): floats of per-CTA partial-sum workspace a statistics producer may use."""
+    return 640 * max(int(channels), 256)
 
 
 class ConvGeom(C.Structure):
@@ -110,7 +119,7 @@ SIGNATURES = {
     "asf_logmel_fwd_tc": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _P, _I, _P],
     "asf_conv_fwd_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
     "asf_conv_dgrad_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
-    "asf_conv_wgrad_simt": [_P, _I, _P, _I, _P, C.POINTER(ConvGeom), _P, _I, _P],
+    "asf_conv_wgrad_simt": [_P, _I, _P, _I, _P, C.POINTER(ConvGeom), _P, _I, _P, _P],
     "asf_tapgemm": [C.POINTER(TapGemm), _I, _P],
     "asf_tapgemm_probe": [_P],
     "asf_pack_weight": [_P, _P, _I, _I, _I, _I, _P, _P],
@@ -120,12 +129,12 @@ SIGNATURES = {
     "asf_unpack_wgrad": [_P, _P, _I, _I, _I, _P, _I, _I, _P],
     "asf_unpack_wgrad_multi": [_P, _I, C.c_longlong, _P],
     "asf_tapgemm_wgrad_ksplit": [C.POINTER(TapGemm)],
-    "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P],
+    "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "asf_bn_fold": [_P, _P, _P, _P, _F, _I, _P, _P, _P],
     "asf_bn_train_fwd": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P],
     "asf_bn_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _I, _P],
-    "asf_bn_bwd_reduce": [_P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P],
+    "asf_bn_bwd_reduce": [_P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _P, _P],
     "asf_bn_bwd_apply": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _P, _P, _P, _D, _P, _P, _I, _P],
     "asf_relu_bwd": [_P, _L, _P, _L, _P, _L, _P, _L, _I, _L, _I, _P],
     "asf_bn_relu_maxpool_fwd": [_P, _P, _L, _I, _I, _I, _I, _I, _P, _P, _P, _P],
@@ -136,7 +145,7 @@ SIGNATURES = {
     "asf_softmax_rows": [_P, _I, _I, _L, _P],
     "asf_scale_mask": [_P, _P, _P, _L, _F, _P],
     "asf_gather_rows": [_P, _P, _P, _I, _I, _I, _I, _P],
-    "asf_stem_wgrad": [_P, _P, _I, _P, C.POINTER(ConvGeom), _I, _P],
+    "asf_stem_wgrad": [_P, _P, _I, _P, C.POINTER(ConvGeom), _P],
 }
 
 
@@ -149,6 +158,11 @@ def _declare(l):
     l.asf_launch_count.restype = C.c_longlong
     l.asf_narrow_conv_launches.argtypes = []
     l.asf_narrow_conv_launches.restype = C.c_longlong
+    # queries returning a count (>= 1) or a negative error code
+    l.asf_stem_wgrad_ksplit.argtypes = [C.POINTER(ConvGeom), _I]
+    l.asf_stem_wgrad_ksplit.restype = C.c_int
+    l.asf_conv_wgrad_simt_ksplit.argtypes = [C.POINTER(ConvGeom)]
+    l.asf_conv_wgrad_simt_ksplit.restype = C.c_int
 
 
 def call(name, *args):

@@ -124,7 +124,7 @@ class ConvUnit:
 
 
 def _epilogue(scale=None, shift=None, res=None, mask=None, stats=None, stats_stride=0, relu=False, accumulate=False,
-              row_off=0):
+              row_off=0, stats_ws=None, stats_ticket=None):
     e = L.Epilogue()
     e.scale = scale.data_ptr() if scale is not None else None
     e.shift = shift.data_ptr() if shift is not None else None
@@ -134,6 +134,7 @@ def _epilogue(scale=None, shift=None, res=None, mask=None, stats=None, stats_str
         e.mask, e.ld_mask = mask.row_ptr(row_off), mask.ld
     if stats is not None:
         e.stats, e.stats_stride = stats.data_ptr(), stats_stride
+        e.stats_ws, e.stats_ticket = stats_ws.data_ptr(), stats_ticket.data_ptr()
     e.relu, e.accumulate = int(relu), int(accumulate)
     return e
 
@@ -384,9 +385,11 @@ class Engine:
         allu = plan.stems + plan.units
         tot = sum(u.Cout for u in allu)
         flat = torch.empty(4 * tot, dtype=torch.float32, device=dev)
-        plan.stats_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
-        plan.red_flat = torch.zeros(2 * tot, dtype=torch.float32, device=dev)
-        plan.red_local = torch.zeros(2 * tot, dtype=torch.float32, device=dev)  # per-rank sums under SyncBN
+        # batch statistics are DOUBLES written (not accumulated) by the producers' ordered two-stage reductions
+        # (csrc/stats_reduce.cuh): nothing to zero per pass, nothing order-dependent
+        plan.stats_flat = torch.zeros(2 * tot, dtype=torch.float64, device=dev)
+        plan.red_flat = torch.zeros(2 * tot, dtype=torch.float64, device=dev)
+        plan.red_local = torch.zeros(2 * tot, dtype=torch.float64, device=dev)  # per-rank sums under SyncBN
         o = 0
         for u in allu:
             Cn = u.Cout
@@ -395,8 +398,17 @@ class Engine:
             u.stats = plan.stats_flat[2 * o:2 * o + 2 * Cn]
             u.red = plan.red_flat[2 * o:2 * o + 2 * Cn]
             u.red_local = plan.red_local[2 * o:2 * o + 2 * Cn]
+            u.stats_ws = u.stats_ticket = None  # allocated when the unit first runs with batch statistics
             o += Cn
         return plan
+
+    def _stat_bufs(self, u):
+        """Workspace (per-CTA partial sums) and self-resetting tickets of a unit's statistics reductions; the forward
+        statistics and the backward reduction of one unit are stream-ordered, so they share both."""
+        if getattr(u, "stats_ws", None) is None:
+            u.stats_ws = torch.empty(L.stats_ws_floats(u.Cout), dtype=torch.float32, device=self.device)
+            u.stats_ticket = torch.zeros(L.STATS_TICKETS, dtype=torch.int32, device=self.device)
+        return u.stats_ws, u.stats_ticket
 
     # ------------------------------------------------------------------------------------------ weights
     def _prepare_unit(self, u, training):
@@ -661,14 +673,32 @@ class Engine:
             g.ld_out = dy.ld
             if rscale is not None:
                 raise RuntimeError("stem BN is never folded in training")
-            L.call("asf_stem_wgrad", C.c_void_p(u.x.ptr), C.c_void_p(dy.ptr), dy.code, L.ptr(gview), C.byref(g),
-                   int(accumulate), st)
+            ks = getattr(u, "wg_ksplit", None)
+            if ks is None:
+                ks = L.lib().asf_stem_wgrad_ksplit(C.byref(g), dy.code)
+                if ks < 1:
+                    raise RuntimeError("asf_stem_wgrad_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
+                u.wg_ksplit = ks
+            n = u.Cout * u.taps
+            ws = getattr(u, "wg_ws", None)
+            if ws is None or ws.numel() < ks * n:
+                ws = u.wg_ws = torch.empty(ks * n, dtype=torch.float32, device=self.device)
+            # row-range partial sums [ks][Cout][taps]; their fixed-order sum is a split-K reduction with O = taps = 1
+            L.call("asf_stem_wgrad", C.c_void_p(u.x.ptr), C.c_void_p(dy.ptr), dy.code, L.ptr(ws), C.byref(g), st)
+            if self._defer_unpack():
+                self._pending_unpack.append((u.name, ws, gview, None, bool(accumulate), ks, 1, n, 1))
+            else:
+                L.call("asf_unpack_wgrad", L.ptr(ws), L.ptr(gview), 1, n, 1, None, int(accumulate), ks, st)
             return
         if not self._tc_ok(u):
             g = u.geom()
             g.ld_out = dy.ld
+            ks = L.lib().asf_conv_wgrad_simt_ksplit(C.byref(g))
+            if ks < 1:
+                raise RuntimeError("asf_conv_wgrad_simt_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
+            ws = self._wgrad_ws(ks * u.Cout * u.taps * u.Cin)
             L.call("asf_conv_wgrad_simt", C.c_void_p(u.x.ptr), u.x.code, C.c_void_p(dy.ptr), dy.code, L.ptr(gview),
-                   C.byref(g), L.ptr(rscale), int(accumulate), st)
+                   C.byref(g), L.ptr(rscale), int(accumulate), L.ptr(ws), st)
             return
         tg = L.TapGemm()
         tg_forward_geometry(u, tg, u.x)
@@ -693,7 +723,7 @@ class Engine:
                 ws = u.wg_ws = torch.empty(ks * u.Cout * u.taps * u.Cin, dtype=torch.float32, device=self.device)
             tg.dwp, tg.ksplit = ws.data_ptr(), ks
             L.call("asf_tapgemm", C.byref(tg), 1, st)
-            self._pending_unpack.append((u, gview, rscale, bool(accumulate), ks))
+            self._pending_unpack.append((u.name, ws, gview, rscale, bool(accumulate), ks, u.Cout, u.Cin, u.taps))
             return
         ws = self._wgrad_ws(ks * u.Cout * u.taps * u.Cin)
         tg.dwp, tg.ksplit = ws.data_ptr(), ks
@@ -710,20 +740,20 @@ class Engine:
         if not pend:
             return
         self._pending_unpack = []
-        key = tuple((u.name, u.wg_ws.data_ptr(), g.data_ptr(), rs.data_ptr() if rs is not None else 0, acc, ks)
-                    for u, g, rs, acc, ks in pend)
+        key = tuple((name, ws.data_ptr(), g.data_ptr(), rs.data_ptr() if rs is not None else 0, acc, ks)
+                    for name, ws, g, rs, acc, ks, O, I, taps in pend)
         cache = self.__dict__.setdefault("_unpack_tables", {})
         ent = cache.get(key)
         if ent is None:
             arr = (L.UnpackDesc * len(pend))()
             chunk = 0
-            for i, (u, g, rs, acc, ks) in enumerate(pend):
+            for i, (name, ws, g, rs, acc, ks, O, I, taps) in enumerate(pend):
                 d = arr[i]
-                d.dwp, d.dw = u.wg_ws.data_ptr(), g.data_ptr()
+                d.dwp, d.dw = ws.data_ptr(), g.data_ptr()
                 d.rscale = rs.data_ptr() if rs is not None else None
-                d.O, d.I, d.taps, d.ksplit, d.accumulate = u.Cout, u.Cin, u.taps, ks, int(acc)
+                d.O, d.I, d.taps, d.ksplit, d.accumulate = O, I, taps, ks, int(acc)
                 d.chunk0 = chunk
-                chunk += -(-(u.Cout * u.Cin * u.taps) // 1024)  # ASF_UNPACK_CHUNK
+                chunk += -(-(O * I * taps) // 1024)  # ASF_UNPACK_CHUNK
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             if len(cache) > 64:
                 cache.clear()
@@ -846,12 +876,13 @@ class Engine:
         if u.batch_mode:
             if u.raw is None:
                 u.raw = Act(u.y.B, u.y.T, u.y.F, u.Cout, self.dtype, self.device, name=u.name + ".raw")
+            ws, tk = self._stat_bufs(u)
             if self._tc_ok(u):
-                self._conv_fwd(u, u.raw, dict(stats=u.stats, stats_stride=u.Cout))
+                self._conv_fwd(u, u.raw, dict(stats=u.stats, stats_stride=u.Cout, stats_ws=ws, stats_ticket=tk))
             else:
                 self._conv_fwd(u, u.raw, dict())
                 L.call("asf_channel_stats", C.c_void_p(u.raw.ptr), u.raw.code, u.raw.rows, u.Cout, u.raw.ld,
-                       L.ptr(u.stats), st)
+                       L.ptr(u.stats), L.ptr(ws), L.ptr(tk), st)
             self._bn_forward(u, u.raw, u.y, u.res, u.relu, training, st)
         else:
             self._conv_fwd(u, u.y, dict(shift=u.shift, res=u.res, relu=u.relu))
@@ -859,8 +890,6 @@ class Engine:
     def _forward(self, xs, training, ctx):
         plan, m = self.plan, self.model
         st = L.stream_ptr()
-        if training:
-            plan.stats_flat.zero_()
         self.join_refresh()
         self._prepare_all(training)
         ts = self._ts()
@@ -883,8 +912,9 @@ class Engine:
                 L.call("asf_conv_fwd_simt", C.c_void_p(u.x.ptr), L.F32, L.ptr(u.w_pack), L.F32, C.c_void_p(u.y.ptr),
                        u.y.code, C.byref(g), C.byref(e), st)
                 if u.batch_mode:
+                    ws, tk = self._stat_bufs(u)
                     L.call("asf_channel_stats", C.c_void_p(u.y.ptr), u.y.code, u.y.rows, u.Cout, u.y.ld,
-                           L.ptr(u.stats), st)
+                           L.ptr(u.stats), L.ptr(ws), L.ptr(tk), st)
                     self._bn_forward(u, u.y, None, None, False, training, st)
                 L.call("asf_bn_relu_maxpool_fwd", C.c_void_p(u.y.ptr), C.c_void_p(u.pooled.ptr), u.pooled.ld,
                        u.y.code, u.y.B, u.y.T, u.y.F, u.Cout, L.ptr(u.scale), L.ptr(u.shift), L.ptr(u.pool_argmax), st)
@@ -949,8 +979,9 @@ class Engine:
         bn, conv = u.bn, u.conv
         if u.batch_mode:
             rows = dz.rows
+            ws, tk = self._stat_bufs(u)
             L.call("asf_bn_bwd_reduce", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld, dz.code, rows,
-                   u.Cout, L.ptr(u.mean), L.ptr(u.invstd), L.ptr(u.red), st)
+                   u.Cout, L.ptr(u.mean), L.ptr(u.invstd), L.ptr(u.red), L.ptr(ws), L.ptr(tk), st)
             gw, acc_w = self._grad_target(bn.weight)
             gb, acc_b = self._grad_target(bn.bias)
             if (gw is not None) and (gb is not None) and acc_w != acc_b:
@@ -1001,7 +1032,6 @@ class Engine:
         st = L.stream_ptr()
         B = plan.B
         self._pending_unpack = []
-        plan.red_flat.zero_()
         # ---- head
         plan.dfeat.zero_()
         feat = plan.feat_used

@@ -88,15 +88,15 @@ static inline bool ld8(int64_t ld) { return (ld & 7) == 0; }
 int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
                 int C, const float* scale, const float* shift, int relu, cudaStream_t st);
 int bn_train_fwd_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
-                    int C, const float* stats, double count, const float* gamma, const float* beta, float eps,
+                    int C, const double* stats, double count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked, float* scale,
                     float* shift, float* save_mean, float* save_invstd, int relu, cudaStream_t st);
 int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
-                    int C, const float* gamma, const float* mean, const float* invstd, const float* red,
-                    float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st);
+                    int C, const float* gamma, const float* mean, const float* invstd, const double* red,
+                    double inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st);
 template <bool kBwd>
 int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
-                      const float* invstd, float* out, cudaStream_t st);
+                      const float* invstd, double* out, float* ws, unsigned* ticket, cudaStream_t st);
 int relu_bwd_v8(const bf16* a, int64_t ld_a, const bf16* b, int64_t ld_b, const bf16* mask, int64_t ld_mask, bf16* y,
                 int64_t ld_y, int64_t rows, int C, cudaStream_t st);
 int avgpool_bwd_v8(const float* dfeat, int64_t ld_feat, int c_off, const bf16* mask, bf16* dx, int B, int P, int C,
@@ -106,7 +106,8 @@ int bn_relu_maxpool_fwd_v8(const bf16* x, bf16* y, int64_t ld_y, int B, int T, i
 int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* dz, int B, int T, int F, int C,
                            const float* scale, const float* shift, const uint32_t* argmax, cudaStream_t st);
 int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st);
-int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st);
+int stem_wgrad_v9_blocks(const asf_conv_geom_t* g);
+int stem_wgrad_v9(const float* in, const bf16* dout, float* dwp, const asf_conv_geom_t* g, cudaStream_t st);
 
 // dispatch on a dtype code
 #define ASF_DISPATCH_DTYPE(code, T, ...)                       \

@@ -6,6 +6,10 @@
 
 namespace asf {
 
+// accumulator type: fp32 inputs (the parity mode, an accuracy reference) accumulate in double, bf16 inputs in fp32
+template <typename T> struct AccT { typedef float type; };
+template <> struct AccT<float> { typedef double type; };
+
 template <typename T>
 __device__ __forceinline__ float apply_epilogue(float acc, int64_t row, int n, const asf_epilogue_t& e, T* out,
                                                 int64_t ld_out) {
@@ -32,7 +36,7 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(const TI* __restrict
     int64_t r2 = row / g.Fout;
     int to = (int)(r2 % g.Tout);
     int b = (int)(r2 / g.Tout);
-    float acc = 0.f;
+    typename AccT<TI>::type acc = 0;
     const TW* wn = w + (int64_t)n * taps * g.Cin;
     for (int it = 0; it < g.kt; ++it) {
       int t = to * g.st + it - g.pt;
@@ -42,14 +46,10 @@ __global__ void __launch_bounds__(256) conv_fwd_simt_kernel(const TI* __restrict
         if (f < 0 || f >= g.Fin) continue;
         const TI* ip = in + (((int64_t)b * g.Tin + t) * g.Fin + f) * g.ld_in;
         const TW* wp = wn + (int64_t)(it * g.kf + jf) * g.Cin;
-        for (int c = 0; c < g.Cin; ++c) acc += ldf(ip + c) * ldf(wp + c);
+        for (int c = 0; c < g.Cin; ++c) acc += (typename AccT<TI>::type)ldf(ip + c) * (typename AccT<TI>::type)ldf(wp + c);
       }
     }
-    float v = apply_epilogue<TO>(acc, row, n, e, out, g.ld_out);
-    if (e.stats) {
-      atomicAdd(e.stats + n, v);
-      atomicAdd(e.stats + e.stats_stride + n, v * v);
-    }
+    float v = apply_epilogue<TO>((float)acc, row, n, e, out, g.ld_out);
     stf(out + row * g.ld_out + n, v);
   }
 }
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(256) conv_dgrad_simt_kernel(const TI* __restri
     int64_t r2 = row / g.Fin;
     int ti = (int)(r2 % g.Tin);
     int b = (int)(r2 / g.Tin);
-    float acc = 0.f;
+    typename AccT<TI>::type acc = 0;
     for (int it = 0; it < g.kt; ++it) {
       int tt = ti + g.pt - it;
       if (tt < 0 || tt % g.st != 0) continue;
@@ -81,20 +81,20 @@ __global__ void __launch_bounds__(256) conv_dgrad_simt_kernel(const TI* __restri
         if (fo >= g.Fout) continue;
         const TI* dp = dout + (((int64_t)b * g.Tout + to) * g.Fout + fo) * g.ld_out;
         const TW* wp = w + (int64_t)(it * g.kf + jf) * g.Cin + c;
-        for (int n = 0; n < g.Cout; ++n) acc += ldf(dp + n) * ldf(wp + (int64_t)n * taps * g.Cin);
+        for (int n = 0; n < g.Cout; ++n)
+          acc += (typename AccT<TI>::type)ldf(dp + n) * (typename AccT<TI>::type)ldf(wp + (int64_t)n * taps * g.Cin);
       }
     }
-    float v = apply_epilogue<TO>(acc, row, c, e, din, g.ld_in);
+    float v = apply_epilogue<TO>((float)acc, row, c, e, din, g.ld_in);
     stf(din + row * g.ld_in + c, v);
   }
 }
 
-// One block per (n, tap) pair; threads over c; the block walks all output rows.  The reduction over rows is
-// split across gridDim.y slices and finished with fp32 atomics.
+// One block per (n, tap) pair; threads over c; the block walks a slice of the output rows (gridDim.y slices) and STORES
+// its partial sums to ws[slice][n][tap][c]; asf_unpack_wgrad adds the slices in order (no atomics).
 template <typename TI, typename TD>
 __global__ void __launch_bounds__(128) conv_wgrad_simt_kernel(const TI* __restrict__ in, const TD* __restrict__ dout,
-                                                              float* __restrict__ dw, asf_conv_geom_t g,
-                                                              const float* __restrict__ rscale) {
+                                                              float* __restrict__ ws, asf_conv_geom_t g) {
   const int taps = g.kt * g.kf;
   const int n = blockIdx.x / taps, tap = blockIdx.x % taps;
   const int it = tap / g.kf, jf = tap % g.kf;
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(128) conv_wgrad_simt_kernel(const TI* __restri
   const int64_t r1 = (r0 + per < rows) ? r0 + per : rows;
   for (int c0 = 0; c0 < g.Cin; c0 += blockDim.x) {
     int c = c0 + threadIdx.x;
-    float acc = 0.f;
+    typename AccT<TI>::type acc = 0;
     for (int64_t row = r0; row < r1; ++row) {
       int fo = (int)(row % g.Fout);
       int64_t r2 = row / g.Fout;
@@ -112,14 +112,22 @@ __global__ void __launch_bounds__(128) conv_wgrad_simt_kernel(const TI* __restri
       int b = (int)(r2 / g.Tout);
       int t = to * g.st + it - g.pt, f = fo * g.sf + jf - g.pf;
       if (t < 0 || t >= g.Tin || f < 0 || f >= g.Fin) continue;
-      float d = ldf(dout + row * g.ld_out + n);
-      if (c < g.Cin) acc += d * ldf(in + (((int64_t)b * g.Tin + t) * g.Fin + f) * g.ld_in + c);
+      typename AccT<TI>::type d = ldf(dout + row * g.ld_out + n);
+      if (c < g.Cin) acc += d * (typename AccT<TI>::type)ldf(in + (((int64_t)b * g.Tin + t) * g.Fin + f) * g.ld_in + c);
     }
-    if (c < g.Cin) {
-      if (rscale) acc *= rscale[n];
-      atomicAdd(dw + ((int64_t)n * g.Cin + c) * taps + tap, acc);
-    }
+    if (c < g.Cin) ws[(((int64_t)blockIdx.y * g.Cout + n) * taps + tap) * g.Cin + c] = (float)acc;
   }
+}
+
+static int wgrad_simt_ysplit(const asf_conv_geom_t* g) {
+  const int taps = g->kt * g->kf;
+  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
+  const int64_t blocks_xy = (int64_t)g->Cout * taps;
+  int ysplit = (int)(148 * 8 / blocks_xy);
+  if (ysplit < 1) ysplit = 1;
+  if (ysplit > 256) ysplit = 256;
+  if ((int64_t)ysplit > rows) ysplit = (int)rows;
+  return ysplit;
 }
 
 static int check_geom(const asf_conv_geom_t* g) {
@@ -148,6 +156,7 @@ extern "C" {
 int asf_conv_fwd_simt(const void* in, int in_dtype, const void* w, int w_dtype, void* out, int out_dtype,
                       const asf_conv_geom_t* g, const asf_epilogue_t* epi, void* stream) {
   ASF_CHECK_ARG(in && w && out && epi, "asf_conv_fwd_simt: null pointer");
+  ASF_CHECK_ARG(epi->stats == nullptr, "asf_conv_fwd_simt: statistics are not produced here (use asf_channel_stats)");
   int rc = check_geom(g);
   if (rc) return rc;
   int64_t total = (int64_t)g->B * g->Tout * g->Fout * g->Cout;
@@ -179,26 +188,26 @@ int asf_conv_dgrad_simt(const void* dout, int dout_dtype, const void* w, int w_d
   });
 }
 
+int asf_conv_wgrad_simt_ksplit(const asf_conv_geom_t* g) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  return wgrad_simt_ysplit(g);
+}
+
 int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout_dtype, float* dw_oihw,
-                        const asf_conv_geom_t* g, const float* rscale, int accumulate, void* stream) {
-  ASF_CHECK_ARG(in && dout && dw_oihw, "asf_conv_wgrad_simt: null pointer");
+                        const asf_conv_geom_t* g, const float* rscale, int accumulate, float* ws, void* stream) {
+  ASF_CHECK_ARG(in && dout && dw_oihw && ws, "asf_conv_wgrad_simt: null pointer");
   int rc = check_geom(g);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   int taps = g->kt * g->kf;
-  if (!accumulate) ASF_CUDA(cudaMemsetAsync(dw_oihw, 0, sizeof(float) * (size_t)g->Cout * g->Cin * taps, st));
-  int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
-  int64_t blocks_xy = (int64_t)g->Cout * taps;
-  int ysplit = (int)(148 * 8 / blocks_xy);
-  if (ysplit < 1) ysplit = 1;
-  if (ysplit > 256) ysplit = 256;
-  if ((int64_t)ysplit > rows) ysplit = (int)rows;
-  dim3 grid((unsigned)blocks_xy, ysplit);
+  const int ysplit = wgrad_simt_ysplit(g);
+  dim3 grid((unsigned)((int64_t)g->Cout * taps), ysplit);
   int threads = g->Cin >= 128 ? 128 : (g->Cin >= 64 ? 64 : 32);
   ASF_DISPATCH_DTYPE(in_dtype, TI, ASF_DISPATCH_DTYPE(dout_dtype, TD, {
-    conv_wgrad_simt_kernel<TI, TD><<<grid, threads, 0, st>>>((const TI*)in, (const TD*)dout, dw_oihw, *g, rscale);
+    conv_wgrad_simt_kernel<TI, TD><<<grid, threads, 0, st>>>((const TI*)in, (const TD*)dout, ws, *g);
     ASF_LAUNCH_CHECK();
-    return 0;
+    return asf_unpack_wgrad(ws, dw_oihw, g->Cout, g->Cin, taps, rscale, accumulate, ysplit, stream);
   }));
 }
 

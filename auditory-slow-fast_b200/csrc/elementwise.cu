@@ -5,6 +5,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "stats_reduce.cuh"
 
 namespace asf {
 
@@ -29,19 +30,23 @@ void set_error(const char* fmt, ...) {
 }
 
 // ----------------------------------------------------------------------------------------------- stats
-// block = 256 threads = RP row-lanes x CB channels (CB = min(C,256)); grid.x over row chunks, grid.y over
-// channel blocks.  Each thread streams rows with stride RP, then the block folds its row-lanes in smem.
+// Scalar path (fp32 parity mode and ragged layouts).  block = 256 threads = RP row-lanes x CB channels (CB = min(C,256));
+// grid.x over row chunks, grid.y over channel blocks.  Each thread streams rows with stride RP accumulating in DOUBLE,
+// the block folds its row-lanes in a fixed order and stores one partial row (doubles) into the workspace; the last CTA
+// of a channel block (ticket) adds the partial rows in ascending order.  No atomics on data: bit-reproducible.
 template <typename T, bool kBwd>
 __global__ void __launch_bounds__(256) channel_reduce_kernel(const T* __restrict__ a, int64_t ld_a,
                                                              const T* __restrict__ x, int64_t ld_x, int64_t rows,
                                                              int C, int CB, int64_t rows_per_block,
                                                              const float* __restrict__ mean,
-                                                             const float* __restrict__ invstd, float* out) {
-  __shared__ float s0[256], s1[256];
+                                                             const float* __restrict__ invstd, double* out, double* ws,
+                                                             unsigned* ticket) {
+  __shared__ double s0[256], s1[256];
+  __shared__ unsigned s_flag;
   const int RP = 256 / CB;
   const int cl = threadIdx.x % CB, rl = threadIdx.x / CB;
   const int c = blockIdx.y * CB + cl;
-  float acc0 = 0.f, acc1 = 0.f;
+  double acc0 = 0.0, acc1 = 0.0;
   if (rl < RP && c < C) {
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     int64_t r1 = r0 + rows_per_block;
@@ -52,50 +57,64 @@ __global__ void __launch_bounds__(256) channel_reduce_kernel(const T* __restrict
       is = invstd[c];
     }
     for (int64_t r = r0 + rl; r < r1; r += RP) {
-      float v = ldf(a + r * ld_a + c);
+      const float v = ldf(a + r * ld_a + c);
       if (kBwd) {
-        float xh = (ldf(x + r * ld_x + c) - mu) * is;
-        acc0 += v;
-        acc1 += v * xh;
+        const float xh = (ldf(x + r * ld_x + c) - mu) * is;
+        acc0 += (double)v;
+        acc1 += (double)v * (double)xh;
       } else {
-        acc0 += v;
-        acc1 += v * v;
+        acc0 += (double)v;
+        acc1 += (double)v * (double)v;
       }
     }
   }
   s0[threadIdx.x] = acc0;
   s1[threadIdx.x] = acc1;
   __syncthreads();
-  if (threadIdx.x < CB && c < C) {
-    float t0 = 0.f, t1 = 0.f;
+  // partial row of this CTA: ws[(blockIdx.y * gridDim.x + blockIdx.x)][2][CB]
+  double* my = ws + ((int64_t)blockIdx.y * gridDim.x + blockIdx.x) * 2 * CB;
+  if (threadIdx.x < CB) {
+    double t0 = 0.0, t1 = 0.0;
     for (int k = 0; k < RP; ++k) {
       t0 += s0[threadIdx.x + k * CB];
       t1 += s1[threadIdx.x + k * CB];
     }
-    atomicAdd(out + c, t0);
-    atomicAdd(out + C + c, t1);
+    my[threadIdx.x] = t0;
+    my[CB + threadIdx.x] = t1;
   }
+  if (!stats_last_cta(ticket + blockIdx.y, gridDim.x, &s_flag)) return;
+  const double* col = ws + (int64_t)blockIdx.y * gridDim.x * 2 * CB;
+  const int P = (int)gridDim.x, c0 = blockIdx.y * CB;
+  stats_ordered_reduce_f64(col, P, 2 * CB, 2 * CB, [&](int s, double v) {
+    const int half = s / CB, cc = c0 + (s - half * CB);
+    if (cc < C) out[half * C + cc] = v;
+  });
 }
+
+constexpr int SCALAR_REDUCE_MAX_X = 64;  // row chunks of the scalar path (partial rows per channel block)
 
 template <typename T, bool kBwd>
 static int launch_channel_reduce(const T* a, int64_t ld_a, const T* x, int64_t ld_x, int64_t rows, int C,
-                                 const float* mean, const float* invstd, float* out, cudaStream_t st) {
+                                 const float* mean, const float* invstd, double* out, float* ws, unsigned* ticket,
+                                 cudaStream_t st) {
   int CB = C < 256 ? C : 256;
   // CB must divide 256 for the row-lane layout; otherwise fall back to one row-lane of 256 channels
   if (256 % CB != 0) CB = 256;
   int cblocks = (int)cdiv(C, CB);
-  int64_t target_blocks = 148 * 8 / cblocks;
-  if (target_blocks < 1) target_blocks = 1;
+  ASF_CHECK_ARG(cblocks <= ASF_STATS_TICKETS, "channel reduce: %d channel blocks exceed the %d tickets", cblocks, ASF_STATS_TICKETS);
+  int64_t target_blocks = SCALAR_REDUCE_MAX_X;
   int64_t rpb = cdiv(rows, target_blocks);
   int RP = 256 / CB;
   if (rpb < RP * 4) rpb = RP * 4;
   dim3 grid((unsigned)cdiv(rows, rpb), cblocks);
-  channel_reduce_kernel<T, kBwd><<<grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, CB, rpb, mean, invstd, out);
+  // partial rows are doubles: grid.x * cblocks * 2 * CB doubles <= 64 * 2 * (C + 255) * 2 floats < ASF_STATS_WS_FLOATS(C)
+  ASF_CHECK_ARG(((uintptr_t)ws & 7) == 0, "channel reduce: workspace must be 8-byte aligned");
+  channel_reduce_kernel<T, kBwd><<<grid, 256, 0, st>>>(a, ld_a, x, ld_x, rows, C, CB, rpb, mean, invstd, out, (double*)ws, ticket);
   ASF_LAUNCH_CHECK();
   return 0;
 }
 
-__global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double count,
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, int C, double count,
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                    float momentum, float* running_mean, float* running_var,
                                    int64_t* num_batches_tracked, float* scale, float* shift, float* save_mean,
@@ -103,8 +122,8 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, doubl
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c == 0 && num_batches_tracked) *num_batches_tracked += 1;
   if (c >= C) return;
-  double mean = (double)stats[c] / count;
-  double var = (double)stats[C + c] / count - mean * mean;
+  double mean = stats[c] / count;
+  double var = stats[C + c] / count - mean * mean;
   if (var < 0.0) var = 0.0;
   float invstd = (float)(1.0 / sqrt(var + (double)eps));
   float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
@@ -151,7 +170,7 @@ template <typename T>
 __global__ void bn_bwd_apply_kernel(const T* __restrict__ dz, int64_t ld_dz, const T* __restrict__ x, int64_t ld_x,
                                     T* __restrict__ dx, int64_t ld_dx, int64_t rows, int C,
                                     const float* __restrict__ gamma, const float* __restrict__ mean,
-                                    const float* __restrict__ invstd, const float* __restrict__ red, float inv_count) {
+                                    const float* __restrict__ invstd, const double* __restrict__ red, double inv_count) {
   int64_t total = rows * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = i / C;
@@ -159,17 +178,18 @@ __global__ void bn_bwd_apply_kernel(const T* __restrict__ dz, int64_t ld_dz, con
     float is = invstd[c];
     float xh = (ldf(x + r * ld_x + c) - mean[c]) * is;
     float g = gamma ? gamma[c] : 1.f;
-    float v = g * is * (ldf(dz + r * ld_dz + c) - red[c] * inv_count - xh * red[C + c] * inv_count);
+    const float k0 = (float)(red[c] * inv_count), k1 = (float)(red[C + c] * inv_count);
+    float v = g * is * (ldf(dz + r * ld_dz + c) - k0 - xh * k1);
     stf(dx + r * ld_dx + c, v);
   }
 }
 
-__global__ void copy_dgamma_dbeta_kernel(const float* __restrict__ red, int C, float* dgamma, float* dbeta,
+__global__ void copy_dgamma_dbeta_kernel(const double* __restrict__ red, int C, float* dgamma, float* dbeta,
                                          int accumulate) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + red[c];
-  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + red[C + c];
+  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + (float)red[c];
+  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + (float)red[C + c];
 }
 
 template <typename T>
@@ -685,42 +705,44 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpac
   }
 }
 
-// Stem weight gradient (C_in = 1): dw[n][tap] = sum_rows dout[row][n] * in[row shifted by tap].
-// block = 256 threads = RL row-lanes x Cout channels; each thread keeps all taps (<= 35) in registers while it
-// streams its rows (dout coalesced along n, the input sample is a warp broadcast); row-lanes are folded in smem
-// and one atomic per (n, tap) per block finishes the reduction.
+// Stem weight gradient (C_in = 1), scalar path (fp32 parity mode, ragged shapes):
+//   dwp[block][n][tap] = sum over the block's rows of dout[row][n] * in[row shifted by tap].
+// block = 256 threads = RL row-lanes x Cout channels; each thread keeps all taps (<= 35) in registers (double
+// accumulators) while it streams its rows (dout coalesced along n, the input sample is a warp broadcast); row-lanes are
+// folded in shared memory in a fixed order and the block STORES its partial sums (asf_unpack_wgrad adds the blocks).
 constexpr int STEM_MAX_TAPS = 35;
 template <typename TD>
 __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ in, const TD* __restrict__ dout,
-                                                         float* __restrict__ dw, asf_conv_geom_t g,
+                                                         float* __restrict__ dwp, asf_conv_geom_t g,
                                                          int64_t rows_per_block) {
-  __shared__ float red[256];
+  __shared__ double red[256];
   const int taps = g.kt * g.kf;
   const int n = threadIdx.x % g.Cout, rl = threadIdx.x / g.Cout, RL = 256 / g.Cout;
   const int64_t rows = (int64_t)g.B * g.Tout * g.Fout;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   const int64_t r1 = (r0 + rows_per_block < rows) ? r0 + rows_per_block : rows;
-  float acc[STEM_MAX_TAPS];
+  double acc[STEM_MAX_TAPS];
 #pragma unroll
-  for (int i = 0; i < STEM_MAX_TAPS; ++i) acc[i] = 0.f;
+  for (int i = 0; i < STEM_MAX_TAPS; ++i) acc[i] = 0.0;
   if (rl < RL) {
     for (int64_t row = r0 + rl; row < r1; row += RL) {
       const int fo = (int)(row % g.Fout);
       const int64_t r2 = row / g.Fout;
       const int to = (int)(r2 % g.Tout);
       const int b = (int)(r2 / g.Tout);
-      const float d = ldf(dout + row * g.ld_out + n);
+      const double d = (double)ldf(dout + row * g.ld_out + n);
       const float* ib = in + (int64_t)b * g.Tin * g.Fin;
 #pragma unroll
       for (int tp = 0; tp < STEM_MAX_TAPS; ++tp) {
         if (tp < taps) {
           const int it = tp / g.kf, jf = tp - it * g.kf;
           const int t = to * g.st + it - g.pt, f = fo * g.sf + jf - g.pf;
-          if (t >= 0 && t < g.Tin && f >= 0 && f < g.Fin) acc[tp] = fmaf(d, ib[(int64_t)t * g.Fin + f], acc[tp]);
+          if (t >= 0 && t < g.Tin && f >= 0 && f < g.Fin) acc[tp] += d * (double)ib[(int64_t)t * g.Fin + f];
         }
       }
     }
   }
+  float* my = dwp + (int64_t)blockIdx.x * g.Cout * taps;
 #pragma unroll
   for (int tp = 0; tp < STEM_MAX_TAPS; ++tp) {
     if (tp < taps) {
@@ -728,9 +750,9 @@ __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict
       red[threadIdx.x] = acc[tp];
       __syncthreads();
       if (threadIdx.x < g.Cout) {
-        float t = 0.f;
+        double t = 0.0;
         for (int k = 0; k < RL; ++k) t += red[threadIdx.x + k * g.Cout];
-        atomicAdd(dw + (int64_t)threadIdx.x * taps + tp, t);
+        my[(int64_t)threadIdx.x * taps + tp] = (float)t;
       }
     }
   }
@@ -759,15 +781,18 @@ int asf_device_is_sm100(void) {
   return major == 10 ? 1 : 0;
 }
 
-int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream) {
-  ASF_CHECK_ARG(x && stats && rows > 0 && C > 0 && ld >= C, "asf_channel_stats: bad arguments");
+int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, double* stats, float* ws,
+                      uint32_t* ticket, void* stream) {
+  ASF_CHECK_ARG(x && stats && ws && ticket && rows > 0 && C > 0 && ld >= C, "asf_channel_stats: bad arguments");
   if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld) && al16(x))
-    return channel_reduce_v8<false>((const bf16*)x, ld, nullptr, 0, rows, C, nullptr, nullptr, stats, (cudaStream_t)stream);
+    return channel_reduce_v8<false>((const bf16*)x, ld, nullptr, 0, rows, C, nullptr, nullptr, stats, ws, ticket,
+                                    (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, false>((const T*)x, ld, (const T*)nullptr, 0, rows, C,
-                                                                      nullptr, nullptr, stats, (cudaStream_t)stream)));
+                                                                      nullptr, nullptr, stats, ws, ticket,
+                                                                      (cudaStream_t)stream)));
 }
 
-int asf_bn_finalize(const float* stats, int C, double count, const float* gamma, const float* beta, float eps,
+int asf_bn_finalize(const double* stats, int C, double count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                     float* scale, float* shift, float* save_mean, float* save_invstd, void* stream) {
   ASF_CHECK_ARG(stats && scale && shift && C > 0 && count > 0, "asf_bn_finalize: bad arguments");
@@ -802,7 +827,7 @@ int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, v
 }
 
 int asf_bn_train_fwd(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
-                     int64_t rows, int C, const float* stats, double count, const float* gamma, const float* beta,
+                     int64_t rows, int C, const double* stats, double count, const float* gamma, const float* beta,
                      float eps, float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                      float* scale, float* shift, float* save_mean, float* save_invstd, int relu, void* stream) {
   ASF_CHECK_ARG(x && stats && scale && shift && rows > 0 && C > 0 && count > 0, "asf_bn_train_fwd: bad arguments");
@@ -818,30 +843,31 @@ int asf_bn_train_fwd(const void* x, int64_t ld_x, const void* res, int64_t ld_re
 }
 
 int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
-                      const float* mean, const float* invstd, float* red, void* stream) {
-  ASF_CHECK_ARG(dz && x && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_reduce: bad arguments");
+                      const float* mean, const float* invstd, double* red, float* ws, uint32_t* ticket, void* stream) {
+  ASF_CHECK_ARG(dz && x && mean && invstd && red && ws && ticket && rows > 0 && C > 0, "asf_bn_bwd_reduce: bad arguments");
   if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dz) && ld8(ld_x) && al16(dz) && al16(x))
-    return channel_reduce_v8<true>((const bf16*)dz, ld_dz, (const bf16*)x, ld_x, rows, C, mean, invstd, red,
+    return channel_reduce_v8<true>((const bf16*)dz, ld_dz, (const bf16*)x, ld_x, rows, C, mean, invstd, red, ws, ticket,
                                    (cudaStream_t)stream);
   ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, true>((const T*)dz, ld_dz, (const T*)x, ld_x, rows, C,
-                                                                     mean, invstd, red, (cudaStream_t)stream)));
+                                                                     mean, invstd, red, ws, ticket,
+                                                                     (cudaStream_t)stream)));
 }
 
 int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
                      int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
-                     const float* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream) {
-  ASF_CHECK_ARG(dz && x && dx && mean && invstd && red && rows > 0 && C > 0, "asf_bn_bwd_apply: bad arguments");
+                     const double* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream) {
+  ASF_CHECK_ARG(dz && x && dx && mean && invstd && red && rows > 0 && C > 0 && count > 0, "asf_bn_bwd_apply: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == ASF_BF16 && C % 8 == 0 && ld8(ld_dz) && ld8(ld_x) && ld8(ld_dx) && al16(dz) && al16(x) && al16(dx))
     return bn_bwd_apply_v8((const bf16*)dz, ld_dz, (const bf16*)x, ld_x, (bf16*)dx, ld_dx, rows, C, gamma, mean, invstd,
-                           red, (float)(1.0 / count), dgamma, dbeta, accumulate, st);
+                           red, 1.0 / count, dgamma, dbeta, accumulate, st);
   if (dgamma || dbeta) {
     copy_dgamma_dbeta_kernel<<<(unsigned)cdiv(C, 128), 128, 0, st>>>(red, C, dgamma, dbeta, accumulate);
     ASF_LAUNCH_CHECK();
   }
   ASF_DISPATCH_DTYPE(dtype, T, {
     bn_bwd_apply_kernel<T><<<ew_grid(rows * C), 256, 0, st>>>((const T*)dz, ld_dz, (const T*)x, ld_x, (T*)dx, ld_dx,
-                                                            rows, C, gamma, mean, invstd, red, (float)(1.0 / count));
+                                                            rows, C, gamma, mean, invstd, red, 1.0 / count);
     ASF_LAUNCH_CHECK();
     return 0;
   });
@@ -995,24 +1021,41 @@ int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks
   return 0;
 }
 
-int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_oihw, const asf_conv_geom_t* g,
-                   int accumulate, void* stream) {
-  ASF_CHECK_ARG(in && dout && dw_oihw && g, "asf_stem_wgrad: null pointer");
+// scalar-path geometry: blocks of rows (also the number of partial rows)
+static void stem_scalar_geom(const asf_conv_geom_t* g, int64_t* blocks, int64_t* rpb) {
+  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
+  int64_t b = 148 * 2;
+  int64_t r = cdiv(rows, b);
+  const int RL = 256 / g->Cout;
+  if (r < RL) r = RL;
+  *rpb = r;
+  *blocks = cdiv(rows, r);
+}
+static bool stem_vec_ok(const asf_conv_geom_t* g, int dout_dtype) {
+  return dout_dtype == ASF_BF16 && g->Cout % 8 == 0 && g->kf <= 8 && (g->Cout / 8) * g->kt <= 256 && ld8(g->ld_out);
+}
+
+int asf_stem_wgrad_ksplit(const asf_conv_geom_t* g, int dout_dtype) {
+  ASF_CHECK_ARG(g && g->Cin == 1 && g->kt * g->kf <= STEM_MAX_TAPS && g->Cout > 0 && g->Cout <= 256 && 256 % g->Cout == 0,
+                "asf_stem_wgrad: needs Cin == 1, <= %d taps, Cout dividing 256", STEM_MAX_TAPS);
+  if (stem_vec_ok(g, dout_dtype)) return stem_wgrad_v9_blocks(g);
+  int64_t blocks, rpb;
+  stem_scalar_geom(g, &blocks, &rpb);
+  return (int)blocks;
+}
+
+int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dwp, const asf_conv_geom_t* g,
+                   void* stream) {
+  ASF_CHECK_ARG(in && dout && dwp && g, "asf_stem_wgrad: null pointer");
   ASF_CHECK_ARG(g->Cin == 1 && g->kt * g->kf <= STEM_MAX_TAPS && g->Cout <= 256 && 256 % g->Cout == 0,
                 "asf_stem_wgrad: needs Cin == 1, <= %d taps, Cout dividing 256", STEM_MAX_TAPS);
   cudaStream_t st = (cudaStream_t)stream;
-  const int taps = g->kt * g->kf;
-  if (!accumulate) ASF_CUDA(cudaMemsetAsync(dw_oihw, 0, sizeof(float) * (size_t)g->Cout * taps, st));
-  if (dout_dtype == ASF_BF16 && g->Cout % 8 == 0 && g->kf <= 8 && (g->Cout / 8) * g->kt <= 256 && ld8(g->ld_out) && al16(dout))
-    return stem_wgrad_v8(in, (const bf16*)dout, dw_oihw, g, st);
-  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
-  int64_t blocks = 148 * 4;
-  int64_t rpb = cdiv(rows, blocks);
-  const int RL = 256 / g->Cout;
-  if (rpb < RL) rpb = RL;
-  blocks = cdiv(rows, rpb);
+  if (stem_vec_ok(g, dout_dtype) && al16(dout)) return stem_wgrad_v9(in, (const bf16*)dout, dwp, g, st);
+  ASF_CHECK_ARG(!stem_vec_ok(g, dout_dtype), "asf_stem_wgrad: dout must be 16-byte aligned");
+  int64_t blocks, rpb;
+  stem_scalar_geom(g, &blocks, &rpb);
   ASF_DISPATCH_DTYPE(dout_dtype, TD, {
-    stem_wgrad_kernel<TD><<<(unsigned)blocks, 256, 0, st>>>(in, (const TD*)dout, dw_oihw, *g, rpb);
+    stem_wgrad_kernel<TD><<<(unsigned)blocks, 256, 0, st>>>(in, (const TD*)dout, dwp, *g, rpb);
     ASF_LAUNCH_CHECK();
     return 0;
   });

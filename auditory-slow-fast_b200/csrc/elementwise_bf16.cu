@@ -7,6 +7,7 @@
 // Replaces the separate cuDNN BatchNorm / ATen elementwise / pooling kernels behind
 //   /root/reference/audio_slowfast/models/stem_helper.py:150-168, resnet_helper.py:181-225, :335-341.
 #include "common.cuh"
+#include "stats_reduce.cuh"
 
 namespace asf {
 
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict
                                                           const bf16* __restrict__ res, int64_t ld_res,
                                                           bf16* __restrict__ y, int64_t ld_y, int64_t rows, int C,
                                                           int CVB, int64_t rows_per_block, float* scale, float* shift,
-                                                          int relu, const float* __restrict__ stats, double count,
+                                                          int relu, const double* __restrict__ stats, double count,
                                                           const float* __restrict__ gamma,
                                                           const float* __restrict__ beta, float eps, float momentum,
                                                           float* running_mean, float* running_var,
@@ -95,7 +96,14 @@ __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict
   if (FINALIZE) {
     const bool publish = blockIdx.x == 0 && rl == 0;
     if (publish && c == 0 && num_batches_tracked) *num_batches_tracked += 1;
-    const F8 s0 = ldf8(stats + c), s1 = ldf8(stats + C + c);
+    // the sums are doubles (ordered two-stage reduction): mean and E[x^2] - mean^2 are formed in double, so the
+    // variance does not lose digits to the cancellation; only the final rsqrt runs in fp32 in the streaming blocks
+    double s0[8], s1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s0[j] = stats[c + j];
+      s1[j] = stats[C + c + j];
+    }
     F8 ga, be;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -103,22 +111,21 @@ __global__ void __launch_bounds__(256) bn_apply_v8_kernel(const bf16* __restrict
       be.v[j] = beta ? beta[c + j] : 0.f;
     }
     if (!publish) {
-      // streaming blocks: fp32 (agrees with the published double-precision values to ~1e-6 relative, far below the
-      // bf16 rounding of y); the double divisions / square roots would otherwise dominate short row ranges
-      const float inv_n = (float)(1.0 / count);
+      const double inv_n = 1.0 / count;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float mean = s0.v[j] * inv_n;
-        const float var = fmaxf(fmaf(-mean, mean, s1.v[j] * inv_n), 0.f);
+        const double mean = s0[j] * inv_n;
+        const float var = fmaxf((float)fma(-mean, mean, s1[j] * inv_n), 0.f);
+        const float mf = (float)mean;
         sc.v[j] = ga.v[j] * rsqrtf(var + eps);
-        sh.v[j] = fmaf(-mean, sc.v[j], be.v[j]);
+        sh.v[j] = fmaf(-mf, sc.v[j], be.v[j]);
       }
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       if (publish) {
-        const double mean = (double)s0.v[j] / count;
-        double var = (double)s1.v[j] / count - mean * mean;
+        const double mean = s0[j] / count;
+        double var = s1[j] / count - mean * mean;
         if (var < 0.0) var = 0.0;
         const float invstd = (float)(1.0 / sqrt(var + (double)eps));
         sc.v[j] = ga.v[j] * invstd;
@@ -185,7 +192,7 @@ int bn_apply_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf
 }
 
 int bn_train_fwd_v8(const bf16* x, int64_t ld_x, const bf16* res, int64_t ld_res, bf16* y, int64_t ld_y, int64_t rows,
-                    int C, const float* stats, double count, const float* gamma, const float* beta, float eps,
+                    int C, const double* stats, double count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked, float* scale,
                     float* shift, float* save_mean, float* save_invstd, int relu, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 4);
@@ -206,7 +213,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __rest
                                                               const float* __restrict__ gamma,
                                                               const float* __restrict__ mean,
                                                               const float* __restrict__ invstd,
-                                                              const float* __restrict__ red, float inv_count,
+                                                              const double* __restrict__ red, double inv_count,
                                                               float* dgamma, float* dbeta, int accumulate) {
   pdl_trigger();
   pdl_wait();
@@ -214,12 +221,18 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __rest
   const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
   const int c = (blockIdx.y * CVB + cvl) * 8;
   if (rl >= RP || c >= C) return;
-  const F8 mu = ldf8(mean + c), is = ldf8(invstd + c), r0v = ldf8(red + c), r1v = ldf8(red + C + c);
+  const F8 mu = ldf8(mean + c), is = ldf8(invstd + c);
+  double r0v[8], r1v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    r0v[j] = red[c + j];
+    r1v[j] = red[C + c + j];
+  }
   if (blockIdx.x == 0 && rl == 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      if (dbeta) dbeta[c + j] = (accumulate ? dbeta[c + j] : 0.f) + r0v.v[j];
-      if (dgamma) dgamma[c + j] = (accumulate ? dgamma[c + j] : 0.f) + r1v.v[j];
+      if (dbeta) dbeta[c + j] = (accumulate ? dbeta[c + j] : 0.f) + (float)r0v[j];
+      if (dgamma) dgamma[c + j] = (accumulate ? dgamma[c + j] : 0.f) + (float)r1v[j];
     }
   }
   // o = a * (g - k0 - (x - mu) * is * k1) = a * g - (a * k0 - a * is * k1 * mu) - (a * is * k1) * x
@@ -228,8 +241,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __rest
   for (int j = 0; j < 8; ++j) {
     const float ga = gamma ? gamma[c + j] : 1.f;
     ca.v[j] = ga * is.v[j];
-    cb.v[j] = r0v.v[j] * inv_count;
-    cc.v[j] = r1v.v[j] * inv_count;
+    cb.v[j] = (float)(r0v[j] * inv_count);
+    cc.v[j] = (float)(r1v[j] * inv_count);
   }
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   int64_t r1 = r0 + rows_per_block;
@@ -262,8 +275,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v8_kernel(const bf16* __rest
 }
 
 int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, bf16* dx, int64_t ld_dx, int64_t rows,
-                    int C, const float* gamma, const float* mean, const float* invstd, const float* red,
-                    float inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st) {
+                    int C, const float* gamma, const float* mean, const float* invstd, const double* red,
+                    double inv_count, float* dgamma, float* dbeta, int accumulate, cudaStream_t st) {
   const ColGeom g = col_geom(rows, C, 4);
   ASF_CUDA(launch_pdl(bn_bwd_apply_v8_kernel, dim3(g.grid), dim3(256), 0, st, dz, ld_dz, x, ld_x, dx, ld_dx, rows, C, g.CVB, g.rows_per_block, gamma,
                                                 mean, invstd, red, inv_count, dgamma, dbeta, accumulate));
@@ -272,30 +285,32 @@ int bn_bwd_apply_v8(const bf16* dz, int64_t ld_dz, const bf16* x, int64_t ld_x, 
 }
 
 // ------------------------------------------------------------------------------------------- channel reductions
-// out[c] += sum_rows a ; out[C + c] += sum_rows (kBwd ? a * (x - mean) * invstd : a * a).
-// Row lanes that share a column inside a warp are folded with shuffles first (narrow tensors: C = 8 means 256 row
-// lanes per column), then the block folds through shared memory and issues one global atomic per channel.
+// out[c] = sum_rows a ; out[C + c] = sum_rows (kBwd ? a * (x - mean) * invstd : a * a), as doubles, DETERMINISTIC:
+//   thread:  streams its rows (four 16-byte loads in flight) into 8 + 8 fp32 accumulators;
+//   warp:    row lanes that share a column inside a warp are folded with xor-shuffles (a fixed tree);
+//   block:   the 8 warp partials of a column are added in warp order and STORED as this block's row of the workspace;
+//   grid:    the last block of a channel block to finish (ticket) adds the rows in ascending order in double.
+// A block covers CVB <= 32 vector columns (<= 256 channels) so that the final pass of one block stays short and the
+// channel blocks finish in parallel.  Workspace row of block (x, y): ws[(y * gridDim.x + x)][2][CVB * 8].
 template <bool kBwd>
 __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __restrict__ a, int64_t ld_a,
                                                                 const bf16* __restrict__ x, int64_t ld_x,
                                                                 int64_t rows, int C, int CVB, int64_t rows_per_block,
                                                                 const float* __restrict__ mean,
-                                                                const float* __restrict__ invstd, float* out) {
+                                                                const float* __restrict__ invstd, double* out,
+                                                                float* ws, unsigned* ticket) {
   pdl_trigger();
   pdl_wait();
-  __shared__ float s0[2048], s1[2048];
+  __shared__ __align__(16) float part[2][8][256];  // [sum | second sum][warp][channel of the block]
+  __shared__ unsigned s_flag;
   const int RP = 256 / CVB;
   const int cvl = threadIdx.x % CVB, rl = threadIdx.x / CVB;
   const int c = (blockIdx.y * CVB + cvl) * 8;
-  for (int i = threadIdx.x; i < CVB * 8; i += 256) {
-    s0[i] = 0.f;
-    s1[i] = 0.f;
-  }
-  __syncthreads();
+  const int warp = threadIdx.x >> 5;
   float acc0[8], acc1[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc0[j] = acc1[j] = 0.f;
-  const bool active = rl < RP && c < C;
+  const bool active = c < C;
   if (active) {
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     int64_t r1 = r0 + rows_per_block;
@@ -338,47 +353,63 @@ __global__ void __launch_bounds__(256) channel_reduce_v8_kernel(const bf16* __re
       }
     }
   }
-  // lanes of one warp that own the same column: lane ^ CVB, ^ 2 CVB, ... (CVB a power of two below 32)
-  const bool fold = CVB < 32 && (CVB & (CVB - 1)) == 0;
-  if (fold) {
-    for (int o = 16; o >= CVB; o >>= 1) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], o);
-        acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], o);
-      }
-    }
-  }
-  if (active && (!fold || (int)(threadIdx.x & 31) < CVB)) {
+  // lanes of one warp that own the same column: lane ^ CVB, ^ 2 CVB, ... (CVB is a power of two <= 32)
+  for (int o = 16; o >= CVB; o >>= 1) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      atomicAdd(&s0[cvl * 8 + j], acc0[j]);
-      atomicAdd(&s1[cvl * 8 + j], acc1[j]);
+      acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], o);
+      acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], o);
     }
+  }
+  if ((int)(threadIdx.x & 31) < CVB) {  // one holder per (warp, column); CVB == 32: a warp is one row lane
+    *(float4*)&part[0][warp][cvl * 8] = make_float4(acc0[0], acc0[1], acc0[2], acc0[3]);
+    *(float4*)&part[0][warp][cvl * 8 + 4] = make_float4(acc0[4], acc0[5], acc0[6], acc0[7]);
+    *(float4*)&part[1][warp][cvl * 8] = make_float4(acc1[0], acc1[1], acc1[2], acc1[3]);
+    *(float4*)&part[1][warp][cvl * 8 + 4] = make_float4(acc1[4], acc1[5], acc1[6], acc1[7]);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < CVB * 8; i += 256) {
-    const int cc = blockIdx.y * CVB * 8 + i;
-    if (cc < C) {
-      atomicAdd(out + cc, s0[i]);
-      atomicAdd(out + C + cc, s1[i]);
-    }
+  const int CB = CVB * 8;
+  float* my = ws + ((int64_t)blockIdx.y * gridDim.x + blockIdx.x) * 2 * CB;
+  for (int i = threadIdx.x; i < 2 * CB; i += 256) {
+    const int half = i / CB, ch = i - half * CB;
+    float t = part[half][0][ch];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) t += part[half][w][ch];
+    my[i] = t;
   }
+  if (!stats_last_cta(ticket + blockIdx.y, gridDim.x, &s_flag)) return;
+  const float* col = ws + (int64_t)blockIdx.y * gridDim.x * 2 * CB;
+  const int c0 = blockIdx.y * CB;
+  stats_ordered_reduce(col, (int)gridDim.x, 2 * CB, 2 * CB, (double*)&part[0][0][0], [&](int s, double v) {
+    const int half = s / CB, cc = c0 + (s - half * CB);
+    if (cc < C) out[half * C + cc] = v;
+  });
 }
 
 template <bool kBwd>
 int channel_reduce_v8(const bf16* a, int64_t ld_a, const bf16* x, int64_t ld_x, int64_t rows, int C, const float* mean,
-                      const float* invstd, float* out, cudaStream_t st) {
-  const ColGeom g = col_geom(rows, C, 2);
-  ASF_CUDA(launch_pdl(channel_reduce_v8_kernel<kBwd>, dim3(g.grid), dim3(256), 0, st, a, ld_a, x, ld_x, rows, C, g.CVB, g.rows_per_block, mean, invstd,
-                                                        out));
+                      const float* invstd, double* out, float* ws, unsigned* ticket, cudaStream_t st) {
+  const int CV = C / 8;
+  int CVB = 1;
+  while (CVB < 32 && CVB < CV) CVB *= 2;
+  const int cblocks = (int)cdiv(CV, CVB);
+  ASF_CHECK_ARG(cblocks <= ASF_STATS_TICKETS, "channel reduce: %d channel blocks exceed the %d tickets", cblocks, ASF_STATS_TICKETS);
+  const int RP = 256 / CVB;
+  int64_t target = 148 * 2 / cblocks;  // <= 296 blocks in all: the partial rows fit ASF_STATS_WS_FLOATS(C)
+  if (target < 1) target = 1;
+  int64_t rpb = cdiv(rows, target);
+  const int64_t quantum = (int64_t)RP * 4;
+  rpb = cdiv(rpb, quantum) * quantum;
+  dim3 grid((unsigned)cdiv(rows, rpb), (unsigned)cblocks);
+  ASF_CUDA(launch_pdl(channel_reduce_v8_kernel<kBwd>, grid, dim3(256), 0, st, a, ld_a, x, ld_x, rows, C, CVB, rpb, mean,
+                      invstd, out, ws, ticket));
   ASF_LAUNCH_CHECK();
   return 0;
 }
 template int channel_reduce_v8<false>(const bf16*, int64_t, const bf16*, int64_t, int64_t, int, const float*,
-                                      const float*, float*, cudaStream_t);
+                                      const float*, double*, float*, unsigned*, cudaStream_t);
 template int channel_reduce_v8<true>(const bf16*, int64_t, const bf16*, int64_t, int64_t, int, const float*,
-                                     const float*, float*, cudaStream_t);
+                                     const float*, double*, float*, unsigned*, cudaStream_t);
 
 // ------------------------------------------------------------------------------------------- ReLU backward / add
 __global__ void __launch_bounds__(256) relu_bwd_v8_kernel(const bf16* __restrict__ a, int64_t ld_a,
@@ -682,77 +713,21 @@ int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_con
   return 0;
 }
 
-// dw[n][it*kf + jf] += sum_rows dout[row][n] * in[row shifted by tap].  One thread owns 8 output channels x one
-// kernel row (kf <= 8 taps) and streams a slice of the output rows; a block folds its threads through shared-memory
-// atomics and issues one global atomic per weight.
+// dwp[block][n][it*kf + jf] = sum over the block's rows of dout[row][n] * in[row shifted by tap]  (stem, C_in = 1).
+// A WARP owns one (8-channel group, kernel row, row slice) task, lanes walk consecutive rows (dout loads of a warp are
+// contiguous, two rows per lane in flight, 32-bit index arithmetic), the 8 x kf accumulators are folded by xor-shuffles
+// (a fixed tree) and lane 0 stores them into the task's own shared-memory slot; the slices of a group are then added in
+// slice order and the block STORES its partial sums -- no atomics, bit-reproducible; the cross-block sum is
+// asf_unpack_wgrad(_multi)'s fixed-order split-K reduction.
 constexpr int STEM_KF_MAX = 8;
-__global__ void __launch_bounds__(256) stem_wgrad_v8_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
-                                                            float* __restrict__ dw, asf_conv_geom_t g,
-                                                            int64_t rows_per_block) {
-  pdl_trigger();
-  pdl_wait();
-  extern __shared__ float sacc[];  // [Cout][taps]
-  const int taps = g.kt * g.kf, CG = g.Cout / 8;
-  const int ngroups = CG * g.kt;
-  const int RL = 256 / ngroups;
-  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) sacc[i] = 0.f;
-  __syncthreads();
-  const int grp = threadIdx.x % ngroups, rl = threadIdx.x / ngroups;
-  if (rl < RL) {
-    const int cg = grp % CG, it = grp / CG;
-    float acc[8][STEM_KF_MAX];
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-#pragma unroll
-      for (int k = 0; k < STEM_KF_MAX; ++k) acc[j][k] = 0.f;
-    const int64_t rows = (int64_t)g.B * g.Tout * g.Fout;
-    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
-    const int64_t r1 = (r0 + rows_per_block < rows) ? r0 + rows_per_block : rows;
-    for (int64_t row = r0 + rl; row < r1; row += RL) {
-      const int fo = (int)(row % g.Fout);
-      const int64_t r2 = row / g.Fout;
-      const int to = (int)(r2 % g.Tout);
-      const int b = (int)(r2 / g.Tout);
-      const int t = to * g.st + it - g.pt;
-      if (t < 0 || t >= g.Tin) continue;
-      const F8 d = unpack8(*(const uint4*)(dout + row * g.ld_out + cg * 8));
-      const float* ip = in + ((int64_t)b * g.Tin + t) * g.Fin;
-      const int f0 = fo * g.sf - g.pf;
-#pragma unroll
-      for (int k = 0; k < STEM_KF_MAX; ++k) {
-        const int f = f0 + k;
-        if (k < g.kf && f >= 0 && f < g.Fin) {
-          const float xv = ip[f];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j][k] = fmaf(d.v[j], xv, acc[j][k]);
-        }
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-#pragma unroll
-      for (int k = 0; k < STEM_KF_MAX; ++k)
-        if (k < g.kf) atomicAdd(&sacc[(cg * 8 + j) * taps + it * g.kf + k], acc[j][k]);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) atomicAdd(dw + i, sacc[i]);
-}
-
-// Second generation: a WARP owns one (8-channel group, kernel row) and a slice of the block's output rows, lanes walk
-// consecutive rows (dout loads of a warp are contiguous, two rows per lane in flight, 32-bit index arithmetic), the
-// 8 x kf accumulators are folded by shuffles and only lane 0 touches the shared accumulators.  The v8 kernel spent its
-// time in 64-bit div/mod per row and in 51-way contended shared atomics (157 us for the fast stem, the last kernel of
-// the backward pass and therefore on the critical path of the step).
 __global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
-                                                            float* __restrict__ dw, asf_conv_geom_t g, int rows_per_block,
+                                                            float* __restrict__ dwp, asf_conv_geom_t g, int rows_per_block,
                                                             int nslice) {
   pdl_trigger();
   pdl_wait();
-  extern __shared__ float sacc[];  // [Cout][taps]
+  extern __shared__ float sacc[];  // [nslice][ngroups][8][STEM_KF_MAX]
   const int taps = g.kt * g.kf, CG = g.Cout / 8;
   const int ngroups = CG * g.kt;
-  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) sacc[i] = 0.f;
-  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rows = g.B * g.Tout * g.Fout;
   const int r0 = blockIdx.x * rows_per_block;
@@ -804,6 +779,7 @@ __global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restr
           for (int j = 0; j < 8; ++j) acc[j][k] = fmaf(d.v[j], xv[h][k], acc[j][k]);
       }
     }
+    float* slot = sacc + (size_t)task * 8 * STEM_KF_MAX;  // task = sl * ngroups + grp
 #pragma unroll
     for (int j = 0; j < 8; ++j)
 #pragma unroll
@@ -812,43 +788,55 @@ __global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restr
           float v = acc[j][k];
 #pragma unroll
           for (int sft = 16; sft >= 1; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
-          if (lane == 0) atomicAdd(&sacc[(cg * 8 + j) * taps + it * g.kf + k], v);
+          if (lane == 0) slot[j * STEM_KF_MAX + k] = v;
         }
       }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) atomicAdd(dw + i, sacc[i]);
+  float* my = dwp + (size_t)blockIdx.x * g.Cout * taps;
+  for (int i = threadIdx.x; i < g.Cout * taps; i += 256) {
+    const int n = i / taps, tp = i - n * taps;
+    const int it = tp / g.kf, k = tp - it * g.kf;
+    const int grp = it * CG + (n >> 3), j = n & 7;
+    float t = 0.f;
+    for (int sl = 0; sl < nslice; ++sl) t += sacc[((size_t)(sl * ngroups + grp) * 8 + j) * STEM_KF_MAX + k];
+    my[i] = t;
+  }
 }
 
-int stem_wgrad_v8(const float* in, const bf16* dout, float* dw, const asf_conv_geom_t* g, cudaStream_t st) {
+static void stem_v9_geom(const asf_conv_geom_t* g, int* nslice, int64_t* blocks, int64_t* rpb) {
   const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
   const int ngroups = (g->Cout / 8) * g->kt;
-  const size_t smem = sizeof(float) * (size_t)g->Cout * g->kt * g->kf;
-  static int use_v8 = -1;
-  if (use_v8 < 0) {
-    const char* e = getenv("ASF_STEM_WGRAD_V8");
-    use_v8 = (e && e[0] == '1') ? 1 : 0;
-  }
-  if (!use_v8 && rows < (1LL << 31) && (int64_t)g->B * g->Tin * g->Fin < (1LL << 31)) {
-    // (group, slice) tasks are dealt round robin to the 8 warps of a block: the smallest slice count that balances them
-    int nslice = 1;
-    while ((ngroups * nslice) % 8) ++nslice;
-    int64_t blocks = 148 * 2;
-    int64_t rpb = cdiv(rows, blocks);
-    const int64_t min_rpb = 64LL * 4 * nslice;  // at least four double-row rounds per task
-    if (rpb < min_rpb) rpb = min_rpb;
-    blocks = cdiv(rows, rpb);
-    ASF_CUDA(launch_pdl(stem_wgrad_v9_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dw, *g, (int)rpb,
-                        nslice));
-    ASF_LAUNCH_CHECK();
-    return 0;
-  }
-  const int RL = 256 / ngroups;
-  int64_t blocks = 148 * 4;
-  int64_t rpb = cdiv(rows, blocks);
-  if (rpb < RL * 8) rpb = RL * 8;
-  blocks = cdiv(rows, rpb);
-  ASF_CUDA(launch_pdl(stem_wgrad_v8_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dw, *g, rpb));
+  // (group, slice) tasks are dealt round robin to the 8 warps of a block: the smallest slice count that balances them
+  int ns = 1;
+  while ((ngroups * ns) % 8) ++ns;
+  int64_t b = 148 * 2;
+  int64_t r = cdiv(rows, b);
+  const int64_t min_rpb = 64LL * 4 * ns;  // at least four double-row rounds per task
+  if (r < min_rpb) r = min_rpb;
+  *nslice = ns;
+  *rpb = r;
+  *blocks = cdiv(rows, r);
+}
+
+int stem_wgrad_v9_blocks(const asf_conv_geom_t* g) {
+  int ns;
+  int64_t blocks, rpb;
+  stem_v9_geom(g, &ns, &blocks, &rpb);
+  return (int)blocks;
+}
+
+int stem_wgrad_v9(const float* in, const bf16* dout, float* dwp, const asf_conv_geom_t* g, cudaStream_t st) {
+  const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
+  ASF_CHECK_ARG(rows < (1LL << 31) && (int64_t)g->B * g->Tin * g->Fin < (1LL << 31), "asf_stem_wgrad: tensor too large");
+  const int ngroups = (g->Cout / 8) * g->kt;
+  int nslice;
+  int64_t blocks, rpb;
+  stem_v9_geom(g, &nslice, &blocks, &rpb);
+  const size_t smem = sizeof(float) * (size_t)nslice * ngroups * 8 * STEM_KF_MAX;
+  ASF_CHECK_ARG(smem <= 48 * 1024, "asf_stem_wgrad: %zu bytes of task slots exceed 48 KB", smem);
+  ASF_CUDA(launch_pdl(stem_wgrad_v9_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dwp, *g, (int)rpb,
+                      nslice));
   ASF_LAUNCH_CHECK();
   return 0;
 }

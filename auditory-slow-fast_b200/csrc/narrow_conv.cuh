@@ -85,9 +85,7 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
       if (i < G) wfrag[i] = q[u];
     }
   }
-  float* sstat = (float*)(wfrag + G);  // [2][N] CTA-level statistics
-  if (STATS)
-    for (int i = threadIdx.x; i < 16 * NO; i += NC_THREADS) sstat[i] = 0.f;
+  float* sstat = (float*)(wfrag + G);  // STATS: [4 warps][2][N] warp partial sums, then 128 doubles + a flag
   __syncthreads();
   pdl_wait();
 
@@ -213,6 +211,10 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
     }
   }
   if (STATS) {
+    // deterministic statistics: fixed xor-shuffle tree over the 8 row groups of a warp, one slot per warp in shared
+    // memory, warps added in order, one workspace row per CTA, ordered final pass by the last CTA (stats_reduce.cuh)
+    constexpr int N = 8 * NO;
+    const int warp = threadIdx.x >> 5;
 #pragma unroll
     for (int j = 0; j < NO; ++j) {
 #pragma unroll
@@ -223,15 +225,24 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
           ssq[j][c] += __shfl_xor_sync(0xffffffffu, ssq[j][c], sft);
         }
         if (g == 0) {
-          atomicAdd(sstat + 8 * j + 2 * t + c, ssum[j][c]);
-          atomicAdd(sstat + 8 * NO + 8 * j + 2 * t + c, ssq[j][c]);
+          sstat[warp * 2 * N + 8 * j + 2 * t + c] = ssum[j][c];
+          sstat[warp * 2 * N + N + 8 * j + 2 * t + c] = ssq[j][c];
         }
       }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 8 * NO; i += NC_THREADS) {
-      atomicAdd(p.epi.stats + i, sstat[i]);
-      atomicAdd(p.epi.stats + p.epi.stats_stride + i, sstat[8 * NO + i]);
+    float* my = p.epi.stats_ws + (long long)blockIdx.x * 2 * N;
+    for (int i = threadIdx.x; i < 2 * N; i += NC_THREADS)
+      my[i] = ((sstat[i] + sstat[2 * N + i]) + sstat[4 * N + i]) + sstat[6 * N + i];
+    double* scratch = (double*)(sstat + 8 * N);
+    unsigned* flag = (unsigned*)(scratch + NC_THREADS);
+    if (stats_last_cta(p.epi.stats_ticket, gridDim.x, flag)) {
+      double* out = p.epi.stats;
+      const int stride = p.epi.stats_stride;
+      stats_ordered_reduce(p.epi.stats_ws, (int)gridDim.x, 2 * N, 2 * N, scratch, [&](int s_, double v) {
+        const int half = s_ / N;
+        out[half * stride + (s_ - half * N)] = v;
+      });
     }
   }
 }
@@ -304,11 +315,15 @@ static int narrow_conv_launch(const asf_tapgemm_t* q, cudaStream_t st) {
   p.tiles = (int)cdiv(p.m_total, 16);
   p.epi = q->epi;
   const int no = q->N / 8, wpc = NC_THREADS / 32;
-  const int smem = p.steps * no * 32 * 16 + 2 * q->N * 4;
+  const int smem = p.steps * no * 32 * 16 + (q->epi.stats ? 8 * q->N * 4 + NC_THREADS * 8 + 16 : 0);
   long long grid = cdiv(p.tiles, wpc);
-  // resident CTAs per SM by register count (64 / 72 / 94 / 128 registers); a warp then walks its tiles
-  const long long cap = (long long)num_sms() * (no <= 2 ? 8 : no == 4 ? 5 : 4);
+  // resident CTAs per SM by register count (64 / 72 / 94 / 128 registers); a warp then walks its tiles.
+  // With statistics every CTA leaves one workspace row for the ordered final pass: at most 4 CTAs per SM.
+  const long long cap = (long long)num_sms() * (q->epi.stats ? 4 : (no <= 2 ? 8 : no == 4 ? 5 : 4));
   if (grid > cap) grid = cap;
+  if (q->epi.stats)
+    ASF_CHECK_ARG(q->epi.stats_ws && q->epi.stats_ticket && grid * 2 * q->N <= ASF_STATS_WS_FLOATS(q->N),
+                  "asf_tapgemm: statistics need stats_ws / stats_ticket");
   switch (no) {
     case 1: return narrow_conv_launch_no<1>(p, (int)grid, smem, st);
     case 2: return narrow_conv_launch_no<2>(p, (int)grid, smem, st);

@@ -14,6 +14,11 @@
 constexpr int EPI_SLAB_COLS = 32;
 constexpr int EPI_SLAB_BYTES = TG_BLOCK_M * EPI_SLAB_COLS * 2;  // 8192
 constexpr int EPI_SHIFT_FLOATS = 256;
+// training-BN statistics (STATS launches only): per epilogue group [2][256] column accumulators + [4 warps][64] slab
+// partials.  Deterministic: no atomics, fixed summation order (see epi_slab_stats_part / epi_stats_accumulate).
+constexpr int EPI_STAT_ACC_FLOATS = 2 * 256;
+constexpr int EPI_STAT_SCR_FLOATS = 4 * 64;
+constexpr int EPI_STAT_FLOATS = 2 * (EPI_STAT_ACC_FLOATS + EPI_STAT_SCR_FLOATS);
 constexpr int TGT_THREADS = 352;  // warp 0: TMA (activations), 1: MMA, 2..9: epilogue, 10: TMA (weights)
 
 __device__ __forceinline__ uint32_t slab_off(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
@@ -71,13 +76,10 @@ __device__ __forceinline__ void epi_slab_math(const uint32_t* raw, const float* 
 
 // Column sums / sums of squares of one finished bf16 slab (rows outside the tensor were written as zeros).
 // t = thread index inside the 128-thread epilogue group.  Thread t owns channel pair (2w, 2w+1), w = t & 15, of rows
-// (t >> 4) + 8 i: a warp reads two adjacent rows per step = one conflict-free 128-byte wavefront.
-__device__ __forceinline__ void red_shared_f32(float* p, float v) {
-  asm volatile("red.shared::cta.add.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
-}
-template <bool SMEM>
-__device__ __forceinline__ void epi_slab_stats(const uint8_t* slab, int t, float* gsum, float* gsq, int col0, int N) {
-  // gsum / gsq: global statistics, or the CTA's shared accumulators when one N tile covers all channels
+// (t >> 4) + 8 i: a warp reads two adjacent rows per step = one conflict-free 128-byte wavefront.  The two row groups of
+// a warp are folded with one xor-shuffle; lanes 0..15 then STORE the warp's partial sums into the warp's own 64 floats
+// of `wscr` ([sum 32 | sum of squares 32]).  epi_stats_accumulate adds the four warps in warp order.
+__device__ __forceinline__ void epi_slab_stats_part(const uint8_t* slab, int t, float* wscr) {
   const int w = t & 15, rg = t >> 4;
   float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
@@ -93,27 +95,17 @@ __device__ __forceinline__ void epi_slab_stats(const uint8_t* slab, int t, float
   q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
   q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
   if ((t & 16) == 0) {
-    const int n = col0 + 2 * w;
-    if (SMEM) {
-      if (n < N) {
-        red_shared_f32(gsum + n, s0);
-        red_shared_f32(gsq + n, q0);
-      }
-      if (n + 1 < N) {
-        red_shared_f32(gsum + n + 1, s1);
-        red_shared_f32(gsq + n + 1, q1);
-      }
-    } else {
-      if (n < N) {
-        atomicAdd(gsum + n, s0);
-        atomicAdd(gsq + n, q0);
-      }
-      if (n + 1 < N) {
-        atomicAdd(gsum + n + 1, s1);
-        atomicAdd(gsq + n + 1, q1);
-      }
-    }
+    float* d = wscr + (t >> 5) * 64;
+    *(float2*)(d + 2 * w) = make_float2(s0, s1);
+    *(float2*)(d + 32 + 2 * w) = make_float2(q0, q1);
   }
+}
+// threads t < 64 of a group: slot t = (half, channel) of the pending slab; the group's accumulator of that column is
+// owned by this one thread, so the order of additions over slabs and tiles is the program order.
+__device__ __forceinline__ void epi_stats_accumulate(float* acc, const float* wscr, int t, int col0) {
+  const int half = t >> 5, ch = t & 31;
+  const float v = ((wscr[t] + wscr[64 + t]) + wscr[128 + t]) + wscr[192 + t];
+  acc[half * 256 + col0 + ch] += v;
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
@@ -134,7 +126,8 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
   const int OD = p.op_depth;  // operand ring depth
   const int group_bytes = (2 + OD * n_ops) * EPI_SLAB_BYTES;
   float* shift_base = (float*)(epi_base + 2 * group_bytes);
-  TgShared* sh = (TgShared*)(shift_base + 2 * EPI_SHIFT_FLOATS);
+  float* stat_base = shift_base + 2 * EPI_SHIFT_FLOATS;  // STATS: [2 groups][acc 512 | scratch 256]
+  TgShared* sh = (TgShared*)(stat_base + (STATS ? EPI_STAT_FLOATS : 0));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.m_tiles_total * p.n_tiles;
 
@@ -156,12 +149,10 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&sh->tmem_base, 512);
-  // Training-BN statistics: when one N tile covers every channel the CTA sums into shared memory (the two shift
-  // areas, unused in this mode, = [2][256] floats) and touches each global counter once, at the end; thousands of
-  // same-address L2 atomics per launch serialise at ~7 ns each otherwise.
-  const bool stats_smem = STATS && p.n_tiles == 1;
-  if (stats_smem && threadIdx.x >= 64 && threadIdx.x < 320)
-    for (int i = (int)threadIdx.x - 64; i < 2 * EPI_SHIFT_FLOATS; i += 256) shift_base[i] = 0.f;
+  // Training-BN statistics: the launcher sizes the grid as a multiple of n_tiles, so this CTA keeps ONE N tile for all
+  // its M tiles; each epilogue group sums its slabs' columns into its own shared-memory accumulators.
+  if (STATS && threadIdx.x >= 64 && threadIdx.x < 320)
+    for (int i = (int)threadIdx.x - 64; i < EPI_STAT_FLOATS; i += 256) stat_base[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -282,6 +273,9 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
     const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
     uint32_t gs = 0;  // slabs processed by this group so far (selects buffers and mbarrier parities)
+    float* st_acc = stat_base + group * (EPI_STAT_ACC_FLOATS + EPI_STAT_SCR_FLOATS);
+    float* st_scr = st_acc + EPI_STAT_ACC_FLOATS;
+    int st_pend = -1;  // column offset of the slab whose warp partials wait in st_scr (uniform across the group)
     // Operand prefetch runs one slab ahead of the math ACROSS tile boundaries (leader thread only): the sequence of
     // (tile, slab) pairs of a group is known up front, and for narrow layers (one slab per tile) the TMA latency of
     // the residual / mask slab would otherwise sit in every tile's critical path.
@@ -389,6 +383,12 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         }
         if (n_ops > 0) mbar_wait_warp(&sh->op_full[group][oslot], oph, 5);
         named_bar(bar_id, 128);  // out_buf[b] is free for everybody
+        if (STATS && st_pend >= 0) {
+          // every warp stored its partials of the previous slab before this barrier, and nobody overwrites them before
+          // the next one ("slab complete")
+          if (t < 64) epi_stats_accumulate(st_acc, st_scr, t, st_pend);
+          st_pend = -1;
+        }
         uint8_t* ob = out_buf + b * EPI_SLAB_BYTES;
         const uint8_t* op0 = op_buf + oslot * EPI_SLAB_BYTES;
         const uint8_t* op1 = op_buf + (OD + oslot) * EPI_SLAB_BYTES;
@@ -423,14 +423,16 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           bulk_commit();
         }
         if (STATS) {
-          if (stats_smem)
-            epi_slab_stats<true>(ob, t, shift_base, shift_base + EPI_SHIFT_FLOATS, s * 32, p.block_n);
-          else
-            epi_slab_stats<false>(ob, t, p.epi.stats, p.epi.stats + p.epi.stats_stride, n0 + s * 32, p.N);
+          epi_slab_stats_part(ob, t, st_scr);
+          st_pend = s * 32;
         }
         __syncwarp();
       }
       if (leader) pb.end(5);  // tmem_full seen -> last slab of the tile handed to the store engine
+    }
+    if (STATS && st_pend >= 0) {
+      named_bar(bar_id, 128);
+      if (t < 64) epi_stats_accumulate(st_acc, st_scr, t, st_pend);
     }
     if (leader) {
       pb.begin();
@@ -453,10 +455,25 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g3));
     atomicMax(p.dbg + 12, g3);
   }
-  if (stats_smem && threadIdx.x >= 64 && threadIdx.x < 320) {
-    for (int i = (int)threadIdx.x - 64; i < p.N; i += 256) {
-      atomicAdd(p.epi.stats + i, shift_base[i]);
-      atomicAdd(p.epi.stats + p.epi.stats_stride + i, shift_base[EPI_SHIFT_FLOATS + i]);
+  if (STATS) {
+    // this CTA's row of the workspace: ws[n_tile][row][2][block_n]; the last CTA of the column (ticket) adds the rows
+    // in ascending order in double and writes the final sums (stats_reduce.cuh)
+    const int n_tile = (int)blockIdx.x % p.n_tiles, prow = (int)blockIdx.x / p.n_tiles, P = (int)gridDim.x / p.n_tiles;
+    const int bn = p.block_n;
+    float* col = p.epi.stats_ws + (long long)n_tile * P * 2 * bn;
+    float* my = col + (long long)prow * 2 * bn;
+    const float* g0 = stat_base, * g1 = stat_base + EPI_STAT_ACC_FLOATS + EPI_STAT_SCR_FLOATS;
+    for (int i = (int)threadIdx.x; i < 2 * bn; i += (int)blockDim.x) {
+      const int half = i >= bn ? 1 : 0, ch = i - half * bn;
+      my[i] = g0[half * 256 + ch] + g1[half * 256 + ch];
+    }
+    if (stats_last_cta(p.epi.stats_ticket + n_tile, (unsigned)P, &sh->stat_flag)) {
+      double* out = p.epi.stats;
+      const int stride = p.epi.stats_stride, N = p.N, n0 = n_tile * bn;
+      stats_ordered_reduce(col, P, 2 * bn, 2 * bn, (double*)smem, [&](int s_, double v) {
+        const int half = s_ >= bn ? 1 : 0, n = n0 + s_ - half * bn;
+        if (n < N) out[half * stride + n] = v;
+      });
     }
   }
 }

@@ -18,6 +18,7 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "stats_reduce.cuh"
 
 namespace asf {
 
@@ -26,8 +27,6 @@ constexpr int TG_MAX_STAGES = 8;
 constexpr int TG_BLOCK_M = 128;
 constexpr int TG_KC = 64;                 // bf16 elements per 128B swizzle row
 constexpr int TG_A_BYTES = TG_BLOCK_M * 128;
-constexpr int TG_THREADS = 320;           // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2..5 / 6..9 two epilogue groups
-constexpr int TG_SMEM_BUDGET = 200 * 1024;
 
 struct TgParams {
   CUtensorMap tm_a;  // mode 0: activations (A operand).   mode 1: X (activations, UMMA B operand)
@@ -77,6 +76,7 @@ struct TgShared {
   uint64_t tmem_empty[2];
   uint64_t op_full[2][4];  // [epilogue group][operand buffer] (TgParams::op_depth of them in use)
   uint32_t tmem_base;
+  uint32_t stat_flag;  // "this CTA drew the last statistics ticket" (stats_reduce.cuh)
 };
 
 __device__ __forceinline__ void tile_coords(const TgParams& p, int m_tile, int start[3]) {
@@ -101,312 +101,6 @@ __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t* r) {
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// residual / accumulate / mask operands of one 32-column chunk of one output row (four 8-column granules each),
-// fetched one chunk ahead of their use so that their latency hides behind the TMEM load + math of the previous chunk
-struct EpiOps {
-  uint4 res[4], acc[4], mask[4];
-};
-
-__device__ __forceinline__ void epi_prefetch(const TgParams& p, EpiOps& o, long long orow, int nb, bool valid) {
-  const asf_epilogue_t& e = p.epi;
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int n = nb + 8 * g;
-    if (valid && p.vec_ok && n + 8 <= p.N) {
-      if (e.res) o.res[g] = *(const uint4*)((const bf16*)e.res + orow * e.ld_res + n);
-      if (e.accumulate) o.acc[g] = *(const uint4*)((const bf16*)p.out + orow * p.ld_out + n);
-      if (e.mask) o.mask[g] = *(const uint4*)((const bf16*)e.mask + orow * e.ld_mask + n);
-    }
-  }
-}
-
-__device__ __forceinline__ void epi_chunk_bf16(const TgParams& p, const EpiOps& o, float* v, long long orow, int nb,
-                                               bool valid) {
-  const asf_epilogue_t& e = p.epi;
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int n = nb + 8 * g;
-    float* w = v + 8 * g;
-    if (n >= p.N) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) w[j] = 0.f;
-      continue;
-    }
-    if (p.vec_ok && n + 8 <= p.N) {
-      if (e.scale) {
-        const float4 s0 = *(const float4*)(e.scale + n), s1 = *(const float4*)(e.scale + n + 4);
-        w[0] *= s0.x; w[1] *= s0.y; w[2] *= s0.z; w[3] *= s0.w; w[4] *= s1.x; w[5] *= s1.y; w[6] *= s1.z; w[7] *= s1.w;
-      }
-      if (e.shift) {
-        const float4 s0 = *(const float4*)(e.shift + n), s1 = *(const float4*)(e.shift + n + 4);
-        w[0] += s0.x; w[1] += s0.y; w[2] += s0.z; w[3] += s0.w; w[4] += s1.x; w[5] += s1.y; w[6] += s1.z; w[7] += s1.w;
-      }
-      if (valid) {
-        if (e.res) {
-          const bf16* q = (const bf16*)&o.res[g];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) w[j] += __bfloat162float(q[j]);
-        }
-        if (e.accumulate) {
-          const bf16* q = (const bf16*)&o.acc[g];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) w[j] += __bfloat162float(q[j]);
-        }
-        if (e.relu) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) w[j] = fmaxf(w[j], 0.f);
-        }
-        if (e.mask) {
-          const bf16* q = (const bf16*)&o.mask[g];
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (!(__bfloat162float(q[j]) > 0.f)) w[j] = 0.f;
-        }
-        uint4 out;
-        __nv_bfloat162* ob = (__nv_bfloat162*)&out;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(w[2 * j], w[2 * j + 1]);
-        *(uint4*)((bf16*)p.out + orow * p.ld_out + n) = out;
-      }
-    } else {
-      bf16* op = (bf16*)p.out + orow * p.ld_out + n;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (n + j < p.N) {
-          if (e.scale) w[j] *= e.scale[n + j];
-          if (e.shift) w[j] += e.shift[n + j];
-          if (valid) {
-            if (e.res) w[j] += __bfloat162float(((const bf16*)e.res)[orow * e.ld_res + n + j]);
-            if (e.accumulate) w[j] += __bfloat162float(op[j]);
-            if (e.relu) w[j] = fmaxf(w[j], 0.f);
-            if (e.mask && !(__bfloat162float(((const bf16*)e.mask)[orow * e.ld_mask + n + j]) > 0.f)) w[j] = 0.f;
-            op[j] = __float2bfloat16_rn(w[j]);
-          }
-        } else {
-          w[j] = 0.f;
-        }
-      }
-    }
-  }
-}
-
-__device__ __forceinline__ void epi_chunk_f32(const TgParams& p, float* v, long long orow, int nb, bool valid) {
-  const asf_epilogue_t& e = p.epi;
-  float* op = (float*)p.out + orow * p.ld_out + nb;
-#pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const int n = nb + j;
-    if (n < p.N) {
-      if (e.scale) v[j] *= e.scale[n];
-      if (e.shift) v[j] += e.shift[n];
-      if (valid) {
-        if (e.res) v[j] += ((const float*)e.res)[orow * e.ld_res + n];
-        if (e.accumulate) v[j] += op[j];
-        if (e.relu) v[j] = fmaxf(v[j], 0.f);
-        if (e.mask && !(((const float*)e.mask)[orow * e.ld_mask + n] > 0.f)) v[j] = 0.f;
-        op[j] = v[j];
-      }
-    } else {
-      v[j] = 0.f;
-    }
-  }
-}
-
-// per-channel sum / sum of squares over the 32 rows of this warp for 16 consecutive channels: recursive-halving
-// transpose-reduce (16 shuffles per quantity instead of 80), then one atomic per channel from the even lanes.
-__device__ __forceinline__ void epi_stats16(const TgParams& p, const float* v, int nb, bool valid, int lane) {
-  const asf_epilogue_t& e = p.epi;
-  float a[16], q[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float x = valid ? v[j] : 0.f;
-    a[j] = x;
-    q[j] = x * x;
-  }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const bool up = lane & 16;
-    const float sa_ = up ? a[i] : a[i + 8], ka = up ? a[i + 8] : a[i];
-    const float sq_ = up ? q[i] : q[i + 8], kq = up ? q[i + 8] : q[i];
-    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 16);
-    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 16);
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const bool up = lane & 8;
-    const float sa_ = up ? a[i] : a[i + 4], ka = up ? a[i + 4] : a[i];
-    const float sq_ = up ? q[i] : q[i + 4], kq = up ? q[i + 4] : q[i];
-    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 8);
-    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 8);
-  }
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const bool up = lane & 4;
-    const float sa_ = up ? a[i] : a[i + 2], ka = up ? a[i + 2] : a[i];
-    const float sq_ = up ? q[i] : q[i + 2], kq = up ? q[i + 2] : q[i];
-    a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, 4);
-    q[i] = kq + __shfl_xor_sync(0xffffffffu, sq_, 4);
-  }
-  {
-    const bool up = lane & 2;
-    const float sa_ = up ? a[0] : a[1], ka = up ? a[1] : a[0];
-    const float sq_ = up ? q[0] : q[1], kq = up ? q[1] : q[0];
-    a[0] = ka + __shfl_xor_sync(0xffffffffu, sa_, 2);
-    q[0] = kq + __shfl_xor_sync(0xffffffffu, sq_, 2);
-  }
-  a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
-  q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
-  const int jch = (((lane >> 4) & 1) << 3) | (((lane >> 3) & 1) << 2) | (((lane >> 2) & 1) << 1) | ((lane >> 1) & 1);
-  const int n = nb + jch;
-  if (!(lane & 1) && n < p.N) {
-    atomicAdd(e.stats + n, a[0]);
-    atomicAdd(e.stats + e.stats_stride + n, q[0]);
-  }
-}
-
-// ------------------------------------------------------------------------------------------------ mode 0
-__global__ void __launch_bounds__(TG_THREADS, 1) tapgemm_fwd_kernel(const __grid_constant__ TgParams p) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const int b_bytes = p.block_n * 128;
-  const int stage_bytes = TG_A_BYTES + b_bytes;
-  TgShared* sh = (TgShared*)(smem + (size_t)p.stages * stage_bytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_tiles = p.m_tiles_total * p.n_tiles;
-  const int kiters = p.ntaps * p.kchunks;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tm_a);
-    tma_prefetch_desc(&p.tm_b);
-    for (int s = 0; s < p.stages; ++s) {
-      mbar_init(&sh->full[s], 1);
-      mbar_init(&sh->empty[s], 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&sh->tmem_full[i], 1);
-      mbar_init(&sh->tmem_empty[i], 4);
-    }
-    fence_barrier_init();
-  }
-  if (warp == 1) tmem_alloc(&sh->tmem_base, 512);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = sh->tmem_base;
-
-  if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
-        int st[3];
-        tile_coords(p, m_tile, st);
-        int base[5] = {0, 0, 0, 0, 0};
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-          if (p.m_to_a[j] > 0) base[p.m_to_a[j]] = st[j];
-        for (int tap = 0; tap < p.ntaps; ++tap) {
-          const int c1 = base[1] + p.a_off[tap][0], c2 = base[2] + p.a_off[tap][1], c3 = base[3] + p.a_off[tap][2],
-                    c4 = base[4] + p.a_off[tap][3];
-          for (int kc = 0; kc < p.kchunks; ++kc) {
-            mbar_wait(&sh->empty[s], ph ^ 1, 1);
-            uint8_t* sa = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&sh->full[s], (uint32_t)stage_bytes);
-            tma_load(&p.tm_a, &sh->full[s], sa, p.rank_a, kc * TG_KC, c1, c2, c3, c4);
-            tma_load(&p.tm_b, &sh->full[s], sa + TG_A_BYTES, 3, kc * TG_KC, p.b_tap[tap], n_tile * p.block_n, 0, 0);
-            if (++s == p.stages) { s = 0; ph ^= 1; }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(TG_BLOCK_M, p.block_n, 0, 0);
-      int s = 0;
-      uint32_t ph = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int buf = it & 1;
-        mbar_wait(&sh->tmem_empty[buf], ((it >> 1) & 1) ^ 1, 2);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 256);
-        for (int ki = 0; ki < kiters; ++ki) {
-          mbar_wait(&sh->full[s], ph, 3);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint64_t adesc = make_sdesc(sa, 16, 1024);
-          const uint64_t bdesc = make_sdesc(sa + TG_A_BYTES, 16, 1024);
-          const int kc = ki % p.kchunks;
-          const int ksteps = min(TG_KC / 16, (p.K - kc * TG_KC + 15) >> 4);  // skip the zero-filled tail of a short chunk
-          for (int k = 0; k < ksteps; ++k)  // +32 bytes (2 x 16B units) per UMMA_K=16 step inside the swizzle row
-            umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (ki | k) != 0);
-          umma_commit(&sh->empty[s]);
-          if (++s == p.stages) { s = 0; ph ^= 1; }
-        }
-        umma_commit(&sh->tmem_full[buf]);
-      }
-    }
-  } else {
-    // ===== epilogue: two groups of four warps (warps 2..5 own TMEM buffer 0, warps 6..9 buffer 1), so the
-    // epilogues of two consecutive tiles run concurrently.  TMEM lane quarter of a warp = warp % 4.
-    const int group = (warp - 2) >> 2;
-    const int quarter = warp & 3;
-    const int r = quarter * 32 + lane;
-    const int r1 = r & ((1 << p.m_log2[0]) - 1);
-    const int r2 = (r >> p.m_log2[0]) & ((1 << p.m_log2[1]) - 1);
-    const int r3 = r >> (p.m_log2[0] + p.m_log2[1]);
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      if ((it & 1) != group) continue;
-      const int buf = group;
-      const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
-      int st[3];
-      tile_coords(p, m_tile, st);
-      const int m1 = st[0] + r1, m2 = st[1] + r2, m3 = st[2] + r3;
-      const bool valid = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
-      const long long orow = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
-      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * 256);
-      const int n0 = n_tile * p.block_n;
-      int nch = (min(p.block_n, p.N - n0) + 31) >> 5;
-      EpiOps cur, nxt;
-      if (p.out_bf16) epi_prefetch(p, cur, orow, n0, valid);
-      mbar_wait(&sh->tmem_full[buf], (it >> 1) & 1, 4);
-      tc_fence_after();
-      for (int ch = 0; ch < nch; ++ch) {
-        const int nb = n0 + ch * 32;
-        uint32_t raw[32];
-        tmem_ld32_issue(taddr0 + (uint32_t)(ch * 32), raw);
-        if (p.out_bf16 && ch + 1 < nch) epi_prefetch(p, nxt, orow, nb + 32, valid);
-        tmem_ld_wait();
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-        if (p.out_bf16)
-          epi_chunk_bf16(p, cur, v, orow, nb, valid);
-        else
-          epi_chunk_f32(p, v, orow, nb, valid);
-        if (p.epi.stats) {
-          epi_stats16(p, v, nb, valid, lane);
-          if (nb + 16 < p.N) epi_stats16(p, v + 16, nb + 16, valid, lane);
-        }
-        cur = nxt;
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
-  }
-}
 
 #include "tapgemm_fwd_tma.cuh"
 
@@ -662,14 +356,15 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     if (q->epi.res) vec = vec && (q->epi.ld_res % 8 == 0) && (((uintptr_t)q->epi.res & 15) == 0);
     if (q->epi.mask) vec = vec && (q->epi.ld_mask % 8 == 0) && (((uintptr_t)q->epi.mask & 15) == 0);
     p.vec_ok = vec ? 1 : 0;
-    // the TMA epilogue handles every launch of the network; the direct-store kernel stays for fp32 outputs,
-    // unaligned tensors, an explicit per-channel scale, or residual + accumulate in one launch
-    static int force_direct = -1;
-    if (force_direct < 0) {
-      const char* e = getenv("ASF_TG_DIRECT");
-      force_direct = (e && e[0] == '1') ? 1 : 0;
+    // one kernel (TMA epilogue): bf16 output, 16-byte aligned rows, BN scale folded into the weights, and at most one
+    // additive operand (residual OR accumulate).  Everything the network launches has this form; anything else is
+    // refused (the CUDA-core kernels of conv_simt.cu take arbitrary layouts).
+    if (!vec || q->epi.scale || (q->epi.res && q->epi.accumulate)) {
+      set_error("asf_tapgemm: mode 0 needs a bf16 output with 16-byte aligned rows (out / res / mask), no per-channel "
+                "scale and not residual + accumulate together");
+      return ASF_E_UNSUPPORTED;
     }
-    const bool use_tma = vec && !q->epi.scale && !(q->epi.res && q->epi.accumulate) && !force_direct;
+    const bool use_tma = true;
     const int n_add = (q->epi.res || q->epi.accumulate) ? 1 : 0, has_mask = q->epi.mask ? 1 : 0;
     // Operand slabs (residual / mask) arrive by TMA ahead of the math through a ring of op_depth slabs per operand and
     // epilogue group.  Measured on the training step (ASF_OP_DEPTH): 2 -> 5.21 ms, 3 -> 5.22 ms, 4 -> 5.75 ms -- every
@@ -683,7 +378,8 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     int op_depth = 2;
     if (op_depth_env >= 2 && op_depth_env <= 4) op_depth = op_depth_env;
     const int group_bytes = (2 + op_depth * (n_add + has_mask)) * EPI_SLAB_BYTES;
-    const int tma_fixed = 2 * group_bytes + 2 * EPI_SHIFT_FLOATS * 4 + (int)sizeof(TgShared);
+    const int stat_bytes = q->epi.stats ? EPI_STAT_FLOATS * 4 : 0;
+    const int tma_fixed = 2 * group_bytes + 2 * EPI_SHIFT_FLOATS * 4 + stat_bytes + (int)sizeof(TgShared);
     const int smem_cap = 227 * 1024;
     int bn = q->block_n;
     if (bn <= 0) {
@@ -695,9 +391,6 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
         // doubles the number of busy SMs, or when the operand slabs leave fewer than 3 ring stages
         while (bn > 64 && bn % 32 == 0 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) * 2 <= sm_budget(q)) bn /= 2;
         while (bn > 64 && bn % 32 == 0 && (smem_cap - tma_fixed) / (TG_A_BYTES + bn * 128) < 3) bn /= 2;
-      } else {
-        // keep at least ~1 wave of tiles on the chip when M is small
-        while (bn > 64 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) < sm_budget(q) && bn % 32 == 0) bn /= 2;
       }
     }
     ASF_CHECK_ARG(bn >= 16 && bn <= 256 && bn % 16 == 0, "asf_tapgemm: block_n %d must be a multiple of 16 in [16,256]", bn);
@@ -710,16 +403,20 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     if (rc) return rc;
     p.rank_b = 3;
     const int stage_bytes = TG_A_BYTES + bn * 128;
-    int stages = TG_SMEM_BUDGET / stage_bytes;
-    if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
-    ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: not enough shared memory for 2 stages");
-    p.stages = stages;
+    int stages = 0;
     p.out = q->out;
     p.ld_out = q->ld_out;
     for (int j = 0; j < 3; ++j) p.o_stride[j] = q->o_stride[j];
     p.epi = q->epi;
     int64_t total = (int64_t)p.m_tiles_total * p.n_tiles;
     int grid = (int)(total < sm_budget(q) ? total : sm_budget(q));
+    if (q->epi.stats) {
+      // statistics: a CTA keeps one N tile for all its M tiles (grid a multiple of n_tiles), sums its columns in shared
+      // memory and leaves one workspace row; see tapgemm_fwd_tma.cuh
+      ASF_CHECK_ARG(q->epi.stats_ws && q->epi.stats_ticket && p.n_tiles <= ASF_STATS_TICKETS && grid >= p.n_tiles,
+                    "asf_tapgemm: statistics need stats_ws / stats_ticket (n_tiles %d)", p.n_tiles);
+      grid = grid / p.n_tiles * p.n_tiles;
+    }
     const double flops = 2.0 * (double)q->m_ext[0] * q->m_ext[1] * q->m_ext[2] * q->N * q->K * q->ntaps;
     if (use_tma) {
       stages = (smem_cap - tma_fixed) / stage_bytes;
@@ -797,21 +494,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       ASF_LAUNCH_CHECK();
       return debug_sync(st);
     }
-    const size_t smem = (size_t)stages * stage_bytes + sizeof(TgShared) + 1024;
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-      ASF_CUDA(cudaFuncSetAttribute(tapgemm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      smem_set = smem;
-    }
-    ProfRec* pr = prof_begin(st, 0, flops);
-    if (pr) {
-      pr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; pr->N = q->N; pr->K = q->K; pr->taps = q->ntaps;
-      pr->block_n = bn; pr->grid = grid;
-    }
-    tapgemm_fwd_kernel<<<grid, TG_THREADS, smem, st>>>(p);
-    prof_end(pr, st);
-    ASF_LAUNCH_CHECK();
-    return debug_sync(st);
+    return ASF_E_UNSUPPORTED;
   }
 
   // mode 1: wgrad (second generation: 64-row stages, up to 256 x 256 per CTA, split-K partials by plain stores)

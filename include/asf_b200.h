@@ -106,9 +106,15 @@ int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, 
  *   if (accumulate) v += out[row*ld_out + n]
  *   if (relu)       v = max(v, 0)
  *   if (mask)       v = mask[row*ld_mask + n] > 0 ? v : 0
- *   if (stats)      stats[n] += v ; stats[n_total + n] += v*v      (fp32 atomics, valid rows only)
+ *   if (stats)      stats[n] = sum_rows v ; stats[stats_stride + n] = sum_rows v*v   (valid rows only; see below)
  *   out[row*ld_out + n] = (out dtype) v
- * res / mask have the out dtype. */
+ * res / mask have the out dtype.
+ *
+ * Statistics are DETERMINISTIC: no floating-point atomics anywhere.  Every CTA stores its partial sums into its own
+ * row of `stats_ws`, the CTA that draws the last ticket adds the rows in ascending order in double precision and
+ * WRITES (not accumulates) the final sums as doubles.  stats_ws: >= ASF_STATS_WS_FLOATS(channels) floats, contents
+ * irrelevant; stats_ticket: ASF_STATS_TICKETS uint32 counters, zero before the first launch (they reset themselves);
+ * launches that share a workspace / ticket must be stream-ordered. */
 typedef struct {
   const float* scale;
   const float* shift;
@@ -116,11 +122,15 @@ typedef struct {
   int64_t ld_res;
   const void* mask;
   int64_t ld_mask;
-  float* stats;
+  double* stats;
   int32_t stats_stride; /* offset of the sum-of-squares half (= channels of the stats buffer) */
   int32_t relu;
   int32_t accumulate;
+  float* stats_ws;
+  uint32_t* stats_ticket;
 } asf_epilogue_t;
+#define ASF_STATS_TICKETS 128
+#define ASF_STATS_WS_FLOATS(C) (640ll * ((C) > 256 ? (C) : 256))
 
 /* Dense direct convolution geometry, channels-last. */
 typedef struct {
@@ -134,13 +144,18 @@ typedef struct {
  *   w   : packed weights [Cout][kt*kf][Cin] in dtype w_dtype
  *   fwd : out[b,to,fo,n] = epi( sum in[b,to*st+it-pt,fo*sf+if-pf,c] * w[n][it*kf+if][c] )
  *   dgrad: din[b,ti,fi,c] = epi( sum dout[b,to,fo,n] * w[n][tap][c] )  (epilogue indexed by (in-row, c))
- *   wgrad: dw[n][c][it][if] (OIHW fp32) = (accumulate ? dw : 0) + rscale[n] * sum dout[row,n] * in[row_tap,c] */
+ *   wgrad: dw[n][c][it][if] (OIHW fp32) = (accumulate ? dw : 0) + rscale[n] * sum dout[row,n] * in[row_tap,c]
+ * fp32 inputs accumulate in double (the fp32 parity mode is an accuracy reference, not a fast path); the forward
+ * epilogue does not produce statistics (epi->stats must be NULL: use asf_channel_stats). */
 int asf_conv_fwd_simt(const void* in, int in_dtype, const void* w, int w_dtype, void* out, int out_dtype,
                       const asf_conv_geom_t* g, const asf_epilogue_t* epi, void* stream);
 int asf_conv_dgrad_simt(const void* dout, int dout_dtype, const void* w, int w_dtype, void* din, int din_dtype,
                         const asf_conv_geom_t* g, const asf_epilogue_t* epi, void* stream);
+/* wgrad: the rows are split over asf_conv_wgrad_simt_ksplit(g) slices whose partial sums are STORED to
+ * ws [ksplit][Cout][taps][Cin] fp32 and added in slice order (no atomics). */
+int asf_conv_wgrad_simt_ksplit(const asf_conv_geom_t* g);
 int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout_dtype, float* dw_oihw,
-                        const asf_conv_geom_t* g, const float* rscale, int accumulate, void* stream);
+                        const asf_conv_geom_t* g, const float* rscale, int accumulate, float* ws, void* stream);
 
 /* tcgen05 / TMEM / TMA implicit-GEMM ("tap-GEMM"), bf16 operands, fp32 accumulation in TMEM.
  *
@@ -204,10 +219,14 @@ long long asf_narrow_conv_launches(void);
 /* the ksplit asf_tapgemm(p, 1, ...) uses when p->ksplit == 0 (>= 1), or a negative error code */
 int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* p);
 
-/* Stem weight gradient (Cin = 1, <= 35 taps): in fp32 [B][Tin][Fin], dout [rows][Cout] -> dw OIHW fp32.
- * Replaces cuDNN wgrad of the stem convs (stem_helper.py:150-157). */
-int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dw_oihw, const asf_conv_geom_t* g,
-                   int accumulate, void* stream);
+/* Stem weight gradient (Cin = 1, <= 35 taps): in fp32 [B][Tin][Fin], dout [rows][Cout] -> row-range partial sums
+ * dwp [ksplit][Cout][taps] fp32 (plain stores, fixed summation order inside a CTA: bit-reproducible), to be summed by
+ * asf_unpack_wgrad(dwp, dw, O = 1, I = Cout*taps, taps = 1, NULL, accumulate, ksplit) or as one entry of
+ * asf_unpack_wgrad_multi.  asf_stem_wgrad_ksplit returns the number of partial rows the launch writes (>= 1; < 0 on
+ * error) -- size dwp with it.  Replaces cuDNN wgrad of the stem convs (stem_helper.py:150-157). */
+int asf_stem_wgrad_ksplit(const asf_conv_geom_t* g, int dout_dtype);
+int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dwp, const asf_conv_geom_t* g,
+                   void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Weight (re)packing between the reference's state_dict layout (OIHW fp32) and kernel layouts.
@@ -271,18 +290,22 @@ int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long 
  * BatchNorm2d (audio_slowfast/models/batchnorm_helper.py:16-31 -> nn.BatchNorm2d; train / eval / frozen,
  * audio_model_builder.py:327-344) as per-channel statistics + fused elementwise passes.
  * ---------------------------------------------------------------------------------------------- */
-/* stats[c] += sum_rows x, stats[C + c] += sum_rows x^2 (fp32 atomics; caller zeroes stats) */
-int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, float* stats, void* stream);
-/* train-mode finalize: mean/var from stats over `count` rows; scale = gamma*invstd, shift = beta - mean*scale;
+/* stats[c] = sum_rows x, stats[C + c] = sum_rows x^2 as doubles, written (not accumulated) by a deterministic
+ * two-stage reduction: per-CTA partial sums in `ws` (>= ASF_STATS_WS_FLOATS(C) floats), ordered final pass by the last
+ * CTA (`ticket`: ASF_STATS_TICKETS zero-initialised uint32, self-resetting).  See asf_epilogue_t. */
+int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, double* stats, float* ws,
+                      uint32_t* ticket, void* stream);
+/* train-mode finalize: mean/var from stats over `count` rows (in double: var = E[x^2] - mean^2 is formed from the
+ * double sums); scale = gamma*invstd, shift = beta - mean*scale;
  * running_mean/var momentum update (unbiased var) and num_batches_tracked += 1 when running_mean != NULL. */
-int asf_bn_finalize(const float* stats, int C, double count, const float* gamma, const float* beta, float eps,
+int asf_bn_finalize(const double* stats, int C, double count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                     float* scale, float* shift, float* save_mean, float* save_invstd, void* stream);
 /* train-mode BatchNorm forward in one pass over the raw conv output: asf_bn_finalize (same side effects, computed
  * per block from `stats`) fused with asf_bn_apply; y == NULL publishes the statistics only.  Replaces the forward of
  * nn.BatchNorm2d in training mode (+ ReLU / residual add: resnet_helper.py:181-225, :335-341). */
 int asf_bn_train_fwd(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
-                     int64_t rows, int C, const float* stats, double count, const float* gamma, const float* beta,
+                     int64_t rows, int C, const double* stats, double count, const float* gamma, const float* beta,
                      float eps, float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                      float* scale, float* shift, float* save_mean, float* save_invstd, int relu, void* stream);
 /* eval/frozen: scale = gamma / sqrt(running_var + eps), shift = beta - running_mean*scale */
@@ -291,14 +314,15 @@ int asf_bn_fold(const float* gamma, const float* beta, const float* running_mean
 /* y = [relu]( x*scale[c] + shift[c] (+ res) ) */
 int asf_bn_apply(const void* x, int64_t ld_x, const void* res, int64_t ld_res, void* y, int64_t ld_y, int dtype,
                  int64_t rows, int C, const float* scale, const float* shift, int relu, void* stream);
-/* backward reductions: red[c] += sum dz, red[C + c] += sum dz * (x - mean[c]) * invstd[c] */
+/* backward reductions: red[c] = sum dz, red[C + c] = sum dz * (x - mean[c]) * invstd[c]  (doubles, written; same
+ * deterministic two-stage reduction, workspace and ticket as asf_channel_stats) */
 int asf_bn_bwd_reduce(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, int dtype, int64_t rows, int C,
-                      const float* mean, const float* invstd, float* red, void* stream);
+                      const float* mean, const float* invstd, double* red, float* ws, uint32_t* ticket, void* stream);
 /* dx = gamma*invstd * (dz - red[c]/count - xhat * red[C+c]/count);  dgamma (+)= red[C+c], dbeta (+)= red[c]
  * (+= when accumulate != 0, the autograd convention for an existing .grad) */
 int asf_bn_bwd_apply(const void* dz, int64_t ld_dz, const void* x, int64_t ld_x, void* dx, int64_t ld_dx, int dtype,
                      int64_t rows, int C, const float* gamma, const float* mean, const float* invstd,
-                     const float* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream);
+                     const double* red, double count, float* dgamma, float* dbeta, int accumulate, void* stream);
 /* elementwise helper: y = (mask > 0) ? (a (+ b)) : 0  -- ReLU backward / gradient accumulation */
 int asf_relu_bwd(const void* a, int64_t ld_a, const void* b, int64_t ld_b, const void* mask, int64_t ld_mask,
                  void* y, int64_t ld_y, int dtype, int64_t rows, int C, void* stream);

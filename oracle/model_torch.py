@@ -254,14 +254,31 @@ class Net:
             sd[name + ".num_batches_tracked"] += 1
         return y
 
+    # ``forced`` (test aid): the ReLU / max-pool DECISIONS of another execution of the same network.  A ReLU named
+    # ``n`` becomes ``x * forced[n]`` ({0,1} mask, NCHW) and the stem max-pool gathers ``forced[n + ".pool"]`` (int64
+    # flat (t, f) indices per output element) instead of taking its own arg-max.  With forced decisions the network is
+    # a fixed piecewise-linear map, so two executions in different precisions differ by accumulated rounding only (a
+    # few 1e-3 in bf16) instead of by the sqrt(eps) amplification of flipped ReLU masks -- which is what lets a
+    # gradient parity test tell a wrong backward from rounding noise.  forced = None is the plain network.
+    forced = None
+
+    def relu(self, name, x):
+        if self.forced is None:
+            return F.relu(x)
+        return x * self.forced[name].to(x.dtype)
+
     def stem(self, p, x, training):
         pre = "s1.pathway%d_stem." % p
-        x = F.relu(self.bn(pre + "bn", self.conv(pre + "conv", x), training))
-        return F.max_pool2d(x, kernel_size=[3, 3], stride=[2, 2], padding=[1, 1])
+        name = pre[:-1]
+        x = self.relu(name, self.bn(pre + "bn", self.conv(pre + "conv", x), training))
+        if self.forced is None:
+            return F.max_pool2d(x, kernel_size=[3, 3], stride=[2, 2], padding=[1, 1])
+        idx = self.forced[name + ".pool"]  # (B, C, Tp, Fp) flat indices into the (T, F) plane
+        return torch.gather(x.flatten(2), 2, idx.flatten(2)).view(idx.shape)
 
     def fuse(self, stage, xs, xf, training):
         pre = "s%d_fuse." % stage
-        f = F.relu(self.bn(pre + "bn", self.conv(pre + "conv_f2s", xf), training))
+        f = self.relu(pre[:-1], self.bn(pre + "bn", self.conv(pre + "conv_f2s", xf), training))
         return torch.cat([xs, f], 1)
 
     def block(self, pre, x, training):
@@ -269,10 +286,10 @@ class Net:
             sc = self.bn(pre + "branch1_bn", self.conv(pre + "branch1", x), training)
         else:
             sc = x
-        h = F.relu(self.bn(pre + "branch2.a_bn", self.conv(pre + "branch2.a", x), training))
-        h = F.relu(self.bn(pre + "branch2.b_bn", self.conv(pre + "branch2.b", h), training))
+        h = self.relu(pre + "branch2.a", self.bn(pre + "branch2.a_bn", self.conv(pre + "branch2.a", x), training))
+        h = self.relu(pre + "branch2.b", self.bn(pre + "branch2.b_bn", self.conv(pre + "branch2.b", h), training))
         h = self.bn(pre + "branch2.c_bn", self.conv(pre + "branch2.c", h), training)
-        return F.relu(sc + h)
+        return self.relu(pre + "branch2.c", sc + h)
 
     def forward(self, inputs, training=False, dropout_mask=None, taps=None):
         """inputs: [slow (B,1,Ts,F), fast (B,1,Tf,F)] or [x].  Returns what the reference head
@@ -316,6 +333,28 @@ class Net:
         return tuple(outs) if len(outs) > 1 else outs[0]
 
 
+def record_decisions(cfg, sd, inputs, training=True):
+    """The oracle's own ReLU masks and stem pooling indices in the ``forced`` format (used to pin the forced path:
+    a network forced with its own decisions reproduces itself)."""
+    forced = {}
+
+    class Rec(Net):
+        def relu(self, name, x):
+            forced[name] = (x > 0)
+            return F.relu(x)
+
+        def stem(self, p, x, training):
+            pre = "s1.pathway%d_stem." % p
+            x = self.relu(pre[:-1], self.bn(pre + "bn", self.conv(pre + "conv", x), training))
+            y, idx = F.max_pool2d(x, kernel_size=[3, 3], stride=[2, 2], padding=[1, 1], return_indices=True)
+            forced[pre[:-1] + ".pool"] = idx
+            return y
+
+    with torch.no_grad():
+        Rec(cfg, OrderedDict((k, v.clone()) for k, v in sd.items())).forward(inputs, training=training)
+    return forced
+
+
 def compute_loss(preds, labels):
     """train_utils.py:76-101 (ONLY_ACTION_RECOGNITION branch): mean of verb and noun CE."""
     if isinstance(preds, (tuple, list)):
@@ -326,8 +365,9 @@ def compute_loss(preds, labels):
     return loss, loss, loss
 
 
-def loss_and_grads(cfg, sd, inputs, labels, dropout_mask=None):
-    """One training-mode forward + backward; returns (loss, preds, {param: grad}, updated sd)."""
+def loss_and_grads(cfg, sd, inputs, labels, dropout_mask=None, forced=None, taps=None):
+    """One training-mode forward + backward; returns (loss, preds, {param: grad}, updated sd).
+    ``forced``: see Net.relu (ReLU masks / pooling indices of another execution)."""
     sd = OrderedDict((k, v.clone()) for k, v in sd.items())
     params = {}
     for k, v in sd.items():
@@ -337,7 +377,8 @@ def loss_and_grads(cfg, sd, inputs, labels, dropout_mask=None):
                 v.requires_grad_(True)
                 params[k] = v
     net = Net(cfg, sd)
-    preds = net.forward(inputs, training=True, dropout_mask=dropout_mask)
+    net.forced = forced
+    preds = net.forward(inputs, training=True, dropout_mask=dropout_mask, taps=taps)
     loss, _, _ = compute_loss(preds, labels)
     grads = torch.autograd.grad(loss, list(params.values()))
     return loss.detach(), preds, dict(zip(params.keys(), grads)), sd

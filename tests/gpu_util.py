@@ -76,8 +76,8 @@ def make_unit(h, B, T, Fq, cin, cout, k, s, p, seed=0, ld_in=None, ld_out=None, 
     u.shift = torch.empty(cout, dtype=torch.float32, device=dev)
     u.mean = torch.empty(cout, dtype=torch.float32, device=dev)
     u.invstd = torch.empty(cout, dtype=torch.float32, device=dev)
-    u.stats = torch.zeros(2 * cout, dtype=torch.float32, device=dev)
-    u.red = torch.zeros(2 * cout, dtype=torch.float32, device=dev)
+    u.stats = torch.zeros(2 * cout, dtype=torch.float64, device=dev)
+    u.red = torch.zeros(2 * cout, dtype=torch.float64, device=dev)
     # what the kernels really see: the rounded input
     x_seen = nchw(xa.view().float())
     return u, x_seen, conv.weight.detach().clone()

@@ -333,8 +333,17 @@ def test_bn_stats_apply_backward(dtype):
     beta = torch.randn(Cn, generator=g).cuda()
     st = L.stream_ptr()
     code = L.dtype_code(dtype)
-    stats = torch.zeros(2 * Cn, device="cuda")
-    L.call("asf_channel_stats", L.ptr(x), code, rows, Cn, Cn, L.ptr(stats), st)
+    # statistics come out as doubles from an ordered two-stage reduction: garbage in, no zeroing needed, bit-reproducible
+    stats = torch.full((2 * Cn,), 123.0, dtype=torch.float64, device="cuda")
+    ws = torch.empty(L.stats_ws_floats(Cn), device="cuda")
+    tk = torch.zeros(L.STATS_TICKETS, dtype=torch.int32, device="cuda")
+    L.call("asf_channel_stats", L.ptr(x), code, rows, Cn, Cn, L.ptr(stats), L.ptr(ws), L.ptr(tk), st)
+    stats_again = torch.empty_like(stats)
+    L.call("asf_channel_stats", L.ptr(x), code, rows, Cn, Cn, L.ptr(stats_again), L.ptr(ws), L.ptr(tk), st)
+    xd = x.double()
+    assert torch.equal(stats, stats_again) and int(tk.abs().sum()) == 0
+    assert torch.allclose(stats[:Cn], xd.sum(0), rtol=1e-6 if dtype == torch.bfloat16 else 1e-12)
+    assert torch.allclose(stats[Cn:], (xd * xd).sum(0), rtol=1e-6 if dtype == torch.bfloat16 else 1e-12)
     scale, shift, mean, invstd = (torch.empty(Cn, device="cuda") for _ in range(4))
     rm, rv, nbt = torch.zeros(Cn, device="cuda"), torch.ones(Cn, device="cuda"), torch.zeros((), dtype=torch.int64, device="cuda")
     L.call("asf_bn_finalize", L.ptr(stats), Cn, C.c_double(rows), L.ptr(gamma), L.ptr(beta), C.c_float(1e-5), C.c_float(0.1),
@@ -349,8 +358,13 @@ def test_bn_stats_apply_backward(dtype):
     # backward (no relu): dx
     ref2 = F.batch_norm(xf, None, None, gamma, beta, True, 0.1, 1e-5)
     ref2.backward(dz.float())
-    red = torch.zeros(2 * Cn, device="cuda")
-    L.call("asf_bn_bwd_reduce", L.ptr(dz), Cn, L.ptr(x), Cn, code, rows, Cn, L.ptr(mean), L.ptr(invstd), L.ptr(red), st)
+    red = torch.full((2 * Cn,), -5.0, dtype=torch.float64, device="cuda")
+    L.call("asf_bn_bwd_reduce", L.ptr(dz), Cn, L.ptr(x), Cn, code, rows, Cn, L.ptr(mean), L.ptr(invstd), L.ptr(red),
+           L.ptr(ws), L.ptr(tk), st)
+    red_again = torch.empty_like(red)
+    L.call("asf_bn_bwd_reduce", L.ptr(dz), Cn, L.ptr(x), Cn, code, rows, Cn, L.ptr(mean), L.ptr(invstd), L.ptr(red_again),
+           L.ptr(ws), L.ptr(tk), st)
+    assert torch.equal(red, red_again)
     dx, dg, db = torch.empty_like(x), torch.empty(Cn, device="cuda"), torch.empty(Cn, device="cuda")
     L.call("asf_bn_bwd_apply", L.ptr(dz), Cn, L.ptr(x), Cn, L.ptr(dx), Cn, code, rows, Cn, L.ptr(gamma), L.ptr(mean),
            L.ptr(invstd), L.ptr(red), C.c_double(rows), L.ptr(dg), L.ptr(db), 0, st)
@@ -413,14 +427,30 @@ def test_stem_wgrad(name, T, cout, k, s, p):
     g.ld_in, g.ld_out = 1, cout
     dw = torch.full((cout, 1, k[0], k[1]), 7.0, device="cuda")
     st = L.stream_ptr()
-    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dw), C.byref(g), 0, st)
+    ks = L.lib().asf_stem_wgrad_ksplit(C.byref(g), L.BF16)
+    assert ks >= 1
+    n = cout * k[0] * k[1]
+    dwp = torch.full((ks, n), float("nan"), device="cuda")  # every partial row is written, none accumulated into
+    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dwp), C.byref(g), st)
+    L.call("asf_unpack_wgrad", L.ptr(dwp), L.ptr(dw), 1, n, 1, None, 0, ks, st)
     torch.cuda.synchronize()
     w = torch.zeros(cout, 1, k[0], k[1], device="cuda", requires_grad=True)
     F.conv2d(x, w, stride=s, padding=p).backward(nchw(dy.float()))
     assert rel_err(dw, w.grad) < 1e-4, rel_err(dw, w.grad)
-    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dw), C.byref(g), 1, st)
+    dwp2 = torch.empty_like(dwp)
+    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(dwp2), C.byref(g), st)
+    L.call("asf_unpack_wgrad", L.ptr(dwp2), L.ptr(dw), 1, n, 1, None, 1, ks, st)
     torch.cuda.synchronize()
+    assert torch.equal(dwp, dwp2), "the stem weight gradient must be bit-reproducible (no atomics)"
     assert rel_err(dw, 2 * w.grad) < 1e-4
+    # fp32 dout (parity mode): the scalar kernel, double accumulators
+    dyf = dy.float()
+    ksf = L.lib().asf_stem_wgrad_ksplit(C.byref(g), L.F32)
+    dwpf = torch.empty((ksf, n), device="cuda")
+    L.call("asf_stem_wgrad", L.ptr(x), L.ptr(dyf), L.F32, L.ptr(dwpf), C.byref(g), st)
+    L.call("asf_unpack_wgrad", L.ptr(dwpf), L.ptr(dw), 1, n, 1, None, 0, ksf, st)
+    torch.cuda.synchronize()
+    assert rel_err(dw, w.grad) < 2e-6, rel_err(dw, w.grad)
 
 
 def test_head_kernels():
@@ -504,7 +534,7 @@ def test_weight_pack_multi():
 
 def test_bad_arguments_raise():
     with pytest.raises(RuntimeError):
-        L.call("asf_channel_stats", None, L.F32, 10, 8, 8, None, L.stream_ptr())
+        L.call("asf_channel_stats", None, L.F32, 10, 8, 8, None, None, None, L.stream_ptr())
     x = torch.zeros(4, 8, device="cuda")
     with pytest.raises(RuntimeError):
-        L.call("asf_channel_stats", L.ptr(x), 7, 4, 8, 8, L.ptr(x), L.stream_ptr())
+        L.call("asf_channel_stats", L.ptr(x), 7, 4, 8, 8, L.ptr(x), L.ptr(x), L.ptr(x), L.stream_ptr())
