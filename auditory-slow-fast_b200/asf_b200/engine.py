@@ -227,6 +227,9 @@ class Engine:
         if self.device.type != "cuda":
             raise RuntimeError("asf_b200 models must live on a CUDA device (call .cuda()); there is no CPU path")
         self.plan = None
+        # plans are cached per (batch, input shapes) and never freed: a captured CUDA graph keeps raw pointers into its
+        # plan's buffers, so running another batch size (e.g. the partial last eval batch) must not release them
+        self._plans = {}
         self.grad_hook = None        # callable(engine, names_done) used by the data-parallel wrapper
         self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
         # (process_group, world_size) set by the data-parallel wrapper: train-mode BatchNorm then normalises with the
@@ -253,9 +256,13 @@ class Engine:
 
     # ------------------------------------------------------------------------------------------ plan
     def invalidate_weights(self):
-        if self.plan is not None:
-            for u in self.plan.units:
+        """Marks every derived weight copy (packed bf16 layouts, folded BN affine) of every cached plan stale.  Needed
+        after the fp32 masters changed behind autograd's version counters -- e.g. a CUDA-graph replay of a captured
+        optimiser step, which never runs the Python that bumps them."""
+        for plan in self._plans.values():
+            for u in plan.stems + plan.units:
                 u.w_key = None
+                u.fold_key = None
 
     def _build_plan(self, B, in_shapes):
         m = self.model
@@ -626,8 +633,13 @@ class Engine:
                    C.c_void_p(dx.ptr), dx.code, C.byref(g), C.byref(e), st)
             return
         B, k, s, p = dy.B, u.k, u.s, u.p
+        # test hook (tests/test_gpu_model.py::test_forced_parity_detects_a_broken_dgrad): shift the first tap of every
+        # 3-tap dgrad by one position, i.e. a deliberately wrong backward pass.  Never set outside that test.
+        broken = k == 3 and os.environ.get("ASF_TEST_BREAK_DGRAD") == "1"
         for rho in range(s):
             taps = [(j, (rho + p - j) // s) for j in range(k) if (rho + p - j) % s == 0]
+            if broken:
+                taps = [(j, off + (1 if i == 0 else 0)) for i, (j, off) in enumerate(taps)]
             if not taps:
                 assert accumulate or getattr(dx, "zeroed", False), "uncovered phase without zero fill: " + u.name
                 continue
@@ -833,9 +845,10 @@ class Engine:
             if t.device != self.device:
                 raise RuntimeError("input on %s but the model is on %s" % (t.device, self.device))
         if self.plan is None or self.plan.B != B or self.plan.in_shapes != shapes:
-            self.plan = self._build_plan(B, shapes)
-            self._flat_grad = None
-            self._grad_views = {}
+            plan = self._plans.get((B, shapes))
+            if plan is None:
+                plan = self._plans[(B, shapes)] = self._build_plan(B, shapes)
+            self.plan = plan
         training = m.training
         needs_grad = torch.is_grad_enabled() and training and any(p.requires_grad for p in m.parameters())
         if needs_grad:

@@ -76,14 +76,54 @@ class TrainStep:
         else:
             self.labels.copy_(labels, non_blocking=True)
 
+    def _snapshot(self):
+        """Everything a training iteration mutates: parameters, buffers (BN running statistics, num_batches_tracked),
+        optimiser state and the CUDA RNG (dropout)."""
+        net = self.model.module if hasattr(self.model, "module") else self.model
+        snap = {"params": [p.detach().clone() for p in net.parameters()],
+                "buffers": [b.detach().clone() for b in net.buffers()],
+                "rng": torch.cuda.get_rng_state(self.device),
+                "opt": {id(p): {k: (v.detach().clone() if torch.is_tensor(v) else v) for k, v in st.items()}
+                        for p, st in self.opt.state.items()},
+                "opt_steps": getattr(self.opt, "_steps", None)}
+        return snap
+
+    def _restore(self, snap):
+        net = self.model.module if hasattr(self.model, "module") else self.model
+        with torch.no_grad():
+            for p, q in zip(net.parameters(), snap["params"]):
+                p.copy_(q)
+            for b, q in zip(net.buffers(), snap["buffers"]):
+                b.copy_(q)
+            for p, st in self.opt.state.items():
+                old = snap["opt"].get(id(p))
+                for k, v in st.items():
+                    if torch.is_tensor(v):
+                        # state created by the warm-up (momentum buffers) goes back to its initial value: zero
+                        v.copy_(old[k]) if old is not None and k in old else v.zero_()
+                    elif old is not None and k in old:
+                        st[k] = old[k]
+        if snap["opt_steps"] is not None:
+            self.opt._steps = snap["opt_steps"]
+        torch.cuda.set_rng_state(snap["rng"], self.device)
+        if hasattr(net, "engine"):
+            net.engine.invalidate_weights()
+
     def _capture(self):
-        # side-stream warm-up (allocations, lazy plans, cudaFuncSetAttribute) as torch's capture rules require
+        """Capture of the whole iteration.  torch's capture rules need a few eager warm-up runs on a side stream first
+        (allocations, lazy plans, cudaFuncSetAttribute); those runs are REAL iterations, so everything they mutate --
+        parameters, momentum buffers, BN running statistics / num_batches_tracked, the dropout RNG -- is restored
+        afterwards: the first replay is the first update, exactly one per batch like the reference's train_epoch
+        (tools/train_net.py:472-493)."""
+        snap = self._snapshot()
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
-            for _ in range(self._warmup):
+            for _ in range(max(1, self._warmup)):
                 self._body()
         torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        self._restore(snap)
         torch.cuda.synchronize(self.device)
         if hasattr(self.opt, "refresh_lr"):
             self.opt.refresh_lr()
@@ -104,4 +144,9 @@ class TrainStep:
             self.opt.refresh_lr()
         self.graph.replay()
         self._calls += 1
+        # the replayed optimiser step wrote the fp32 masters without running the Python that bumps autograd's version
+        # counters: an eager forward between replays (validation) must not reuse packed copies from before the update
+        net = self.model.module if hasattr(self.model, "module") else self.model
+        if hasattr(net, "engine"):
+            net.engine.invalidate_weights()
         return self.loss

@@ -32,6 +32,7 @@ class Harness(Engine):
         self.grad_hook = None
         self.sync_bn = None
         self.plan = None
+        self._plans = {}
         self.two_stream = False
         self.sm_split = (0, 0)
         self._side = None
@@ -90,3 +91,38 @@ def rel_err(a, b):
 
 def max_err(a, b):
     return float((a.float() - b.float()).abs().max())
+
+
+def engine_decisions(model):
+    """The ReLU masks and stem max-pool selections of the engine's LAST forward, in the ``forced`` format of
+    oracle.model_torch.Net (NCHW masks named like the units, flat (t, f) pooling indices).  Read from the plan's
+    activation buffers, which the engine keeps for its backward pass."""
+    eng = model.engine
+    plan = eng.plan
+    forced = {}
+    for u in plan.units:
+        if u.relu:
+            forced[u.name] = (u.y.view().float() > 0).permute(0, 3, 1, 2).contiguous()
+    for u in plan.stems:
+        raw = u.y.view().float()  # (B, To, Fo, C) raw conv output; BN + ReLU + max-pool are one fused kernel
+        a = raw * u.scale.view(1, 1, 1, -1) + u.shift.view(1, 1, 1, -1)
+        forced[u.name] = (a > 0).permute(0, 3, 1, 2).contiguous()
+        B, To, Fo, Cn = raw.shape
+        if u.pool_argmax is not None:
+            codes = u.pool_argmax  # (B, Tp, Fp, C/8) one nibble per channel: (dt+1)*3 + (df+1), 15 = nothing positive
+            Tp, Fp = codes.shape[1], codes.shape[2]
+            sh = torch.arange(8, device=codes.device, dtype=torch.int32) * 4
+            nib = (codes.unsqueeze(-1) >> sh) & 15                       # (B, Tp, Fp, C/8, 8)
+            nib = nib.reshape(B, Tp, Fp, Cn).long()
+            none = nib == 15
+            nib = torch.where(none, torch.full_like(nib, 4), nib)        # window centre: always inside the plane
+            tp = torch.arange(Tp, device=codes.device).view(1, Tp, 1, 1)
+            fp = torch.arange(Fp, device=codes.device).view(1, 1, Fp, 1)
+            t = 2 * tp + nib // 3 - 1
+            f = 2 * fp + nib % 3 - 1
+            idx = (t * Fo + f).permute(0, 3, 1, 2).contiguous()
+        else:
+            act = F.relu(a).permute(0, 3, 1, 2).contiguous()
+            _, idx = F.max_pool2d(act, kernel_size=[3, 3], stride=[2, 2], padding=[1, 1], return_indices=True)
+        forced[u.name + ".pool"] = idx
+    return forced

@@ -38,6 +38,23 @@ CONV_CASES = [
 ]
 IDS = [c[0] for c in CONV_CASES]
 
+# The same conv classes at the BENCHMARKED size (64 clips per GPU): M = 6 400 ... 204 800 rows, several tiles per
+# persistent CTA, split-K weight gradients over many CTAs, the largest layers of both pathways.
+BENCH_CASES = [
+    ("B64_3x1_slow_s4a", 64, 25, 8, 1024, 256, (3, 1), (1, 1), (1, 0)),
+    ("B64_3x1_slow_s5a", 64, 25, 4, 2048, 512, (3, 1), (1, 1), (1, 0)),
+    ("B64_1x1_slow_s5c", 64, 25, 4, 512, 2048, (1, 1), (1, 1), (0, 0)),
+    ("B64_1x3_slow_s4b", 64, 25, 8, 256, 256, (1, 3), (1, 1), (0, 1)),
+    ("B64_1x3s2_slow_s5b", 64, 25, 8, 512, 512, (1, 3), (1, 2), (0, 1)),
+    ("B64_1x1s2_short_s5", 64, 25, 8, 1280, 2048, (1, 1), (1, 2), (0, 0)),
+    ("B64_1x1_slow_s2a", 64, 25, 32, 80, 64, (1, 1), (1, 1), (0, 0)),
+    ("B64_7x1s4_lat_s4", 64, 100, 8, 128, 256, (7, 1), (4, 1), (3, 0)),
+    ("B64_3x1_fast_s2a", 64, 100, 32, 32, 8, (3, 1), (1, 1), (1, 0)),
+    ("B64_1x3_fast_s3b", 64, 100, 16, 16, 16, (1, 3), (1, 1), (0, 1)),
+    ("B64_1x1_fast_s5c", 64, 100, 4, 64, 256, (1, 1), (1, 1), (0, 0)),
+]
+BENCH_IDS = [c[0] for c in BENCH_CASES]
+
 
 def _ref_conv(x, w, s, p):
     return F.conv2d(x, w, None, stride=s, padding=p)
@@ -53,7 +70,7 @@ def h_f32():
     return Harness(torch.float32)
 
 
-@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+@pytest.mark.parametrize("case", CONV_CASES + BENCH_CASES, ids=IDS + BENCH_IDS)
 def test_tapgemm_forward_fused_affine(h_tc, case):
     """frozen/eval BN: conv with BN scale folded into the weights, shift + residual + ReLU in the epilogue."""
     _, B, T, Fq, cin, cout, k, s, p = case
@@ -75,15 +92,34 @@ def test_tapgemm_forward_fused_affine(h_tc, case):
     assert rel_err(out, ref) < 6e-3, rel_err(out, ref)
 
 
-@pytest.mark.parametrize("case", [CONV_CASES[i] for i in (0, 4, 6, 9, 11, 13, 15, 16)], ids=[IDS[i] for i in (0, 4, 6, 9, 11, 13, 15, 16)])
+_STAT_CASES = [CONV_CASES[i] for i in (0, 4, 6, 9, 11, 13, 15, 16)] + [BENCH_CASES[i] for i in (0, 2, 5, 8, 10)]
+
+
+@pytest.mark.parametrize("case", _STAT_CASES, ids=[c[0] for c in _STAT_CASES])
 def test_tapgemm_forward_batch_stats(h_tc, case):
-    """training BN: raw conv output + per-channel sum / sum-of-squares from the epilogue, then normalise."""
+    """training BN: raw conv output + per-channel sum / sum-of-squares from the epilogue (ordered two-stage reduction in
+    double, bit-reproducible), then normalise."""
     _, B, T, Fq, cin, cout, k, s, p = case
     u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=2)
     u.bn.train()
     rm0, rv0 = u.bn.running_mean.clone(), u.bn.running_var.clone()
     h_tc._unit_forward(u, training=True)
     torch.cuda.synchronize()
+    stats1, y1 = u.stats.clone(), u.y.buf.clone()
+    rm1, rv1 = u.bn.running_mean.clone(), u.bn.running_var.clone()
+    u.stats.fill_(-1.0)
+    h_tc._unit_forward(u, training=True)  # a second launch on the same workspace / tickets: same bits
+    torch.cuda.synchronize()
+    assert torch.equal(u.stats, stats1) and torch.equal(u.y.buf, y1)
+    assert int(u.stats_ticket.abs().sum()) == 0, "the tickets reset themselves"
+    with torch.no_grad():  # undo the second running-statistics update
+        u.bn.running_mean.copy_(rm1)
+        u.bn.running_var.copy_(rv1)
+        u.bn.num_batches_tracked.fill_(1)
+    stored = u.raw.view().double()  # the bf16 values BN reads: the sums are over exactly these
+    # (fp32 partial sums inside a CTA, double across CTAs: ~1e-6 of the sum of magnitudes)
+    assert torch.allclose(stats1[:cout], stored.sum((0, 1, 2)), rtol=0, atol=1e-5 * float(stored.abs().sum((0, 1, 2)).max()))
+    assert torch.allclose(stats1[cout:], (stored * stored).sum((0, 1, 2)), rtol=1e-5, atol=0)
     conv = _ref_conv(x, w.to(torch.bfloat16).float(), s, p)
     mean = conv.mean((0, 2, 3))
     var = conv.var((0, 2, 3), unbiased=False)
@@ -98,7 +134,7 @@ def test_tapgemm_forward_batch_stats(h_tc, case):
     assert int(u.bn.num_batches_tracked) == 1
 
 
-@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+@pytest.mark.parametrize("case", CONV_CASES + BENCH_CASES, ids=IDS + BENCH_IDS)
 def test_tapgemm_dgrad(h_tc, case):
     _, B, T, Fq, cin, cout, k, s, p = case
     u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=3)
@@ -124,7 +160,7 @@ def test_tapgemm_dgrad(h_tc, case):
     assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
 
 
-@pytest.mark.parametrize("case", CONV_CASES, ids=IDS)
+@pytest.mark.parametrize("case", CONV_CASES + BENCH_CASES, ids=IDS + BENCH_IDS)
 def test_tapgemm_wgrad(h_tc, case):
     _, B, T, Fq, cin, cout, k, s, p = case
     u, x, w = make_unit(h_tc, B, T, Fq, cin, cout, k, s, p, seed=4)
