@@ -77,6 +77,13 @@ class PackDesc(C.Structure):
 
 PACK_CHUNK = 2048
 
+SPECAUG_MAX_MASKS = 2
+
+
+class SpecAugParams(C.Structure):
+    _fields_ = [("coef", C.c_float * 3), ("fmask", (C.c_int32 * 2) * SPECAUG_MAX_MASKS),
+                ("tmask", (C.c_int32 * 2) * SPECAUG_MAX_MASKS), ("pad_", C.c_int32)]
+
 
 class SgdDesc(C.Structure):
     _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("n", C.c_int64), ("wd", C.c_float),
@@ -117,6 +124,8 @@ SIGNATURES = {
     "asf_logmel_tc_btab_floats": [_I],
     "asf_logmel_tc_tables": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "asf_logmel_fwd_tc": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _P, _I, _P],
+    "asf_specaug_params": [_P, _I, _I, _I, C.c_ulonglong, _P, _I, _I, _I, _I, _I, _P, _P],
+    "asf_specaug_apply": [_P, _P, _P, _I, _I, _I, _P],
     "asf_conv_fwd_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
     "asf_conv_dgrad_simt": [_P, _I, _P, _I, _P, _I, C.POINTER(ConvGeom), C.POINTER(Epilogue), _P],
     "asf_conv_wgrad_simt": [_P, _I, _P, _I, _P, C.POINTER(ConvGeom), _P, _I, _P, _P],

@@ -92,6 +92,30 @@ int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, 
                       int n_mels, float eps, const float* btab, const float* melw, const int32_t* melj, float* fast,
                       int T_out, void* stream);
 
+/* SpecAugment, batched on the device.  Replaces datasets/spec_augment.py:144-191 (time_warp through
+ * datasets/sparse_image_warp.py:5-354, 2 frequency masks of width < Fmax, 2 time masks of width < Tmax, each filled with
+ * the current mean of the clip) as called per training sample at datasets/epickitchens.py:160-168.
+ *   asf_specaug_params  draws, per clip, the reference's random quantities with a counter-based generator (Philox4x32-10
+ *                       keyed by `seed`, counter = (clip, draw, *counter); *counter, a DEVICE uint64 that may be NULL, is
+ *                       advanced by one per launch so that a replayed CUDA graph keeps drawing fresh numbers) and
+ *                       reduces them to the affine time flow  flow(f, t) = coef[0] f + coef[1] t + coef[2]  that the
+ *                       reference's one-control-point spline amounts to, plus the half-open mask intervals.
+ *                       spec is read at (t = i, f = F/2): the reference uses that VALUE as a control coordinate.
+ *   asf_specaug_apply   out[b][t][f] = augmented in[b][t][f]  (fp32 [B][T][F], in != out): time resampling with linear
+ *                       interpolation clamped at the borders, then the fills.  Bit-reproducible for given params. */
+#define ASF_SPECAUG_MAX_MASKS 2
+typedef struct {
+  float coef[3];
+  int32_t fmask[ASF_SPECAUG_MAX_MASKS][2]; /* [start, end) along frequency; end <= start: nothing */
+  int32_t tmask[ASF_SPECAUG_MAX_MASKS][2]; /* [start, end) along time */
+  int32_t pad_;
+} asf_specaug_params_t;
+int asf_specaug_params(const float* spec, int B, int T, int F, unsigned long long seed, unsigned long long* counter,
+                       int W, int Fmax, int Tmax, int num_freq_masks, int num_time_masks, asf_specaug_params_t* params,
+                       void* stream);
+int asf_specaug_apply(const float* in, float* out, const asf_specaug_params_t* params, int B, int T, int F,
+                      void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Convolution family.  Replaces every nn.Conv2d (+ the BatchNorm2d / ReLU / residual add / torch.cat
  * that follow it) of

@@ -196,6 +196,15 @@ def load_reference():
     return ns
 
 
+def load_spec_augment():
+    """The reference's own datasets/spec_augment.py module (spec_augment, time_warp, freq_mask, time_mask; it imports
+    datasets/sparse_image_warp.py), unmodified."""
+    load_reference()
+    import audio_slowfast.datasets.spec_augment as sa  # type: ignore
+
+    return sa
+
+
 def reference_cfg(arch="slowfast", num_classes=(97, 300), bn_freeze=None):
     """cfg of the shipped EPIC recipe (models/asf/config/asf-original-augment.yaml) on CPU,
     optionally switched to a single pathway (BASELINE config 1 = SLOW_R50)."""

@@ -134,6 +134,43 @@ def logmel_case():
     np.savez_compressed(os.path.join(HERE, "logmel.npz"), **out)
 
 
+def specaug_case():
+    """specaug.npz -- the REAL reference spec_augment (datasets/spec_augment.py:144-191) on small seeded clips, with the
+    random draws it made (replayed from the same Python / torch seeds in the order the reference consumes them, the
+    3 x 3 normal block included), so that the oracle and the GPU kernel can be checked against reference OUTPUTS."""
+    import random
+
+    from oracle import spec_augment_np as SA
+
+    sa = ref_shim.load_spec_augment()
+    out = {}
+    F, T = 32, 64
+    rng = np.random.default_rng(5)
+    n = 0
+    for trial in range(40):
+        spec = (rng.standard_normal((T, F)) * 1.5 - 3.0).astype(np.float32)      # [T, F], log-mel-like values
+        x = torch.from_numpy(spec).unsqueeze(0).permute(0, 2, 1)                  # (C, F, T) as in epickitchens.py:163
+        random.seed(1000 + trial)
+        torch.manual_seed(2000 + trial)
+        ref = sa.spec_augment(x, F=9, T=12).permute(0, 2, 1)[0].numpy()
+        random.seed(1000 + trial)
+        torch.manual_seed(2000 + trial)
+        p = SA.draw_params(random, lambda: torch.randn((1, 3, 3)).numpy(), spec[:, F // 2], F, T, Fmax=9, Tmax=12)
+        if np.abs(p["coef"]).max() > 2.0:   # a near-singular draw: the reference's fp32 solve is noise there
+            continue
+        out["in%d" % n], out["ref%d" % n] = spec, ref
+        out["coef%d" % n] = np.asarray(p["coef"], dtype=np.float64)
+        out["fmask%d" % n] = np.asarray(p["fmask"], dtype=np.int32).reshape(-1, 2)
+        out["tmask%d" % n] = np.asarray(p["tmask"], dtype=np.int32).reshape(-1, 2)
+        out["draw%d" % n] = np.array([p["i"], p["d"]], dtype=np.int32)
+        n += 1
+        if n == 12:
+            break
+    out["count"] = np.array(n)
+    np.savez_compressed(os.path.join(HERE, "specaug.npz"), **out)
+    print("specaug.npz: %d cases" % n)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
     logmel_case()
@@ -141,3 +178,4 @@ if __name__ == "__main__":
     model_case("slowfast_epic", "slowfast", (97, 300), 2)
     model_case("slowfast_vgg", "slowfast", (309,), 2)
     model_case("slow_r50", "slow", (97, 300), 1)
+    specaug_case()
