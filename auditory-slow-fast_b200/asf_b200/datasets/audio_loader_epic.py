@@ -93,12 +93,16 @@ def logmel_cuda(waveforms, sr=24000, n_fft=2048, win=240, hop=120, n_mels=128, e
     return out
 
 
-def logmel_batch(cfg, waveforms, epic_quirk=True):
+def logmel_batch(cfg, waveforms, epic_quirk=True, augment=None):
     """Batched waveform -> model inputs: CUDA float32 [B, N] -> ``[slow (B,1,T//alpha,F), fast (B,1,T,F)]``
-    (or ``[x]`` for single-pathway archs), i.e. _extract_sound_feature + pack_pathway_output for a batch."""
+    (or ``[x]`` for single-pathway archs), i.e. _extract_sound_feature + pack_pathway_output for a batch.
+    ``augment``: a ``datasets.spec_augment.SpecAugmenter`` applied to the spectrograms BEFORE the pathway packing,
+    which is where the reference's training dataset applies SpecAugment (datasets/epickitchens.py:160-170)."""
     win, hop = _stft_sizes(cfg, cfg.AUDIO_DATA.WINDOW_LENGTH, cfg.AUDIO_DATA.HOP_LENGTH, epic_quirk)
     spec = logmel_cuda(waveforms, cfg.AUDIO_DATA.SAMPLING_RATE, cfg.AUDIO_DATA.N_FFT, win, hop,
                        cfg.AUDIO_DATA.NUM_FREQUENCIES, 1e-6, cfg.AUDIO_DATA.NUM_FRAMES)
+    if augment is not None:
+        spec = augment(spec)
     if cfg.MODEL.ARCH in cfg.MODEL.SINGLE_PATHWAY_ARCH:
         return [spec]
     if cfg.MODEL.ARCH in cfg.MODEL.MULTI_PATHWAY_ARCH:

@@ -32,7 +32,10 @@ def compute_loss(preds, labels):
 
 
 class TrainStep:
-    def __init__(self, cfg, model, optimizer, batch_size, n_samples, graph=True, warmup=3):
+    def __init__(self, cfg, model, optimizer, batch_size, n_samples, graph=True, warmup=3, augment=None):
+        """``augment``: optional ``datasets.spec_augment.SpecAugmenter`` (the reference's training-time SpecAugment,
+        datasets/epickitchens.py:160-168) applied on the device between extraction and the stems; its random numbers
+        come from a device-side counter, so every replay of the captured step augments differently."""
         self.cfg, self.model, self.opt = cfg, model, optimizer
         net = model.module if hasattr(model, "module") else model
         dev = next(net.parameters()).device
@@ -45,6 +48,7 @@ class TrainStep:
         else:
             self.labels = torch.zeros(batch_size, dtype=torch.int64, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.augment = augment
         self.graph = None
         self._want_graph = graph
         self._warmup = warmup
@@ -54,7 +58,7 @@ class TrainStep:
         net = self.model.module if hasattr(self.model, "module") else self.model
         fork = torch.cuda.Event()
         fork.record(torch.cuda.current_stream(self.device))
-        x = logmel_batch(self.cfg, self.wave)
+        x = logmel_batch(self.cfg, self.wave, augment=self.augment)
         if hasattr(net, "engine"):
             # the optimiser step of the previous iteration left every packed weight copy stale: refresh them on a side
             # stream forked BEFORE the log-mel kernel but launched after it, so the HBM-bound re-layout runs beside the

@@ -383,6 +383,36 @@ int asf_scale_mask(const float* x, const float* mask, float* y, int64_t n, float
 int asf_gather_rows(const float* src, float* dst, const int32_t* idx, int B, int T_src, int n_idx, int F,
                     void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Waveform staging: clip slicing on the device.  Replaces the host-side whole-video read + slice of
+ * audio_slowfast/datasets/audio_loader_epic.py:45, :138 and the per-view crops of get_start_end_idx
+ * (datasets/utils.py:12-40; 10 test views: datasets/epickitchens.py:46-47).
+ *   out[b][j] = samples[starts[b] + j] for j < n while starts[b] + j < limits[b] (absolute end of that clip's video
+ *   inside `samples`), else 0;  valid[b] (optional) = number of real samples of clip b.
+ * ---------------------------------------------------------------------------------------------- */
+int asf_gather_clips(const float* samples, const int64_t* starts, const int64_t* limits, int B, int n, float* out,
+                     int64_t out_ld, int32_t* valid, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Metrics and the multi-view test ensemble on the device (no per-iteration host sync).  Replaces
+ * audio_slowfast/utils/metrics.py:11-41, :80-108 (topks_correct, multitask_topks_correct), their nine .item() syncs
+ * in tools/train_net.py:497-539, and EPICTestMeter.update_stats / finalize_metrics (utils/meters.py:1641-1755) fed by
+ * tools/test_net.py:194-239.
+ *   asf_topk_counts       counts[0..1] += samples whose label_a ranks inside the top k1 / k2 of preds_a; with a second
+ *                         task (preds_b != NULL) counts[2..3] the same for b and counts[4..5] for both at once (the
+ *                         "action" accuracy).  Rank ties go to the lower class index.  uint64 integer counters.
+ *   asf_ensemble_scatter  clip id = video * num_views + view: stores the clip's scores in clips[video][view][:], its
+ *                         label in vid_labels[video], seen[video][view] = 1.
+ *   asf_ensemble_reduce   ens[video][:] = sum (mode 0) / max(0, .) (mode 1) over the views, in view order.
+ * ---------------------------------------------------------------------------------------------- */
+int asf_topk_counts(const float* preds_a, int Ca, int64_t lda, const int64_t* labels_a, const float* preds_b, int Cb,
+                    int64_t ldb, const int64_t* labels_b, int B, int k1, int k2, unsigned long long* counts,
+                    void* stream);
+int asf_ensemble_scatter(const float* preds, int C, int64_t ld, const int64_t* labels, const int64_t* clip_ids, int B,
+                         int num_views, int num_videos, float* clips, int64_t* vid_labels, int32_t* seen,
+                         void* stream);
+int asf_ensemble_reduce(const float* clips, int C, int num_views, int num_videos, int mode, float* ens, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
