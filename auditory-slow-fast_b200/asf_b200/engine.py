@@ -255,14 +255,22 @@ class Engine:
         self._pending_unpack = []
 
     # ------------------------------------------------------------------------------------------ plan
-    def invalidate_weights(self):
-        """Marks every derived weight copy (packed bf16 layouts, folded BN affine) of every cached plan stale.  Needed
-        after the fp32 masters changed behind autograd's version counters -- e.g. a CUDA-graph replay of a captured
-        optimiser step, which never runs the Python that bumps them."""
+    def invalidate_weights(self, folds=True):
+        """Marks every derived weight copy (packed bf16 layouts and, with ``folds``, the folded BN affine) of every
+        cached plan stale.  Needed after the fp32 masters / BN buffers changed behind autograd's version counters --
+        e.g. a CUDA-graph replay of a captured optimiser step, which never runs the Python that bumps them."""
         for plan in self._plans.values():
             for u in plan.stems + plan.units:
                 u.w_key = None
-                u.fold_key = None
+                if folds:
+                    u.fold_key = None
+
+    def prepare_weights(self, training):
+        """Refreshes the stale derived copies of the current plan now, on the current stream (TrainStep calls this
+        before capturing: the folded affine of FROZEN BatchNorm layers is constant during training and must not be
+        re-derived by 100 tiny launches inside every replay; the weight re-pack must)."""
+        if self.plan is not None:
+            self._prepare_all(training)
 
     def _build_plan(self, B, in_shapes):
         m = self.model
@@ -809,11 +817,10 @@ class Engine:
     def _wgrad_ws(self, nfloats):
         """Split-K workspace of the tcgen05 wgrad ([ksplit][Cout][taps][Cin] fp32 partial tiles, written then summed
         by asf_unpack_wgrad on the same stream): one grow-only buffer per stream, shared by the layers issued on it."""
-        cur = torch.cuda.current_stream(self.device)  # one workspace per issuing stream
-        key = 0
-        for i, s_ in enumerate([self._side, self._slow] + [self._wg[k] for k in sorted(self._wg)]):
-            if s_ is not None and cur == s_:
-                key = i + 1
+        # one workspace per issuing stream, keyed by the stream's handle (an index into the list of streams would shift
+        # while the weight-gradient streams are being created during the first backward pass and hand a buffer that
+        # another stream's kernels are still using to a new owner)
+        key = torch.cuda.current_stream(self.device).cuda_stream
         ws = self._ws.get(key)
         if ws is None or ws.numel() < nfloats:
             ws = self._ws[key] = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=self.device)

@@ -128,6 +128,12 @@ class TrainStep:
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
         self._restore(snap)
+        net = self.model.module if hasattr(self.model, "module") else self.model
+        if hasattr(net, "engine"):
+            # constants (folded affine of the frozen BatchNorm layers) are derived once, here; only the re-pack of the
+            # weights that the optimiser changes every step goes into the graph
+            net.engine.prepare_weights(net.training)
+            net.engine.invalidate_weights(folds=False)
         torch.cuda.synchronize(self.device)
         if hasattr(self.opt, "refresh_lr"):
             self.opt.refresh_lr()

@@ -32,7 +32,7 @@ def test_apply_full_size_edge_cases():
     """400 x 128 clips: no warp, large flows that clamp at both borders, negative flows, empty / full-height / adjacent
     masks, and bit-reproducibility."""
     wav = OL.synthetic_waveforms(6, 47975, 11)
-    spec = np.stack([OL.extract_sound_feature(w, 400)[0] for w in wav])
+    spec = np.ascontiguousarray(np.stack([OL.extract_sound_feature(w, 400)[0] for w in wav]))
     recs = [
         {"coef": (0.0, 0.0, 0.0), "fmask": [], "tmask": []},
         {"coef": (0.03, -0.008, 2.5), "fmask": [(98, 100), (50, 61)], "tmask": [(259, 271), (272, 272)]},
@@ -90,7 +90,7 @@ def test_parameter_generator_distributions():
 
 def test_augmenter_end_to_end_and_reference_signature():
     wav = OL.synthetic_waveforms(4, 47975, 21)
-    spec = torch.from_numpy(np.stack([OL.extract_sound_feature(w, 400) for w in wav])).cuda()  # (4, 1, 400, 128)
+    spec = torch.from_numpy(np.ascontiguousarray(np.stack([OL.extract_sound_feature(w, 400) for w in wav]))).cuda()  # (4, 1, 400, 128)
     aug = GA.SpecAugmenter(seed=7)
     out = aug(spec)
     assert out.shape == spec.shape and torch.isfinite(out).all()
