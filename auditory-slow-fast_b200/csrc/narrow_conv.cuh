@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
       if (i < G) wfrag[i] = q[u];
     }
   }
-  float* sstat = (float*)(wfrag + G);  // STATS: [4 warps][2][N] warp partial sums, then 128 doubles + a flag
+  float* sstat = (float*)(wfrag + G);  // STATS: [4 warps][2][N] warp partial sums, then 4 x 128 doubles + a flag
   __syncthreads();
   pdl_wait();
 
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(NC_THREADS) narrow_conv_kernel(const __grid_co
     for (int i = threadIdx.x; i < 2 * N; i += NC_THREADS)
       my[i] = ((sstat[i] + sstat[2 * N + i]) + sstat[4 * N + i]) + sstat[6 * N + i];
     double* scratch = (double*)(sstat + 8 * N);
-    unsigned* flag = (unsigned*)(scratch + NC_THREADS);
+    unsigned* flag = (unsigned*)(scratch + 4 * NC_THREADS);
     if (stats_last_cta(p.epi.stats_ticket, gridDim.x, flag)) {
       double* out = p.epi.stats;
       const int stride = p.epi.stats_stride;
@@ -315,7 +315,7 @@ static int narrow_conv_launch(const asf_tapgemm_t* q, cudaStream_t st) {
   p.tiles = (int)cdiv(p.m_total, 16);
   p.epi = q->epi;
   const int no = q->N / 8, wpc = NC_THREADS / 32;
-  const int smem = p.steps * no * 32 * 16 + (q->epi.stats ? 8 * q->N * 4 + NC_THREADS * 8 + 16 : 0);
+  const int smem = p.steps * no * 32 * 16 + (q->epi.stats ? 8 * q->N * 4 + 4 * NC_THREADS * 8 + 16 : 0);
   long long grid = cdiv(p.tiles, wpc);
   // resident CTAs per SM by register count (64 / 72 / 94 / 128 registers); a warp then walks its tiles.
   // With statistics every CTA leaves one workspace row for the ordered final pass: at most 4 CTAs per SM.

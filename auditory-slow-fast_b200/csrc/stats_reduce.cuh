@@ -32,44 +32,68 @@ __device__ __forceinline__ bool stats_last_cta(unsigned* ticket, unsigned total,
 }
 
 // Ordered sum over P workspace rows for `slots` independent columns: slot s of row p is ws[p * row_stride + s].
-// L lanes share a slot (lane l adds rows l, l + L, ... in ascending order; the lanes are then folded in ascending
-// order through `scratch`, >= blockDim.x doubles of shared memory).  emit(s, sum) is called once per slot.
-// Must be called by all threads of the CTA (it synchronises).
+// A thread owns FOUR adjacent slots (one 16-byte load per row; slots, row_stride multiples of 4, ws 16-byte aligned --
+// every caller's layout) and L lanes share a slot group: lane l adds rows l, l + L, ... in ascending order with eight
+// independent loads in flight, the lanes are then folded in ascending order through `scratch` (>= 4 * blockDim.x
+// doubles of shared memory).  emit(s, sum) is called once per slot.  Must be called by all threads of the CTA.
 template <typename Emit>
 __device__ __forceinline__ void stats_ordered_reduce(const float* ws, int P, long long row_stride, int slots,
                                                      double* scratch, Emit emit) {
   const int nthreads = (int)blockDim.x, tid = (int)threadIdx.x;
+  const int groups = slots >> 2;  // 4-slot groups
   int L = 1;
-  while (L < 16 && slots * (L * 2) <= nthreads && L * 2 <= P) L *= 2;
-  const int per = nthreads / L;  // slots handled per pass
-  const int sl = tid % per, l = tid / per;
-  for (int s0 = 0; s0 < slots; s0 += per) {
-    const int s = s0 + sl;
-    const bool act = s < slots && l < L;
-    double acc = 0.0;
+  while (L < 32 && groups * (L * 2) <= nthreads && L * 2 <= P) L *= 2;
+  const int per = nthreads / L;  // slot groups handled per pass
+  const int gl = tid % per, l = tid / per;
+  for (int g0 = 0; g0 < groups; g0 += per) {
+    const int g = g0 + gl;
+    const bool act = g < groups && l < L;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     if (act) {
-      const float* src = ws + s;
+      const float* src = ws + 4 * g;
       int p = l;
-      for (; p + 3 * L < P; p += 4 * L) {  // four independent loads in flight, added in row order
-        const float a = __ldcg(src + (long long)p * row_stride);
-        const float b = __ldcg(src + (long long)(p + L) * row_stride);
-        const float c = __ldcg(src + (long long)(p + 2 * L) * row_stride);
-        const float d = __ldcg(src + (long long)(p + 3 * L) * row_stride);
-        acc += (double)a;
-        acc += (double)b;
-        acc += (double)c;
-        acc += (double)d;
+      for (; p + 7 * L < P; p += 8 * L) {
+        float4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __ldcg((const float4*)(src + (long long)(p + j * L) * row_stride));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {  // added in row order
+          a0 += (double)v[j].x;
+          a1 += (double)v[j].y;
+          a2 += (double)v[j].z;
+          a3 += (double)v[j].w;
+        }
       }
-      for (; p < P; p += L) acc += (double)__ldcg(src + (long long)p * row_stride);
+      for (; p < P; p += L) {
+        const float4 v = __ldcg((const float4*)(src + (long long)p * row_stride));
+        a0 += (double)v.x;
+        a1 += (double)v.y;
+        a2 += (double)v.z;
+        a3 += (double)v.w;
+      }
     }
     if (L > 1) {
-      scratch[tid] = acc;
+      scratch[4 * tid] = a0;
+      scratch[4 * tid + 1] = a1;
+      scratch[4 * tid + 2] = a2;
+      scratch[4 * tid + 3] = a3;
       __syncthreads();
       if (act && l == 0)
-        for (int j = 1; j < L; ++j) acc += scratch[j * per + sl];
+        for (int j = 1; j < L; ++j) {
+          const double* q = scratch + 4 * (j * per + gl);
+          a0 += q[0];
+          a1 += q[1];
+          a2 += q[2];
+          a3 += q[3];
+        }
       __syncthreads();
     }
-    if (act && l == 0) emit(s, acc);
+    if (act && l == 0) {
+      emit(4 * g, a0);
+      emit(4 * g + 1, a1);
+      emit(4 * g + 2, a2);
+      emit(4 * g + 3, a3);
+    }
   }
 }
 

@@ -104,8 +104,11 @@ def engine_decisions(model):
         if u.relu:
             forced[u.name] = (u.y.view().float() > 0).permute(0, 3, 1, 2).contiguous()
     for u in plan.stems:
-        raw = u.y.view().float()  # (B, To, Fo, C) raw conv output; BN + ReLU + max-pool are one fused kernel
-        a = raw * u.scale.view(1, 1, 1, -1) + u.shift.view(1, 1, 1, -1)
+        raw = u.y.view().double()  # (B, To, Fo, C) raw conv output; BN + ReLU + max-pool are one fused kernel
+        # the kernels evaluate fma(raw, scale, shift) in fp32 = the exact value rounded once: form it in double and
+        # round, so that the decisions read here are the kernel's own even for pre-activations within an ulp of zero
+        # (ONE flipped stem element moves the fast stem's bias gradient, a heavily cancelling sum, by 8e-3)
+        a = (raw * u.scale.double().view(1, 1, 1, -1) + u.shift.double().view(1, 1, 1, -1)).float()
         forced[u.name] = (a > 0).permute(0, 3, 1, 2).contiguous()
         B, To, Fo, Cn = raw.shape
         if u.pool_argmax is not None:
