@@ -2,8 +2,9 @@
 //
 // Same mainloop contract as tapgemm_fwd_kernel (TMA -> smem ring -> tcgen05.mma -> TMEM, persistent CTAs), with
 //   * a tight single-thread MMA issue loop (no integer division, four unrolled K=16 steps per 64-channel chunk),
-//   * an all-asynchronous epilogue: residual / accumulate / mask operands arrive by TMA into swizzled smem slabs
-//     (prefetched one slab ahead), results leave through smem + TMA store; no thread ever waits on a global load.
+//   * an all-asynchronous epilogue: residual / accumulate / mask operands arrive by per-thread cp.async into swizzled
+//     smem slabs (prefetched one slab ahead, each thread its own row), results leave through smem + TMA store, one
+//     named barrier per slab; no thread ever waits on a global load.
 //     OOB rows / channels of a ragged tile are clipped by the TMA store, so the math runs unpredicated,
 //   * training-BN statistics summed column-wise from the bf16 slab that is being stored (what BN will read).
 //
@@ -17,7 +18,8 @@ constexpr int EPI_SHIFT_FLOATS = 256;
 // training-BN statistics (STATS launches only): per epilogue group [2][256] column accumulators + [4 warps][64] slab
 // partials.  Deterministic: no atomics, fixed summation order (see epi_slab_stats_part / epi_stats_accumulate).
 constexpr int EPI_STAT_ACC_FLOATS = 2 * 256;
-constexpr int EPI_STAT_SCR_FLOATS = 4 * 64;
+constexpr int EPI_STAT_SCR_HALF = 4 * 64;                   // [4 warps][64] partials of one slab
+constexpr int EPI_STAT_SCR_FLOATS = 2 * EPI_STAT_SCR_HALF;  // double buffered: one barrier per slab
 constexpr int EPI_STAT_FLOATS = 2 * (EPI_STAT_ACC_FLOATS + EPI_STAT_SCR_FLOATS);
 constexpr int TGT_THREADS = 352;  // warp 0: TMA (activations), 1: MMA, 2..9: epilogue, 10: TMA (weights)
 
@@ -135,8 +137,6 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     tma_prefetch_desc(&p.tm_a);
     tma_prefetch_desc(&p.tm_b);
     tma_prefetch_desc(&p.tm_out);
-    if (n_ops > 0) tma_prefetch_desc(&p.tm_op[0]);
-    if (n_ops > 1) tma_prefetch_desc(&p.tm_op[1]);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&sh->full[s], 1);
       mbar_init(&sh->empty[s], 1);
@@ -144,7 +144,6 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     for (int i = 0; i < 2; ++i) {
       mbar_init(&sh->tmem_full[i], 1);
       mbar_init(&sh->tmem_empty[i], 4);
-      for (int j = 0; j < 4; ++j) mbar_init(&sh->op_full[i][j], 1);
     }
     fence_barrier_init();
   }
@@ -275,7 +274,10 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     uint32_t gs = 0;  // slabs processed by this group so far (selects buffers and mbarrier parities)
     float* st_acc = stat_base + group * (EPI_STAT_ACC_FLOATS + EPI_STAT_SCR_FLOATS);
     float* st_scr = st_acc + EPI_STAT_ACC_FLOATS;
-    int st_pend = -1;  // column offset of the slab whose warp partials wait in st_scr (uniform across the group)
+    // column offsets of the (at most two) slabs whose warp partials wait in the two halves of st_scr (uniform across
+    // the group): with ONE barrier per slab the partials of slab g are complete only after the barrier that closes
+    // slab g + 1, so they are added during slab g + 2, just before that half is written again
+    int st_pend = -1, st_pend_old = -1;
     // Operand prefetch runs one slab ahead of the math ACROSS tile boundaries (leader thread only): the sequence of
     // (tile, slab) pairs of a group is known up front, and for narrow layers (one slab per tile) the TMA latency of
     // the residual / mask slab would otherwise sit in every tile's critical path.
@@ -295,42 +297,66 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
       s1 = owner ? h : nslab_;
       return true;
     };
-    int pf_it = -1, pf_s = 0, pf_s1 = 0;
+    // Residual / accumulate / mask operands: every thread fetches ITS OWN row of a slab (4 x 16 bytes per operand) with
+    // cp.async straight into the swizzled slot it will read itself -- no TMA (a 128-row x 64-byte operand box costs
+    // ~1.3 kcycles of TMA row rate, 2.7 kcycles per slab with two operands, against ~0.1 for the LSU path), no
+    // mbarrier, no cross-thread hand-off, no registers held across the wait.  The prefetch runs OD - 1 slabs ahead
+    // ACROSS tile boundaries: the (tile, slab) sequence of a group is known up front.
+    const uint8_t* opsrc[2] = {nullptr, nullptr};
+    long long opld[2] = {0, 0};
+    {
+      int no = 0;
+      if (p.n_add) {
+        opsrc[no] = (const uint8_t*)(p.epi.accumulate ? p.out : p.epi.res);
+        opld[no] = p.epi.accumulate ? p.ld_out : p.epi.ld_res;
+        ++no;
+      }
+      if (p.has_mask) {
+        opsrc[no] = (const uint8_t*)p.epi.mask;
+        opld[no] = p.epi.ld_mask;
+      }
+    }
+    int pf_it = -1, pf_s = 0, pf_s1 = 0, pf_n0 = 0;
     int pf_ob = 0;  // operand ring slot of the next prefetch
-    auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs
+    long long pf_row = 0;
+    bool pf_valid = false;
+    auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs; this thread's row in it
       for (++pf_it; pf_it < n_it; ++pf_it) {
-        const int n0_ = ((blockIdx.x + pf_it * gridDim.x) % p.n_tiles) * p.block_n;
+        const int tile_ = blockIdx.x + pf_it * gridDim.x;
+        const int n0_ = (tile_ % p.n_tiles) * p.block_n;
         const int nslab_ = (min(p.block_n, p.N - n0_) + EPI_SLAB_COLS - 1) / EPI_SLAB_COLS;
-        if (seg(pf_it, nslab_, pf_s, pf_s1)) return;
+        if (seg(pf_it, nslab_, pf_s, pf_s1)) {
+          int st_[3];
+          tile_coords(p, tile_ / p.n_tiles, st_);
+          const int m1 = st_[0] + r1, m2 = st_[1] + r2, m3 = st_[2] + r3;
+          pf_valid = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
+          pf_row = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
+          pf_n0 = n0_;
+          return;
+        }
       }
     };
     pf_seek();
     auto prefetch_next = [&]() {
-      if (pf_it >= n_it) return;
-      const int pf_tile = blockIdx.x + pf_it * gridDim.x;
-      const int n_tile = pf_tile % p.n_tiles, m_tile = pf_tile / p.n_tiles;
-      int st[3];
-      tile_coords(p, m_tile, st);
-      int o1 = 0, o2 = 0, o3 = 0;
+      if (pf_it < n_it) {
+        const int nb = pf_n0 + pf_s * 32;
+        if (pf_valid) {
+          for (int o = 0; o < n_ops; ++o) {
+            const uint8_t* src = opsrc[o] + (pf_row * opld[o] + nb) * 2;
+            uint8_t* dst = op_buf + (o * OD + pf_ob) * EPI_SLAB_BYTES;
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const int d = p.o_dim[j];
-        o1 = d == 1 ? st[j] : o1;
-        o2 = d == 2 ? st[j] : o2;
-        o3 = d == 3 ? st[j] : o3;
+            for (int c = 0; c < 4; ++c)
+              if (nb + 8 * c + 8 <= p.N) cp_async16(dst + slab_off(r, c), src + 16 * c);
+          }
+        }
+        if (++pf_ob == OD) pf_ob = 0;
+        if (++pf_s == pf_s1) pf_seek();
       }
-      const int n0 = n_tile * p.block_n;
-      uint64_t* bar = &sh->op_full[group][pf_ob];
-      mbar_expect_tx(bar, (uint32_t)(n_ops * EPI_SLAB_BYTES));
-      for (int o = 0; o < n_ops; ++o)
-        tma_load(&p.tm_op[o], bar, op_buf + (o * OD + pf_ob) * EPI_SLAB_BYTES, p.rank_o, n0 + pf_s * 32, o1, o2, o3, 0);
-      if (++pf_ob == OD) pf_ob = 0;
-      if (++pf_s == pf_s1) pf_seek();
+      cp_async_commit();  // one group per call, also when empty: the wait counts stay aligned with the slab index
     };
-    if (leader && n_ops > 0)
+    if (n_ops > 0)
       for (int i = 0; i < OD - 1; ++i) prefetch_next();  // the first OD - 1 slabs of this group's sequence
     int oslot = 0;     // operand ring slot of the slab being processed
-    uint32_t oph = 0;  // its mbarrier parity
     for (int it = 0; it < n_it; ++it) {
       const int tile = blockIdx.x + it * gridDim.x;
       const int buf = it & 1;
@@ -364,15 +390,9 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         const int b = gs & 1;
         uint32_t raw[32];
         tmem_ld32_issue(taddr0 + (uint32_t)(s * 32), raw);
-        if (leader) {
-          // operands of slab gs + OD - 1 (possibly of a later tile) into the ring slot that slab gs - 1 used: every
-          // thread has passed that slab's closing barrier
-          if (n_ops > 0) prefetch_next();
-          Probe pw{p.dbg, 0};
-          pw.begin();
-          bulk_wait_read<1>();
-          pw.end(6);  // the store that last read out_buf[b] (two slabs ago) has drained it
-        }
+        // this thread's operand rows of slab gs + OD - 1 (possibly of a later tile) into the ring slot that slab
+        // gs - 1 used -- read by this same thread one iteration ago, so plain program order protects it
+        if (n_ops > 0) prefetch_next();
         tmem_ld_wait();
         // accumulators are in registers: the owning group hands the TMEM buffer back to the MMA warp (on a shared last
         // tile the other group may still be reading it, but no mainloop follows the last tile)
@@ -381,21 +401,21 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           __syncwarp();
           if (lane == 0) mbar_arrive(&sh->tmem_empty[buf]);
         }
-        if (n_ops > 0) mbar_wait_warp(&sh->op_full[group][oslot], oph, 5);
-        named_bar(bar_id, 128);  // out_buf[b] is free for everybody
-        if (STATS && st_pend >= 0) {
-          // every warp stored its partials of the previous slab before this barrier, and nobody overwrites them before
-          // the next one ("slab complete")
-          if (t < 64) epi_stats_accumulate(st_acc, st_scr, t, st_pend);
+        if (n_ops > 0) {
+          if (OD == 2) cp_async_wait<1>(); else if (OD == 3) cp_async_wait<2>(); else cp_async_wait<3>();
+        }
+        if (STATS) {
+          // two barriers ago every warp had stored slab gs - 2's partials into scratch half gs & 1; nobody writes that
+          // half again before the barrier that closes THIS slab
+          if (st_pend_old >= 0 && t < 64) epi_stats_accumulate(st_acc, st_scr + (gs & 1) * EPI_STAT_SCR_HALF, t, st_pend_old);
+          st_pend_old = st_pend;
           st_pend = -1;
         }
+        // out_buf[b] is free: the leader drained the store that last read it before it arrived at the previous barrier
         uint8_t* ob = out_buf + b * EPI_SLAB_BYTES;
         const uint8_t* op0 = op_buf + oslot * EPI_SLAB_BYTES;
         const uint8_t* op1 = op_buf + (OD + oslot) * EPI_SLAB_BYTES;
-        if (++oslot == OD) {
-          oslot = 0;
-          oph ^= 1;
-        }
+        if (++oslot == OD) oslot = 0;
         const float* ss = s_shift + s * 32;
         const bool zero = STATS && !valid;
         switch (variant) {
@@ -417,22 +437,31 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           default: epi_slab_math<true, 1, true, true>(raw, ss, op0, op1, ob, r, zero); break;
         }
         fence_proxy_async();
-        named_bar(bar_id, 128);  // slab complete
+        if (leader) {
+          // ONE barrier per slab: before arriving, the leader makes sure the store issued one slab ago has finished
+          // reading the OTHER output buffer, so everybody may overwrite it right after this barrier
+          Probe pw{p.dbg, 0};
+          pw.begin();
+          bulk_wait_read<0>();
+          pw.end(6);
+        }
+        named_bar(bar_id, 128);  // slab complete; the other output buffer is free
         if (leader) {
           tma_store(&p.tm_out, ob, p.rank_o, n0 + s * 32, o1, o2, o3);
           bulk_commit();
         }
         if (STATS) {
-          epi_slab_stats_part(ob, t, st_scr);
+          epi_slab_stats_part(ob, t, st_scr + (gs & 1) * EPI_STAT_SCR_HALF);
           st_pend = s * 32;
         }
         __syncwarp();
       }
       if (leader) pb.end(5);  // tmem_full seen -> last slab of the tile handed to the store engine
     }
-    if (STATS && st_pend >= 0) {
+    if (STATS) {
       named_bar(bar_id, 128);
-      if (t < 64) epi_stats_accumulate(st_acc, st_scr, t, st_pend);
+      if (st_pend_old >= 0 && t < 64) epi_stats_accumulate(st_acc, st_scr + (gs & 1) * EPI_STAT_SCR_HALF, t, st_pend_old);
+      if (st_pend >= 0 && t < 64) epi_stats_accumulate(st_acc, st_scr + ((gs + 1) & 1) * EPI_STAT_SCR_HALF, t, st_pend);
     }
     if (leader) {
       pb.begin();

@@ -47,7 +47,6 @@ struct TgParams {
   asf_epilogue_t epi;
   // mode 0, TMA epilogue: output / operand tensor maps over the output M-space, 32-channel boxes, 64B swizzle
   CUtensorMap tm_out;
-  CUtensorMap tm_op[2];  // op 0: additive (residual, or the output itself when accumulating) else mask; op 1: mask
   int rank_o;            // rank of tm_out / tm_op (1 + mapped M dims)
   int o_dim[3];          // M-dim j -> coordinate slot (1..3) of the output maps, 0 = unmapped
   int n_add, has_mask;   // operands: n_add in {0,1} additive, has_mask in {0,1}
@@ -74,7 +73,6 @@ struct TgShared {
   uint64_t empty[TG_MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t op_full[2][4];  // [epilogue group][operand buffer] (TgParams::op_depth of them in use)
   uint32_t tmem_base;
   uint32_t stat_flag;  // "this CTA drew the last statistics ticket" (stats_reduce.cuh)
 };
@@ -454,23 +452,6 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->ld_out;
       rc = encode_map(&p.tm_out, q->out, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS, CU_TENSOR_MAP_SWIZZLE_64B);
       if (rc) return rc;
-      int no = 0;
-      if (n_add) {
-        if (q->epi.accumulate) {
-          p.tm_op[no++] = p.tm_out;
-        } else {
-          for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->epi.ld_res;
-          rc = encode_map(&p.tm_op[no++], q->epi.res, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS,
-                          CU_TENSOR_MAP_SWIZZLE_64B);
-          if (rc) return rc;
-        }
-      }
-      if (has_mask) {
-        for (int i = 0; i < nd_o; ++i) ostr[i] = ostr_rows[i] * q->epi.ld_mask;
-        rc = encode_map(&p.tm_op[no++], q->epi.mask, q->N, nd_o, oext, ostr, obox, EPI_SLAB_COLS,
-                        CU_TENSOR_MAP_SWIZZLE_64B);
-        if (rc) return rc;
-      }
       const size_t smem_t = (size_t)stages * stage_bytes + tma_fixed;
       static size_t smem_set_t[2] = {0, 0};
       const int si = q->epi.stats ? 1 : 0;
