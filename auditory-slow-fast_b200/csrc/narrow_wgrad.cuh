@@ -174,7 +174,17 @@ __global__ void __launch_bounds__(NW_THREADS) narrow_wgrad_kernel(const __grid_c
   }
 }
 
-// which launches take this path, and with how many CTAs (= the ksplit the caller sizes the workspace for)
+// positions per CTA and number of CTAs (= the ksplit the caller sizes the workspace for) of a narrow-layer launch
+static void narrow_wgrad_rows(const asf_tapgemm_t* q, int* ksplit, int* rows_per_cta) {
+  const long long m_total = (long long)q->m_ext[0] * q->m_ext[1] * q->m_ext[2];
+  int ctas = 2 * sm_budget(q);
+  long long rpc = (cdiv(m_total, ctas) + NW_ROWS - 1) / NW_ROWS * NW_ROWS;
+  if (rpc < 4 * NW_ROWS) rpc = 4 * NW_ROWS;
+  *rows_per_cta = (int)rpc;
+  *ksplit = (int)cdiv(m_total, rpc);
+}
+
+// which launches take the CUDA-core path
 static bool narrow_wgrad_plan(const asf_tapgemm_t* q, int* ksplit, int* rows_per_cta) {
   const long long m_total = (long long)q->m_ext[0] * q->m_ext[1] * q->m_ext[2];
   const long long nblk = (long long)(q->N / 2) * q->ntaps * (q->K / 4);
@@ -189,11 +199,7 @@ static bool narrow_wgrad_plan(const asf_tapgemm_t* q, int* ksplit, int* rows_per
     return false;
   // every tensor-map stride keeps 8-channel vectors 16-byte aligned (checked by the launcher); all taps of a
   // layer share b_tap space ntaps_w
-  int ctas = 2 * sm_budget(q);
-  long long rpc = (cdiv(m_total, ctas) + NW_ROWS - 1) / NW_ROWS * NW_ROWS;
-  if (rpc < 4 * NW_ROWS) rpc = 4 * NW_ROWS;
-  *rows_per_cta = (int)rpc;
-  *ksplit = (int)cdiv(m_total, rpc);
+  narrow_wgrad_rows(q, ksplit, rows_per_cta);
   return true;
 }
 

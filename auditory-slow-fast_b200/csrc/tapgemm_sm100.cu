@@ -217,6 +217,7 @@ static int debug_sync(cudaStream_t st) {
 }
 
 #include "narrow_wgrad.cuh"
+#include "narrow_wgrad_mma.cuh"
 #include "narrow_conv.cuh"
 
 // wgrad tiling: 64-row boxes (half of the 128-row M tile, split on its slowest boxed dim), output-channel tile of one
@@ -230,7 +231,14 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   w->narrow = 0;
   {
     int ks = 0, rpc = 0;  // a caller-chosen ksplit other than the plan's keeps the layer on the tensor-core kernel
-    if (narrow_wgrad_plan(q, &ks, &rpc) && (q->ksplit <= 0 || q->ksplit == ks)) {
+    if (narrow_wgrad_mma_ok(q)) {  // warp-MMA kernel: every narrow layer (N <= 64, taps * K <= 256)
+      narrow_wgrad_rows(q, &ks, &rpc);
+      if (q->ksplit <= 0 || q->ksplit == ks) {
+        w->narrow = 2;
+        w->narrow_rows = rpc;
+        w->ksplit = ks;
+      }
+    } else if (narrow_wgrad_plan(q, &ks, &rpc) && (q->ksplit <= 0 || q->ksplit == ks)) {
       w->narrow = 1;
       w->narrow_rows = rpc;
       w->ksplit = ks;
@@ -490,7 +498,8 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       npr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; npr->N = q->N; npr->K = q->K; npr->taps = q->ntaps;
       npr->block_n = wp.ksplit; npr->grid = wp.ksplit;
     }
-    rc = narrow_wgrad_launch(q, wp.ksplit, wp.narrow_rows, st);
+    rc = wp.narrow == 2 ? narrow_wgrad_mma_launch(q, wp.ksplit, wp.narrow_rows, st)
+                        : narrow_wgrad_launch(q, wp.ksplit, wp.narrow_rows, st);
     if (rc) return rc;
     prof_end(npr, st);
     ASF_LAUNCH_CHECK();

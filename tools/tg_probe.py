@@ -40,6 +40,8 @@ def main():
         res.buf.normal_()
         dy = Act(u.y.B, u.y.T, u.y.F, cout, h.dtype, h.device)
         dy.buf.normal_()
+        xres = Act(u.x.B, u.x.T, u.x.F, cin, h.dtype, h.device)
+        xres.buf.normal_()
 
         def fwd_frozen():
             u.bn.eval()
@@ -50,7 +52,18 @@ def main():
             u.bn.train()
             u.res = None
             h._prepare_unit(u, True)
-            h._conv_fwd(u, u.y, dict(stats=u.stats, stats_stride=u.Cout))
+            ws, tk = h._stat_bufs(u)
+            h._conv_fwd(u, u.y, dict(stats=u.stats, stats_stride=u.Cout, stats_ws=ws, stats_ticket=tk))
+
+        def fwd_plain():
+            u.bn.eval()
+            u.res = None
+            h._unit_forward(u, training=False)
+
+        def dgrad_res():
+            u.bn.eval()
+            h._prepare_unit(u, True)
+            h._conv_dgrad(u, dy, u.x.grad, accumulate=False, res=xres, mask=u.x)
 
         def dgrad():
             u.bn.eval()
@@ -58,7 +71,10 @@ def main():
             h._conv_dgrad(u, dy, u.x.grad, accumulate=False, mask=u.x)
 
         for mode in modes:
-            fn = {"fwd_frozen": fwd_frozen, "fwd_stats": fwd_stats, "dgrad": dgrad}[mode]
+            fn = {"fwd_frozen": fwd_frozen, "fwd_stats": fwd_stats, "dgrad": dgrad, "fwd_plain": fwd_plain,
+                  "dgrad_res": dgrad_res}[mode]
+            if mode == "dgrad_res" and (s != (1, 1)):
+                continue
             fn()
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
