@@ -11,16 +11,33 @@
 // owns the 8-column blocks jb = w, w + 8, ... of j for ALL n blocks, so every B fragment feeds up to four MMAs.
 // Partial sums leave as plain stores in the [ksplit][N][taps][K] workspace that asf_unpack_wgrad(_multi) reduces.
 //
-// Why: the CUDA-core version (narrow_wgrad.cuh) needed 74 KB of shared memory per CTA and ~42 us per launch on every
-// SM -- 21 launches = 0.9 ms during which no tcgen05 CTA (which needs the whole SM's shared memory) could start.
+// History: the first (CUDA-core FMA) version of this kernel took 18..44 us per launch for 7..16 MB of operands
+// (profiles/r02_narrow_wgrad_ncu.txt); the layers with N * K * taps > 2048 ran on the tcgen05 kernel at 30..70 us,
+// bound by the TMA row rate of their 16..64-byte rows.
 #pragma once
 
 constexpr int NWM_THREADS = 256;
+constexpr int NW_ROWS = 128;  // granularity of a CTA's range of positions
+
+struct NwParams {
+  const bf16* x;
+  const bf16* y;
+  float* dwp;
+  int nd, y_nd;
+  long long a_dim[4], a_stride[4], y_stride[4];
+  int m_ext[3], m_to_a[3], y_m_to_a[3];
+  int ntaps, ntaps_w, N, K;
+  int a_off[ASF_MAX_TAPS][4];
+  int b_tap[ASF_MAX_TAPS];
+  int m_total;
+  int rows_per_cta;  // multiple of NW_ROWS
+  int groups;        // row groups sharing an accumulator block (power of two, nblk * groups <= 256)
+};
+
 constexpr int NWM_MAX_JBW = 4;   // 8-column blocks of j per warp -> taps * K <= 256
-constexpr int NWM_MAX_VEC = 17;  // 16-byte vectors per thread per tile (2 threads per position)
 
 struct NwmParams {
-  NwParams g;     // geometry / pointers (narrow_wgrad.cuh)
+  NwParams g;     // geometry / pointers
   int rows_tile;  // positions per pipeline stage: 128 or 64
   int py, px;     // shared-memory pitches (elements) of the Y and X tiles
   int n_pad;      // N rounded up to 16
@@ -46,13 +63,13 @@ __device__ __forceinline__ void nwm_cp16(void* dst, const void* src, int src_byt
 }
 
 template <int NB>  // 16-row blocks of n: 1, 2 or 4
-__global__ void __launch_bounds__(NWM_THREADS) narrow_wgrad_mma_kernel(const __grid_constant__ NwmParams q) {
+__global__ void __maxnreg__(96) narrow_wgrad_mma_kernel(const __grid_constant__ NwmParams q) {
   extern __shared__ __align__(16) uint8_t nwm_smem[];
   pdl_trigger();
   const NwParams& p = q.g;
   const int N = p.N, K = p.K, T = p.ntaps;
   const int J = T * K, JB = J >> 3;
-  const int NV = N >> 3, KV = K >> 3, vpr = NV + T * KV;
+  const int NV = N >> 3, KV = K >> 3;
   const int R = q.rows_tile, PY = q.py, PX = q.px;
   const int stage_elems = R * (PY + PX);
   bf16* sbase = (bf16*)nwm_smem;
@@ -60,52 +77,57 @@ __global__ void __launch_bounds__(NWM_THREADS) narrow_wgrad_mma_kernel(const __g
   const int r_begin = blockIdx.x * p.rows_per_cta;
   const int r_end = min(r_begin + p.rows_per_cta, p.m_total);
   const unsigned e0 = (unsigned)p.m_ext[0], e1 = (unsigned)p.m_ext[1];
-  // load role: position row_l of the tile, vectors part_l, part_l + parts, ...
-  const int parts = NWM_THREADS / R;
-  const int row_l = t % R, part_l = t / R;
-
+  // Load role.  A tile is R positions x (1 + T) "units": unit 0 = the position's N output gradients, unit 1 + tap = the
+  // K input channels that tap reads.  A unit is CONTIGUOUS in global and in shared memory, so a thread does the
+  // coordinate arithmetic once per unit (two 32-bit divisions, the tap's bounds test) and then issues plain 16-byte
+  // cp.async with constant offsets.  (The first version decoded every 16-byte vector separately: 1200 instructions
+  // per warp and tile, 16.6 M warp instructions per launch -- the kernel was bound by address generation, 38 us for
+  // 16 MB.)
+  const int r_log2 = R == 128 ? 7 : 6;
   auto load_tile = [&](int tile0, int stage) {
     bf16* sy = sbase + (size_t)stage * stage_elems;
     bf16* sx = sy + R * PY;
-    const int pnt = tile0 + row_l;
-    const bool live = pnt < r_end;
-    const unsigned up = (unsigned)(live ? pnt : 0);
-    const unsigned q1 = up / e0;
-    const long long m[3] = {(long long)(up - q1 * e0), (long long)(q1 % e1), (long long)(q1 / e1)};
-    long long yoff = 0;
+    for (int uidx = t; uidx < R * (T + 1); uidx += NWM_THREADS) {
+      const int row = uidx & (R - 1), unit = uidx >> r_log2;
+      const int pnt = tile0 + row;
+      const bool live = pnt < r_end;
+      const unsigned up = (unsigned)(live ? pnt : 0);
+      const unsigned q1 = up / e0;
+      const unsigned q2 = q1 / e1;
+      const int m[3] = {(int)(up - q1 * e0), (int)(q1 - q2 * e1), (int)q2};
+      const bf16* src;
+      bf16* dst;
+      int nvec;
+      bool ok = live;
+      if (unit == 0) {
+        long long yoff = 0;
 #pragma unroll
-    for (int j = 0; j < 3; ++j)
-      if (p.y_m_to_a[j] > 0) yoff += m[j] * p.y_stride[p.y_m_to_a[j] - 1];
-    long long base[4];
+        for (int j = 0; j < 3; ++j)
+          if (p.y_m_to_a[j] > 0) yoff += (long long)m[j] * p.y_stride[p.y_m_to_a[j] - 1];
+        src = p.y + yoff;
+        dst = sy + row * PY;
+        nvec = NV;
+      } else {
+        const int tp = unit - 1;
+        long long off = 0;
 #pragma unroll
-    for (int d = 0; d < 4; ++d) {
-      long long c0 = 0;
+        for (int d = 0; d < 4; ++d) {
+          if (d < p.nd) {
+            int c0 = p.a_off[tp][d];
 #pragma unroll
-      for (int j = 0; j < 3; ++j)
-        if (p.m_to_a[j] == d + 1) c0 += m[j];
-      base[d] = c0;
-    }
-#pragma unroll
-    for (int u = 0; u < NWM_MAX_VEC; ++u) {
-      const int v = part_l + parts * u;
-      if (v < vpr) {
-        if (v < NV) {
-          nwm_cp16(sy + row_l * PY + v * 8, p.y + (live ? yoff + v * 8 : 0), live ? 16 : 0);
-        } else {
-          const int w = v - NV, tp = w / KV, cv = w - tp * KV;
-          long long off = cv * 8;
-          bool ok = live;
-#pragma unroll
-          for (int d = 0; d < 4; ++d) {
-            if (d < p.nd) {
-              const long long coord = base[d] + p.a_off[tp][d];
-              ok = ok && coord >= 0 && coord < p.a_dim[d];
-              off += coord * p.a_stride[d];
-            }
+            for (int j = 0; j < 3; ++j)
+              if (p.m_to_a[j] == d + 1) c0 += m[j];
+            ok = ok && c0 >= 0 && c0 < (int)p.a_dim[d];
+            off += (long long)c0 * p.a_stride[d];
           }
-          nwm_cp16(sx + row_l * PX + tp * K + cv * 8, p.x + (ok ? off : 0), ok ? 16 : 0);
         }
+        src = p.x + off;
+        dst = sx + row * PX + tp * K;
+        nvec = KV;
       }
+      if (!ok) src = p.x;  // any valid address: zero bytes are read, sixteen zero bytes are written
+      const int nbytes = ok ? 16 : 0;
+      for (int v = 0; v < nvec; ++v) nwm_cp16(dst + v * 8, src + v * 8, nbytes);
     }
     cp_async_commit();
   };
@@ -179,6 +201,16 @@ __global__ void __launch_bounds__(NWM_THREADS) narrow_wgrad_mma_kernel(const __g
   }
 }
 
+// positions per CTA and number of CTAs (= the ksplit the caller sizes the workspace for) of a narrow-layer launch
+static void narrow_wgrad_rows(const asf_tapgemm_t* q, int* ksplit, int* rows_per_cta) {
+  const long long m_total = (long long)q->m_ext[0] * q->m_ext[1] * q->m_ext[2];
+  int ctas = 2 * sm_budget(q);
+  long long rpc = (cdiv(m_total, ctas) + NW_ROWS - 1) / NW_ROWS * NW_ROWS;
+  if (rpc < 4 * NW_ROWS) rpc = 4 * NW_ROWS;
+  *rows_per_cta = (int)rpc;
+  *ksplit = (int)cdiv(m_total, rpc);
+}
+
 // which layers this kernel takes
 static bool narrow_wgrad_mma_ok(const asf_tapgemm_t* q) {
   static int enabled = -1;
@@ -199,9 +231,14 @@ static void nwm_geometry(const asf_tapgemm_t* q, NwmParams* w) {
   // pitch / 8 odd: the eight 16-byte rows of an ldmatrix 8 x 8 tile fall into distinct bank groups
   w->py = w->n_pad + 8;
   w->px = J + (((J >> 3) & 1) ? 16 : 8);
-  const int vpr = q->N / 8 + J / 8;
   int R = 128;
-  if (vpr > 2 * NWM_MAX_VEC || (size_t)2 * 128 * (w->py + w->px) * 2 > 96 * 1024) R = 64;
+  static int r_env = -1;
+  if (r_env < 0) {
+    const char* e = getenv("ASF_NWM_ROWS");
+    r_env = e ? atoi(e) : 0;
+  }
+  if (r_env == 64) R = 64;
+  if ((size_t)2 * 128 * (w->py + w->px) * 2 > 96 * 1024) R = 64;
   w->rows_tile = R;
 }
 
@@ -237,8 +274,6 @@ static int narrow_wgrad_mma_launch(const asf_tapgemm_t* q, int ksplit, int rows_
   p.m_total = q->m_ext[0] * q->m_ext[1] * q->m_ext[2];
   p.rows_per_cta = rows_per_cta;
   nwm_geometry(q, &w);
-  const int vpr = q->N / 8 + q->ntaps * q->K / 8;
-  ASF_CHECK_ARG(vpr <= (NWM_THREADS / w.rows_tile) * NWM_MAX_VEC, "asf_tapgemm: narrow wgrad position too wide (%d vectors)", vpr);
   const size_t smem = (size_t)2 * w.rows_tile * (w.py + w.px) * sizeof(bf16);
   ASF_CHECK_ARG(smem <= 200 * 1024, "asf_tapgemm: narrow wgrad tile does not fit in shared memory");
   const int nb = w.n_pad / 16;

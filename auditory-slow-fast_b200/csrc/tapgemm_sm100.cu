@@ -216,7 +216,6 @@ static int debug_sync(cudaStream_t st) {
   return 0;
 }
 
-#include "narrow_wgrad.cuh"
 #include "narrow_wgrad_mma.cuh"
 #include "narrow_conv.cuh"
 
@@ -225,7 +224,7 @@ static int debug_sync(cudaStream_t st) {
 struct WgPlan {
   int box[3];
   int halves, tn, ny, nx, r_tiles, c_tiles, tmem_cols, stages, ksplit, m_tiles;
-  int narrow, narrow_rows;  // CUDA-core path for the narrow layers (narrow_wgrad.cuh): ksplit = its CTA count
+  int narrow, narrow_rows;  // warp-MMA path for the narrow layers (narrow_wgrad_mma.cuh): ksplit = its CTA count
 };
 static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   w->narrow = 0;
@@ -238,10 +237,6 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
         w->narrow_rows = rpc;
         w->ksplit = ks;
       }
-    } else if (narrow_wgrad_plan(q, &ks, &rpc) && (q->ksplit <= 0 || q->ksplit == ks)) {
-      w->narrow = 1;
-      w->narrow_rows = rpc;
-      w->ksplit = ks;
     }
   }
   int prod = 1;
@@ -275,6 +270,14 @@ static int wgrad_plan(const asf_tapgemm_t* q, WgPlan* w) {
   const int stage_bytes = (w->ny + w->nx) * WG2_BOX_BYTES;
   int stages = (227 * 1024 - (int)sizeof(TgShared)) / stage_bytes;
   if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
+  {
+    static int cap = -1;
+    if (cap < 0) {
+      const char* e = getenv("ASF_WG_STAGES");
+      cap = e ? atoi(e) : 0;
+    }
+    if (cap >= 2 && stages > cap) stages = cap;
+  }
   ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: wgrad stage does not fit twice in shared memory");
   w->stages = stages;
   const int64_t base_tiles = (int64_t)w->r_tiles * w->c_tiles * q->ntaps;
@@ -427,6 +430,16 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
     if (use_tma) {
       stages = (smem_cap - tma_fixed) / stage_bytes;
       if (stages > TG_MAX_STAGES) stages = TG_MAX_STAGES;
+      {
+        // ring depth cap (ASF_TG_STAGES): shared memory a tcgen05 CTA does not take is what lets the CUDA-core /
+        // warp-MMA CTAs of the narrow layers run on the same SM beside it
+        static int cap = -1;
+        if (cap < 0) {
+          const char* e = getenv("ASF_TG_STAGES");
+          cap = e ? atoi(e) : 0;
+        }
+        if (cap >= 2 && stages > cap) stages = cap;
+      }
       ASF_CHECK_ARG(stages >= 2, "asf_tapgemm: not enough shared memory for 2 stages");
       p.stages = stages;
       p.n_add = n_add;
@@ -498,8 +511,7 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
       npr->M = q->m_ext[0] * q->m_ext[1] * q->m_ext[2]; npr->N = q->N; npr->K = q->K; npr->taps = q->ntaps;
       npr->block_n = wp.ksplit; npr->grid = wp.ksplit;
     }
-    rc = wp.narrow == 2 ? narrow_wgrad_mma_launch(q, wp.ksplit, wp.narrow_rows, st)
-                        : narrow_wgrad_launch(q, wp.ksplit, wp.narrow_rows, st);
+    rc = narrow_wgrad_mma_launch(q, wp.ksplit, wp.narrow_rows, st);
     if (rc) return rc;
     prof_end(npr, st);
     ASF_LAUNCH_CHECK();

@@ -300,11 +300,20 @@ def run_ours(args):
         j = i % args.rotate
         return step(dev_w[j], dev_v[j], dev_n[j])
 
+    def host_batch(i):
+        j = i % args.rotate
+        return host_w[j], ({"verb": host_v[j], "noun": host_n[j]} if two_heads else host_v[j])
+
     def host_step(i):
         j = i % args.rotate
         if train:
-            lab = {"verb": host_v[j], "noun": host_n[j]} if two_heads else host_v[j]
-            return float(tstep(host_w[j], lab))  # H2D copies + step + loss read back
+            # every step: this step's pinned-host batch -> device (started while the previous step was still running:
+            # TrainStep.prefetch, a copy stream and two staging slots), the step, and the loss read back to the host
+            if not tstep_pending[0]:
+                tstep.prefetch(*host_batch(i))
+            tstep.prefetch(*host_batch(i + 1))
+            tstep_pending[0] = True
+            return float(tstep())
         w = host_w[j].to(dev, non_blocking=True)
         out = step(w, None, None)
         return out.float().sum().item() if args.workload == "logmel" else out.cpu()
@@ -341,6 +350,7 @@ def run_ours(args):
         return ms, launches, clocks
 
     launches_per_step = [0]
+    tstep_pending = [False]
     if train:
         resident_step(0)  # builds plans / captures the graph
         torch.cuda.synchronize()
@@ -520,6 +530,31 @@ def _stock_gpu(args, dev, B, steps=12, warmup=4):
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / steps
             res[tag] = {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms}
+            # the same step as ONE CUDA graph (what our arm does): removes stock PyTorch's launch overhead, leaves its kernels
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    for _ in range(3):
+                        one()
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    one()
+                for _ in range(warmup):
+                    g.replay()
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(steps):
+                    g.replay()
+                e1.record()
+                torch.cuda.synchronize()
+                msg = e0.elapsed_time(e1) / steps
+                res[tag + "_cudagraph"] = {"value": B / (msg * 1e-3), "unit": UNIT, "ms_per_step": msg}
+                del g
+            except Exception as e:
+                res[tag + "_cudagraph"] = {"error": "%s: %s" % (type(e).__name__, str(e)[:200])}
             del opt, params, state, net
             torch.cuda.empty_cache()
     finally:

@@ -198,9 +198,10 @@ int asf_conv_wgrad_simt(const void* in, int in_dtype, const void* dout, int dout
  *         pre-zeroing) its partial sums to dwp[k][N][ntaps_w][K] at tap b_tap[tap]; asf_unpack_wgrad adds the
  *         groups.  ksplit = 0 lets the launcher choose -- query it first with asf_tapgemm_wgrad_ksplit to size dwp.
  *
- * Narrow layers (N, K powers of two in 8..64, >= 16384 output positions: the fast pathway) do not fill a 128-row MMA
- * tile; both modes route them to CUDA-core kernels behind this same entry point (mode 0: csrc/narrow_conv.cuh when
- * N*K*ntaps <= 8192 and the output is bf16; mode 1: csrc/narrow_wgrad.cuh, ksplit = its CTA count).
+ * Narrow layers (8..64 output channels, >= 16384 output positions: the fast pathway) do not fill a 128-row tcgen05
+ * tile; both modes route them to warp-level tensor-core kernels (mma.sync) behind this same entry point (mode 0:
+ * csrc/narrow_conv.cuh when N, K are powers of two, K <= 128, N*K*ntaps <= 8192 and the output is bf16; mode 1:
+ * csrc/narrow_wgrad_mma.cuh when N <= 64 and ntaps*K <= 256, ksplit = its CTA count).
  * asf_narrow_conv_launches() counts the mode-0 launches that took that route (tests use it to prove coverage).
  */
 typedef struct {
