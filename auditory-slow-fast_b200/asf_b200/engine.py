@@ -773,7 +773,7 @@ class Engine:
                 d.rscale = rs.data_ptr() if rs is not None else None
                 d.O, d.I, d.taps, d.ksplit, d.accumulate = O, I, taps, ks, int(acc)
                 d.chunk0 = chunk
-                chunk += -(-(O * I * taps) // 1024)  # ASF_UNPACK_CHUNK
+                chunk += -(-(O * I * taps) // (1024 if ks < 32 else 256))  # ASF_UNPACK_CHUNK / ASF_UNPACK_CHUNK_DEEP
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             if len(cache) > 64:
                 cache.clear()
@@ -787,14 +787,16 @@ class Engine:
         params = [(n, p) for n, p in self.model.named_parameters()]
         # reverse registration order ~ order in which backward produces them: head, s5, s4, ... stems
         params = params[::-1]
-        total = sum(p.numel() for _, p in params)
+        # every view starts on a 16-byte boundary (the 97-element verb bias would otherwise knock every later tensor off
+        # it): the split-K reduction and the optimiser then use 16-byte accesses on all of them
+        total = sum((p.numel() + 3) // 4 * 4 for _, p in params)
         self._flat_grad = torch.zeros(total, dtype=torch.float32, device=self.device)
         off = 0
         self._grad_offsets = {}
         for n, p in params:
             self._grad_views[n] = self._flat_grad[off:off + p.numel()].view_as(p)
             self._grad_offsets[n] = (off, p.numel())
-            off += p.numel()
+            off += (p.numel() + 3) // 4 * 4
         self._param_by_name = dict(params)
         self._name_of = {id(p): n for n, p in params}
 

@@ -644,9 +644,13 @@ __global__ void __launch_bounds__(256) unpack_wgrad_kernel(const float* __restri
 }
 
 // The same reduction for MANY layers in one launch (the engine defers the unpack of a backward segment: ~100 small
-// launches on the weight-gradient streams become a handful).  Block b owns ASF_UNPACK_CHUNK (1024) consecutive elements
-// of the layer whose chunk range contains b: 64 lanes x float4 per pass, four split lanes per element group (lane j
-// adds partial tiles j, j + 4, ... in ascending order, then the lanes are folded in a fixed order).
+// launches on the weight-gradient streams become a handful).  Block b owns `chunk` consecutive elements of the layer
+// whose chunk range contains b.  The 256 threads are EL element lanes (one float4 each) x SL split lanes; SL follows the
+// layer's split depth -- 1 for ksplit <= 2 (the big s4 / s5 layers: every thread streams elements), 4 up to 31, 16 from
+// 32 on (the narrow layers and the stems leave 100..300 partial rows of a few hundred weights: 16 lanes share them
+// and the block is 256 instead of 1024 elements, so that the reduction does not sit on one CTA for 70 dependent loads).
+// Split lane j adds partial rows j, j + SL, ... in ascending order, four loads in flight; the lanes are then folded in
+// ascending order: bit-reproducible.
 __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpack_desc_t* __restrict__ d, int n) {
   __shared__ float4 part[256];
   pdl_trigger();
@@ -658,36 +662,44 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpac
     if (d[mid].chunk0 <= b) lo = mid; else hi = mid - 1;
   }
   const asf_unpack_desc_t u = d[lo];
-  const int el = threadIdx.x & 63, sl = threadIdx.x >> 6;
+  const int sl_log2 = u.ksplit <= 2 ? 0 : (u.ksplit < 32 ? 2 : 4);
+  const int SL = 1 << sl_log2, EL = 256 >> sl_log2;
+  const int chunk = u.ksplit < 32 ? ASF_UNPACK_CHUNK : ASF_UNPACK_CHUNK_DEEP;
+  const int el = threadIdx.x & (EL - 1), sl = threadIdx.x >> (8 - sl_log2);
   const int64_t E = (int64_t)u.O * u.taps * u.I;
-  const int64_t e0 = (b - u.chunk0) * ASF_UNPACK_CHUNK;
+  const int64_t e0 = (b - u.chunk0) * chunk;
+  const int passes = chunk / (EL * 4);
 #pragma unroll 1
-  for (int pass = 0; pass < ASF_UNPACK_CHUNK / 256; ++pass) {
-    const int64_t e = e0 + pass * 256 + el * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f), w = v;
+  for (int pass = 0; pass < passes; ++pass) {
+    const int64_t e = e0 + (int64_t)pass * EL * 4 + el * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (e < E) {
       const float* src = u.dwp + e;
       int k = sl;
-      for (; k + 4 < u.ksplit; k += 8) {
-        const float4 a = *(const float4*)(src + (int64_t)k * E);
-        const float4 c = *(const float4*)(src + (int64_t)(k + 4) * E);
-        v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
-        w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w;
+      for (; k + 3 * SL < u.ksplit; k += 4 * SL) {
+        const float4 a0 = *(const float4*)(src + (int64_t)k * E);
+        const float4 a1 = *(const float4*)(src + (int64_t)(k + SL) * E);
+        const float4 a2 = *(const float4*)(src + (int64_t)(k + 2 * SL) * E);
+        const float4 a3 = *(const float4*)(src + (int64_t)(k + 3 * SL) * E);
+        v.x = (((v.x + a0.x) + a1.x) + a2.x) + a3.x;
+        v.y = (((v.y + a0.y) + a1.y) + a2.y) + a3.y;
+        v.z = (((v.z + a0.z) + a1.z) + a2.z) + a3.z;
+        v.w = (((v.w + a0.w) + a1.w) + a2.w) + a3.w;
       }
-      if (k < u.ksplit) {
-        const float4 a = *(const float4*)(src + (int64_t)k * E);
-        v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+      for (; k < u.ksplit; k += SL) {
+        const float4 a0 = *(const float4*)(src + (int64_t)k * E);
+        v.x += a0.x; v.y += a0.y; v.z += a0.z; v.w += a0.w;
       }
-      v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
     }
-    if (pass) __syncthreads();  // the previous pass has finished reading `part`
-    part[threadIdx.x] = v;
-    __syncthreads();
+    if (SL > 1) {
+      if (pass) __syncthreads();  // the previous pass has finished reading `part`
+      part[threadIdx.x] = v;
+      __syncthreads();
+    }
     if (sl == 0 && e < E) {
       float r[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-      for (int j = 1; j < 4; ++j) {
-        const float4 q = part[j * 64 + el];
+      for (int j = 1; j < SL; ++j) {
+        const float4 q = part[j * EL + el];
         r[0] += q.x; r[1] += q.y; r[2] += q.z; r[3] += q.w;
       }
       const int c = (int)(e % u.I);  // I % 4 == 0: the four elements share (o, tap)
@@ -695,11 +707,20 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const asf_unpac
       const int tp = (int)(ot % u.taps), o = (int)(ot / u.taps);
       const float sc = u.rscale ? u.rscale[o] : 1.f;
       float* dst = u.dw + ((int64_t)o * u.I + c) * u.taps + tp;
+      if (u.taps == 1 && (((uintptr_t)u.dw) & 15) == 0) {  // OIHW with one tap is the packed order: one 16-byte store
+        float4 x = make_float4(r[0] * sc, r[1] * sc, r[2] * sc, r[3] * sc);
+        if (u.accumulate) {
+          const float4 y = *(const float4*)dst;
+          x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+        }
+        *(float4*)dst = x;
+      } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float x = r[j] * sc;
-        if (u.accumulate) x += dst[(int64_t)j * u.taps];
-        dst[(int64_t)j * u.taps] = x;
+        for (int j = 0; j < 4; ++j) {
+          float x = r[j] * sc;
+          if (u.accumulate) x += dst[(int64_t)j * u.taps];
+          dst[(int64_t)j * u.taps] = x;
+        }
       }
     }
   }

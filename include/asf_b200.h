@@ -299,8 +299,8 @@ int asf_sgd_multi(const asf_sgd_desc_t* descs_dev, int n, long long total_chunks
 int asf_unpack_wgrad(const float* dwp, float* dw_oihw, int O, int I, int taps, const float* rscale,
                      int accumulate, int ksplit, void* stream);
 /* The same for many layers in one launch.  descs_dev: DEVICE array of n descriptors sorted by chunk0, where unit i owns
- * the blocks [chunk0_i, chunk0_{i+1}) of ASF_UNPACK_CHUNK destination elements each (chunks_i = ceil(O*I*taps /
- * ASF_UNPACK_CHUNK)); I % 4 == 0 and dwp 16-byte aligned. */
+ * the blocks [chunk0_i, chunk0_{i+1}) of C_i destination elements each, C_i = ASF_UNPACK_CHUNK for ksplit < 32 and
+ * ASF_UNPACK_CHUNK_DEEP from 32 on (chunks_i = ceil(O*I*taps / C_i)); I % 4 == 0, dw and dwp 16-byte aligned. */
 typedef struct {
   const float* dwp;    /* [ksplit][O][taps][I] partial tiles */
   float* dw;           /* OIHW fp32 gradient */
@@ -309,6 +309,7 @@ typedef struct {
   int64_t chunk0;
 } asf_unpack_desc_t;
 #define ASF_UNPACK_CHUNK 1024
+#define ASF_UNPACK_CHUNK_DEEP 256
 int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long total_chunks, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
