@@ -144,6 +144,24 @@ def _pow2_box(first):
     return (first, 128 // first, 1)
 
 
+def _time_box(F, T, B):
+    """128-row tile of a temporal conv's (F, T, B) position space: (F, t, b) with F * t * b = 128, powers of two,
+    chosen to minimise the number of tiles.  A tile must not wrap around a clip, so with the obvious (F, 128 / F, 1)
+    the T = 25 frames of the slow pathway fill 25 of 32 rows: 22 % of the tensor-core work of the largest layers
+    (the 3x1 convs are half of all FLOPs) went into padding.  (8, 1, 16) -- one frame of 16 clips -- covers
+    64 x 25 x 8 positions with exactly 100 tiles instead of 128."""
+    assert F <= 128 and (F & (F - 1)) == 0, "frequency extent %d must be a power of two <= 128" % F
+    best = None
+    t = 128 // F
+    while t >= 1:
+        b = 128 // (F * t)
+        tiles = -(-T // t) * -(-B // b)
+        if best is None or tiles < best[0]:
+            best = (tiles, (F, t, b))
+        t //= 2
+    return best[1]
+
+
 def _set_m(tg, ext, box, m_to_a):
     for j in range(3):
         tg.m_ext[j], tg.m_box[j], tg.m_to_a[j] = ext[j], box[j], m_to_a[j]
@@ -172,7 +190,7 @@ def tg_forward_geometry(u, tg, x):
         return (1, 0, 0)
     if u.axis == "T" and s == 1:
         _set_a(tg, x, [F, T, B], [ld, F * ld, T * F * ld])
-        _set_m(tg, (F, T, B), _pow2_box(F), (1, 2, 3))
+        _set_m(tg, (F, T, B), _time_box(F, T, B), (1, 2, 3))
         for i in range(k):
             tg.a_off[i][1] = i - p
         return (1, F, T * F)
@@ -180,7 +198,7 @@ def tg_forward_geometry(u, tg, x):
         assert T % s == 0 and u.y.T == T // s, "time-strided conv needs T divisible by the stride"
         To = T // s
         _set_a(tg, x, [F, s, To, B], [ld, F * ld, s * F * ld, T * F * ld])
-        _set_m(tg, (F, To, B), _pow2_box(F), (1, 3, 4))
+        _set_m(tg, (F, To, B), _time_box(F, To, B), (1, 3, 4))
         for i in range(k):
             q = i - p
             tg.a_off[i][1] = q % s
@@ -663,7 +681,7 @@ class Engine:
             elif u.axis == "T":
                 _set_a(tg, dy, [F, T, B], [ld, F * ld, T * F * ld])
                 Ti = dx.T
-                _set_m(tg, (F, Ti // s, B), _pow2_box(F), (1, 2, 3))
+                _set_m(tg, (F, Ti // s, B), _time_box(F, Ti // s, B), (1, 2, 3))
                 for i, (j, off) in enumerate(taps):
                     tg.a_off[i][1] = off
                 o_stride = (1, s * F, Ti * F)
