@@ -126,6 +126,7 @@ SIGNATURES = {
     "asf_logmel_fwd_tc": [_P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _P, _P, _P, _I, _P],
     "asf_specaug_params": [_P, _I, _I, _I, C.c_ulonglong, _P, _I, _I, _I, _I, _I, _P, _P],
     "asf_specaug_apply": [_P, _P, _P, _I, _I, _I, _P],
+    "asf_peer_allreduce_f64": [_P, _I, _P, _I, _I, C.c_longlong, C.c_longlong, _P, _P],
     "asf_gather_clips": [_P, _P, _P, _I, _I, _P, _L, _P, _P],
     "asf_topk_counts": [_P, _I, _L, _P, _P, _I, _L, _P, _I, _I, _I, _P, _P],
     "asf_ensemble_scatter": [_P, _I, _L, _P, _P, _I, _I, _I, _P, _P, _P, _P],

@@ -435,6 +435,35 @@ class Engine:
             o += Cn
         return plan
 
+    def _sync_sum(self, u, which, t):
+        """SyncBatchNorm: ``t`` (doubles) <- sum over the replicas.  Over NVLink peer memory (parallel.PeerExchange, one
+        single-CTA kernel, ~5 us) when the symmetric-memory rendezvous works on this system, otherwise the process
+        group's all-reduce (~20 us of latency per call; there are 220 of them per from-scratch step).
+        ASF_PEER_SYNCBN=0 forces the all-reduce."""
+        group, world = self.sync_bn
+        plan = self.plan
+        px = getattr(plan, "peer", None)
+        if px is None and not getattr(plan, "peer_failed", False):
+            if os.environ.get("ASF_PEER_SYNCBN", "1") == "0" or not self._plain_units_keys_ok():
+                plan.peer_failed = True
+            else:
+                try:
+                    from .parallel import PeerExchange
+                    layout = [((v.name, w), 2 * v.Cout) for v in plan.stems + plan.units for w in (0, 1)]
+                    px = plan.peer = PeerExchange(group, self.device, layout)
+                except Exception as e:  # no peer mapping on this system: keep the library collective
+                    plan.peer_failed = True
+                    if dist.get_rank(group) == 0:
+                        print("asf_b200: NVLink peer exchange unavailable (%s: %s); SyncBN statistics use all_reduce"
+                              % (type(e).__name__, str(e)[:120]))
+        if px is not None:
+            px.allreduce((u.name, which), t)
+        else:
+            dist.all_reduce(t, group=group)
+
+    def _plain_units_keys_ok(self):
+        return not torch.cuda.is_current_stream_capturing()  # the rendezvous is a collective setup: never inside a capture
+
     def _stat_bufs(self, u):
         """Workspace (per-CTA partial sums) and self-resetting tickets of a unit's statistics reductions; the forward
         statistics and the backward reduction of one unit are stream-ordered, so they share both."""
@@ -898,7 +927,7 @@ class Engine:
             # SyncBatchNorm forward: sum(x), sum(x^2) and the element count are summed over the replicas; mean, biased
             # variance and the unbiased running-variance update then follow from the global count
             group, world = self.sync_bn
-            dist.all_reduce(u.stats, group=group)
+            self._sync_sum(u, 0, u.stats)
             count *= world
         # statistics -> scale / shift / saved mean, invstd / running stats, and the normalise(+res)(+ReLU) pass: one launch
         L.call("asf_bn_train_fwd", C.c_void_p(raw.ptr), raw.ld, C.c_void_p(res.ptr) if res is not None else None,
@@ -1034,7 +1063,7 @@ class Engine:
                 # per-rank sums (the gradient all-reduce averages them like every other parameter gradient)
                 group, world = self.sync_bn
                 u.red_local.copy_(u.red)
-                dist.all_reduce(u.red, group=group)
+                self._sync_sum(u, 1, u.red)
                 count *= world
                 pg_w = pg_b = None
             L.call("asf_bn_bwd_apply", C.c_void_p(dz.ptr), dz.ld, C.c_void_p(u.raw.ptr), u.raw.ld,

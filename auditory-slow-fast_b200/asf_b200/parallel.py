@@ -79,6 +79,48 @@ class GradBucketer:
             self.pending = []
 
 
+class PeerExchange:
+    """Sum-over-ranks of small double vectors through NVLink peer memory (``asf_peer_allreduce_f64``, csrc/peer.cu):
+    the SyncBatchNorm statistics of every train-mode BatchNorm layer, forward and backward.  One symmetric buffer per
+    rank (torch.distributed._symmetric_memory) holds, for every exchange key, two slots of n doubles and ``world``
+    flags; the kernel publishes, signals the peers, waits for their signals and adds the ranks in rank order.
+    Construction is collective (every rank, same keys, same order)."""
+
+    def __init__(self, group, device, layout):
+        import torch.distributed._symmetric_memory as symm
+
+        from . import _lib as L
+
+        self.L = L
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.where = {}
+        off = 0
+        for key, n in layout:
+            slot = off
+            off += 2 * n * 8
+            flag = off
+            off += (self.world * 4 + 7) // 8 * 8
+            self.where[key] = (len(self.where), n, slot, flag)
+        self.buf = symm.empty(off, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.handle = symm.rendezvous(self.buf, self.group)
+        self.ptrs = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)
+        self.epochs = torch.zeros(len(self.where), dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)  # every rank's buffer is zeroed before anybody signals into it
+
+    def allreduce(self, key, t):
+        i, n, slot, flag = self.where[key]
+        if t.numel() != n or t.dtype != torch.float64:
+            raise ValueError("PeerExchange: %r expects %d doubles" % (key, n))
+        L = self.L
+        L.call("asf_peer_allreduce_f64", L.ptr(t), n, L.ptr(self.ptrs), self.rank, self.world, slot, flag,
+               L.ptr(self.epochs[i:i + 1]), L.stream_ptr())
+
+
 class DataParallel(nn.Module):
     """``DataParallel(model)``: data-parallel replica of an asf_b200 engine model (one process per GPU)."""
 

@@ -46,9 +46,11 @@ def cat_batches():
     return x, lab
 
 
-for freeze, sync in ((True, False), (True, True), (False, False), (False, True)):
+for freeze, sync, dtype in ((True, False, "bfloat16"), (True, True, "bfloat16"), (False, False, "bfloat16"),
+                            (False, True, "bfloat16"), (False, True, "float32"), (True, True, "float32")):
     cfg = epic_slowfast_cfg((97, 300), freeze)
     cfg.BN.FREEZE = freeze
+    cfg.B200.COMPUTE_DTYPE = dtype
     cfg.MODEL.DROPOUT_RATE = 0.0
     cfg.B200.SYNC_BN = sync
     cfg.NUM_GPUS = 1
@@ -88,7 +90,13 @@ for freeze, sync in ((True, False), (True, True), (False, False), (False, True))
     # frozen BN: deterministic up to bf16 rounding.  Training-mode BN at B = 4 from random init is chaotic (fp32 atomics of
     # the batch statistics reorder between runs; the same model twice on the same GPU differs by a few percent on the
     # stems), so there the bound is on the bulk of the tensors.
-    if freeze:
+    # bf16, training-mode BN: the two executions group the statistics differently (per-rank partial sums + all-reduce vs
+    # one reduction), a 1e-7 difference that flips bf16 roundings and ReLU masks downstream (sqrt(eps) amplification,
+    # tests/test_gpu_model.py): bounded on the bulk of the tensors.  The fp32 passes show the machinery itself is exact
+    # to fp32 rounding.
+    if dtype == "float32":
+        assert med < 1e-4 and worst < 2e-2, (med, errs[:5])
+    elif freeze:
         assert worst < 2e-2, errs[:5]
     else:
         assert med < 1e-2 and worst < 0.15, (med, errs[:5])
@@ -99,8 +107,8 @@ for freeze, sync in ((True, False), (True, True), (False, False), (False, True))
         assert serr < 2e-3, serr
         stat = "; running statistics vs the single-process global batch: worst rel err %.1e" % serr
     if rank == 0:
-        print("freeze=%s sync_bn=%s: %d gradient tensors vs %s: median rel err %.2e, worst %.2e (%s)%s"
-              % (freeze, sync, len(ref), "one process on the concatenated batch" if sync else
+        print("%s freeze=%s sync_bn=%s: %d gradient tensors vs %s: median rel err %.2e, worst %.2e (%s)%s"
+              % (dtype, freeze, sync, len(ref), "one process on the concatenated batch" if sync else
                  "the mean over %d ranks" % world, med, worst, errs[0][1], stat))
 dist.barrier()
 dist.destroy_process_group()
