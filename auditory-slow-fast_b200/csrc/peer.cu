@@ -40,7 +40,10 @@ __global__ void __launch_bounds__(256) peer_allreduce_f64_kernel(double* __restr
                                                                  const unsigned long long* __restrict__ peer_base, int rank,
                                                                  int world, long long slot_off, long long flag_off,
                                                                  unsigned* __restrict__ epoch) {
-  pdl_trigger();
+  // NO early trigger of the dependent launch: the next kernel of this stream (a few hundred CTAs of the normalise
+  // pass) would become resident and sit in its griddepcontrol.wait, holding registers and thread slots on every SM
+  // while this kernel waits for the other GPUs -- enough to keep the OTHER pathway's tcgen05 CTAs (a whole SM each)
+  // from being scheduled, i.e. to keep this rank from ever reaching the exchange its peer is waiting in.
   pdl_wait();
   const unsigned e = *epoch + 1u;
   const int parity = (int)(e & 1u);

@@ -31,6 +31,9 @@ import sys
 import threading
 import time
 
+# one hardware work queue per stream of the step (see asf_b200/__init__.py); must be set before the CUDA context exists
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (ROOT, os.path.join(ROOT, "auditory-slow-fast_b200")):
     if p not in sys.path:

@@ -6,6 +6,7 @@ the two-stream / weight-gradient-stream engine.
 import os
 import sys
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "auditory-slow-fast_b200")):
     sys.path.insert(0, p)
