@@ -60,8 +60,8 @@ def _peaks():
 
 def _ncu_traffic(kernel, bn_freeze):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu pass of one training
-    step (profiles/r01_dram_traffic.json, written by tools/ncu_traffic.py); None when no capture matches this workload."""
-    path = os.path.join(ROOT, "profiles", "r01_dram_traffic.json")
+    step (profiles/r02_dram_traffic.json, written by tools/ncu_traffic.py); None when no capture matches this workload."""
+    path = os.path.join(ROOT, "profiles", "r02_dram_traffic.json")
     if not os.path.exists(path) or bn_freeze is None:
         return None
     with open(path) as f:
@@ -333,11 +333,16 @@ def run_ours(args):
             sampler.start()
         n0 = L.lib().asf_launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        prof_range = sample_clocks and os.environ.get("ASF_PROFILER_RANGE") == "1"  # ncu --profile-from-start off
+        if prof_range:
+            torch.cuda.cudart().cudaProfilerStart()
         e0.record()
         for i in range(steps):
             fn(warmup + i)
         e1.record()
         torch.cuda.synchronize()
+        if prof_range:
+            torch.cuda.cudart().cudaProfilerStop()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()

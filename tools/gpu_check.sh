@@ -15,4 +15,6 @@ run kernels_simt 600 tests/test_gpu_kernels.py -k "not tapgemm"
 run model_fp32 900 tests/test_gpu_model.py -k "fp32 or float32"
 ASF_DEBUG_SYNC=1 run tapgemm 900 tests/test_gpu_kernels.py -k "tapgemm"
 run model_bf16 900 tests/test_gpu_model.py -k "not (fp32 or float32)"
+run specaug 600 tests/test_gpu_specaug.py
+run pipeline 600 tests/test_gpu_pipeline.py
 grep -h -E "FAILED|ERROR|passed|failed" gpurun_out/*.log | sort | uniq -c | sort -rn | head -60

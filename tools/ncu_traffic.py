@@ -1,5 +1,5 @@
 """Turns an `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --csv` launch list of one
-training step into profiles/r01_dram_traffic.json (per kernel: launches, DRAM bytes per launch, time per launch).
+training step into profiles/r02_dram_traffic.json (per kernel: launches, DRAM bytes per launch, time per launch).
     python tools/ncu_traffic.py <launches.csv> <bn_freeze 0|1> [out.json]"""
 import collections
 import csv
@@ -9,7 +9,7 @@ import sys
 
 src, freeze = sys.argv[1], int(sys.argv[2])
 out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                                                         "profiles", "r01_dram_traffic.json")
+                                                         "profiles", "r02_dram_traffic.json")
 rows = list(csv.reader(open(src)))
 hdr = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
 h = rows[hdr]
