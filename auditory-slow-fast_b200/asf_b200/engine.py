@@ -249,6 +249,12 @@ class Engine:
         # plan's buffers, so running another batch size (e.g. the partial last eval batch) must not release them
         self._plans = {}
         self.grad_hook = None        # callable(engine, names_done) used by the data-parallel wrapper
+        # callable(engine, lo, hi): elements [lo, hi) of the flat gradient buffer are FINAL (reduced over the ranks when
+        # data parallel) on the current stream -- the training step updates those parameters there, under the rest of
+        # the backward pass, instead of in one launch after it
+        self.update_hook = None
+        self.stage_hook = None       # callable(engine, unit_name) at every stage boundary of the backward pass
+        self._upd_done = 0
         self.force_simt = False      # debugging: run convs on the CUDA-core kernels even in bf16
         # (process_group, world_size) set by the data-parallel wrapper: train-mode BatchNorm then normalises with the
         # statistics of the GLOBAL batch, like the torch.nn.SyncBatchNorm the reference converts to when NUM_GPUS > 1
@@ -726,7 +732,7 @@ class Engine:
             for i, (j, off) in enumerate(taps):
                 tg.b_tap[i] = j
             tg.bw = u.w_pack_t.data_ptr()
-            tg.max_ctas = self._cap(u)
+            tg.max_ctas = self._cap(u) or int(os.environ.get("ASF_DGRAD_CTAS", "0"))
             tg.out, tg.out_dtype, tg.ld_out = dx.row_ptr(row_off), dx.code, dx.ld
             for j in range(3):
                 tg.o_stride[j] = o_stride[j]
@@ -1223,11 +1229,12 @@ class Engine:
         both pathway streams have been given so far.  The weight gradients live on the wgrad streams, so the deferred
         split-K reductions and the hook run on one of those after it has been ordered behind the other and behind the
         current stream -- nothing on the dz -> dgrad chain waits."""
+        if self.stage_hook is not None:
+            self.stage_hook(self, names[-1])
         if not self.wgrad_streams:
-            if self.grad_hook is not None:
-                self.grad_hook(self, names)
+            self._hooks(names)
             return
-        if self.grad_hook is None and not self._pending_unpack:
+        if self.grad_hook is None and self.update_hook is None and not self._pending_unpack:
             return
         cur = torch.cuda.current_stream(self.device)
         j = self._wg_stream(1)
@@ -1239,12 +1246,21 @@ class Engine:
                 j.wait_stream(wg)
         with torch.cuda.stream(j):
             self._flush_unpacks()
-            if self.grad_hook is not None:
-                self.grad_hook(self, names)
+            self._hooks(names)
 
     def _notify(self, names):
+        self._hooks(names)
+
+    def _hooks(self, names):
         if self.grad_hook is not None:
-            self.grad_hook(self, names)
+            self.grad_hook(self, names)  # data parallel: the bucketer forwards to update_hook once a range is reduced
+        elif self.update_hook is not None:
+            if names and names[0] == "head":
+                self._upd_done = 0
+            end = self._flat_grad.numel() if names and names[-1] == "stems" else self.grad_prefix_end(names)
+            if end > self._upd_done:
+                self.update_hook(self, self._upd_done, end)
+                self._upd_done = end
 
 
 class _NetFn(torch.autograd.Function):

@@ -37,6 +37,7 @@ class GradBucketer:
         self.pending = []
         self.buckets = []  # (start, end) of every bucket of the last pass, for tests / logging
         self.comm_stream = torch.cuda.Stream(device=flat.device) if flat.is_cuda else None
+        self.on_reduced = None  # callable(lo, hi), called on the communication stream right behind a bucket's all-reduce
         # gloo has no AVG: reduce with SUM and scale afterwards
         self.avg_op = dist.ReduceOp.AVG if flat.is_cuda else dist.ReduceOp.SUM
 
@@ -46,8 +47,12 @@ class GradBucketer:
         self.buckets = []
 
     def _launch(self, end):
-        if end <= self.launched or self.world == 1:
-            self.launched = max(self.launched, end)
+        if end <= self.launched:
+            return
+        if self.world == 1:
+            if self.on_reduced is not None:
+                self.on_reduced(self.launched, end)
+            self.launched = end
             return
         seg = self.flat[self.launched:end]
         self.buckets.append((self.launched, end))
@@ -57,6 +62,8 @@ class GradBucketer:
             with torch.cuda.stream(self.comm_stream):
                 self.comm_stream.wait_event(ev)
                 dist.all_reduce(seg, op=self.avg_op, group=self.group)
+                if self.on_reduced is not None:
+                    self.on_reduced(self.launched, end)
         else:
             w = dist.all_reduce(seg, op=self.avg_op, group=self.group, async_op=True)
             self.pending.append((w, seg))
@@ -155,6 +162,7 @@ class DataParallel(nn.Module):
         if self._bucketer is None or self._bucketer.flat is not flat:
             self._bucketer = GradBucketer(flat, self.process_group, self.bucket_bytes)
         b = self._bucketer
+        b.on_reduced = (lambda lo, hi: engine.update_hook(engine, lo, hi)) if engine.update_hook is not None else None
         if names and names[0] == "head":
             b.begin()
             self._done = 0

@@ -15,6 +15,8 @@ replay (asf_b200.optim.FusedSGD).  ``graph=False`` runs the same calls eagerly.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -32,10 +34,21 @@ def compute_loss(preds, labels):
 
 
 class TrainStep:
-    def __init__(self, cfg, model, optimizer, batch_size, n_samples, graph=True, warmup=3, augment=None):
+    def __init__(self, cfg, model, optimizer, batch_size, n_samples, graph=True, warmup=3, augment=None,
+                 pipeline=False, segmented_update=False):
         """``augment``: optional ``datasets.spec_augment.SpecAugmenter`` (the reference's training-time SpecAugment,
         datasets/epickitchens.py:160-168) applied on the device between extraction and the stems; its random numbers
-        come from a device-side counter, so every replay of the captured step augments differently."""
+        come from a device-side counter, so every replay of the captured step augments differently.
+
+        ``segmented_update`` (FusedSGD only): parameters are updated piece by piece from inside the backward pass, as
+        soon as a piece of the flat gradient buffer is final (and, data parallel, reduced), instead of by one launch
+        after it.  Same arithmetic per parameter, so the result is bit-identical.
+
+        ``pipeline``: the log-mel extraction (+ SpecAugment) of batch k+1 runs inside step k, beside the end of its
+        backward pass, the way the reference's DataLoader workers extract the next batches while the GPU trains
+        (datasets/epickitchens.py:160-170 runs in the workers).  Needs the ``prefetch()`` / ``step()`` protocol: the
+        batch after the one being trained must have been handed over before ``step()`` is called, otherwise that
+        step extracts its own batch up front (the first and the last step of a run)."""
         self.cfg, self.model, self.opt = cfg, model, optimizer
         net = model.module if hasattr(model, "module") else model
         dev = next(net.parameters()).device
@@ -49,27 +62,85 @@ class TrainStep:
             self.labels = torch.zeros(batch_size, dtype=torch.int64, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.augment = augment
+        self.pipeline = bool(pipeline)
+        self.segmented = bool(segmented_update) and hasattr(optimizer, "step_range")
+        self._x_cur = self._x_next = None
+        self._x_next_holds = None   # id of the staged batch whose spectrogram is in _x_next
+        self._batch_ids = 0
         self.graph = None
         self._want_graph = graph
         self._warmup = warmup
         self._calls = 0
 
+    def _extract(self):
+        return logmel_batch(self.cfg, self.wave, augment=self.augment)
+
+    def _extract_next(self):
+        """pipeline mode: spectrograms of the waveforms in ``self.wave`` -> the ``_x_next`` buffers (current stream)."""
+        x = self._extract()
+        if self._x_next is None:
+            self._x_next = [torch.empty_like(t) for t in x]
+            self._x_cur = [torch.empty_like(t) for t in x]
+        for dst, src in zip(self._x_next, x):
+            dst.copy_(src)
+
     def _body(self):
         net = self.model.module if hasattr(self.model, "module") else self.model
+        cur = torch.cuda.current_stream(self.device)
+        eng = getattr(net, "engine", None)
         fork = torch.cuda.Event()
-        fork.record(torch.cuda.current_stream(self.device))
-        x = logmel_batch(self.cfg, self.wave, augment=self.augment)
-        if hasattr(net, "engine"):
+        fork.record(cur)
+        late = None
+        if self.pipeline:
+            # this batch was extracted during the previous step (or up front by __call__)
+            for dst, src in zip(self._x_cur, self._x_next):
+                dst.copy_(src)
+            x = self._x_cur
+            taken = torch.cuda.Event()
+            taken.record(cur)
+            late = {"ev": None}
+            if eng is not None:
+                after = os.environ.get("ASF_EXTRACT_AFTER", "s2_fuse")
+
+                def stage_hook(engine, name, late=late, after=after):
+                    if name == after and late["ev"] is None:
+                        late["ev"] = torch.cuda.Event()
+                        late["ev"].record(torch.cuda.current_stream(self.device))
+                eng.stage_hook = stage_hook
+        else:
+            x = self._extract()
+        if eng is not None:
             # the optimiser step of the previous iteration left every packed weight copy stale: refresh them on a side
             # stream forked BEFORE the log-mel kernel but launched after it, so the HBM-bound re-layout runs beside the
             # tensor-core kernel (the forward joins that stream before its first launch)
-            net.engine.refresh_weights(net.training, after=fork)
+            eng.refresh_weights(net.training, after=fork)
         self.opt.zero_grad(set_to_none=True)
-        preds = self.model(x)
-        loss, _, _ = compute_loss(preds, self.labels)
-        loss.backward()
+        seg = self.segmented and eng is not None
+        if seg:
+            self.opt.begin_step(self.device)
+            eng.update_hook = lambda engine, lo, hi: self.opt.step_range(engine._flat_grad, lo, hi)
+        try:
+            preds = self.model(x)
+            loss, _, _ = compute_loss(preds, self.labels)
+            loss.backward()
+        finally:
+            if eng is not None:
+                eng.update_hook = None
+                eng.stage_hook = None
         self.opt.step()
         self.loss.copy_(loss.detach())
+        if self.pipeline:
+            # the next batch's extraction: a branch of the step that starts once the backward pass has reached the
+            # chosen stage boundary (and the spectrogram buffers have been handed to this step) and joins at the end
+            if getattr(self, "_ext_stream", None) is None:
+                self._ext_stream = torch.cuda.Stream(device=self.device)
+            ext = self._ext_stream
+            ext.wait_event(taken)
+            if late["ev"] is not None:
+                ext.wait_event(late["ev"])
+            with torch.cuda.stream(ext):
+                self._extract_next()
+            cur.wait_stream(ext)
 
     def prefetch(self, waveforms, labels):
         """Starts the host->device copy of the NEXT batch (pinned host tensors) into a staging slot on a copy stream and
@@ -84,8 +155,11 @@ class TrainStep:
             self._stage_free = [None, None]
             self._stage_next = 0
             self._stage_pending = []
+        if len(self._stage_pending) >= 2:
+            raise RuntimeError("TrainStep.prefetch: both staging slots hold batches that have not been trained on yet")
         k = self._stage_next
         self._stage_next ^= 1
+        self._batch_ids += 1
         w, lab = self._stage[k]
         with torch.cuda.stream(self._copy_stream):
             if self._stage_free[k] is not None:
@@ -99,14 +173,46 @@ class TrainStep:
             ev = torch.cuda.Event()
             ev.record(self._copy_stream)
         self._stage_ready[k] = ev
-        self._stage_pending.append(k)
+        self._stage_pending.append((k, self._batch_ids))
 
     def _consume_prefetched(self):
-        k = self._stage_pending.pop(0)
+        k, _ = self._stage_pending.pop(0)
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(self._stage_ready[k])
         w, lab = self._stage[k]
         self.load(w, lab)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._stage_free[k] = ev
+
+    def _load_labels(self, labels):
+        if self.two_heads:
+            self.labels["verb"].copy_(labels["verb"], non_blocking=True)
+            self.labels["noun"].copy_(labels["noun"], non_blocking=True)
+        else:
+            self.labels.copy_(labels, non_blocking=True)
+
+    def _consume_pipelined(self):
+        """pipeline mode, before the step runs: labels of the batch to train on -> static buffers; its spectrogram is
+        in ``_x_next`` already unless nobody announced it in time (then: extract it now, on the current stream);
+        waveforms of the batch AFTER it (if announced) -> ``self.wave`` for the extraction branch of this step."""
+        if not getattr(self, "_stage_pending", None):
+            raise RuntimeError("TrainStep(pipeline=True): call prefetch(waveforms, labels) before step()")
+        cur = torch.cuda.current_stream(self.device)
+        k, bid = self._stage_pending.pop(0)
+        cur.wait_event(self._stage_ready[k])
+        w, lab = self._stage[k]
+        if self._x_next_holds != bid:
+            self.wave.copy_(w, non_blocking=True)
+            self._extract_next()
+        self._load_labels(lab)
+        if self._stage_pending:
+            k2, bid2 = self._stage_pending[0]
+            cur.wait_event(self._stage_ready[k2])
+            self.wave.copy_(self._stage[k2][0], non_blocking=True)
+            self._x_next_holds = bid2
+        else:
+            self._x_next_holds = None  # the extraction branch re-extracts stale waveforms; nobody reads the result
         ev = torch.cuda.Event()
         ev.record(cur)
         self._stage_free[k] = ev
@@ -160,6 +266,8 @@ class TrainStep:
         afterwards: the first replay is the first update, exactly one per batch like the reference's train_epoch
         (tools/train_net.py:472-493)."""
         snap = self._snapshot()
+        # pipeline mode: the warm-up runs overwrite the hand-over buffers with the NEXT batch's spectrograms
+        x_next = [t.clone() for t in self._x_next] if self.pipeline else None
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
@@ -168,6 +276,9 @@ class TrainStep:
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
         self._restore(snap)
+        if x_next is not None:
+            for dst, src in zip(self._x_next, x_next):
+                dst.copy_(src)
         net = self.model.module if hasattr(self.model, "module") else self.model
         if hasattr(net, "engine"):
             # constants (folded affine of the frozen BatchNorm layers) are derived once, here; only the re-pack of the
@@ -183,7 +294,11 @@ class TrainStep:
         self.graph = g
 
     def __call__(self, waveforms=None, labels=None):
-        if waveforms is not None:
+        if self.pipeline:
+            if waveforms is not None:
+                self.prefetch(waveforms, labels)
+            self._consume_pipelined()
+        elif waveforms is not None:
             self.load(waveforms, labels)
         elif getattr(self, "_stage_pending", None):
             self._consume_prefetched()

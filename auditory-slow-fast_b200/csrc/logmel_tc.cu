@@ -489,6 +489,13 @@ int asf_logmel_fwd_tc(const float* wave, int64_t wave_ld, int B, int n_samples, 
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  {
+    // ASF_LOGMEL_CTAS: SM budget of the extraction when it runs as a side branch of the training step
+    // (TrainStep(pipeline=True)): a full-chip persistent launch holds every SM for its whole duration
+    const char* e = getenv("ASF_LOGMEL_CTAS");
+    const int cap = e ? atoi(e) : 0;
+    if (cap > 0 && cap < sms) sms = cap;
+  }
   const int grid = (int)(n_tiles < sms ? n_tiles : sms);
   unsigned long long* probe = nullptr;
   if (lt_dbg() & 32) {  // ASF_LOGMEL_DBG bit 5: print the stall counters of this launch (synchronises)

@@ -437,6 +437,61 @@ def test_train_step_graph_replay_matches_eager():
     assert int(finals[True][0]["s1.pathway0_stem.bn.num_batches_tracked"]) == 5
 
 
+@pytest.mark.parametrize("freeze", [True, False], ids=["bn_frozen", "bn_train"])
+def test_pipelined_segmented_step_is_bit_identical(freeze):
+    """TrainStep(pipeline=True, segmented_update=True) -- the extraction of batch k+1 inside step k, parameters updated
+    piecewise from inside the backward pass -- is the SAME computation as the plain step (extract, train, one optimiser
+    launch): identical losses over six iterations and identical parameters / momentum / BN statistics afterwards, with
+    the prefetch protocol honoured (batch k+1 announced before step k), broken (nothing announced: the step extracts
+    its own batch up front) and with the direct step(waveforms, labels) form."""
+    from asf_b200.optim import FusedSGD
+    from asf_b200.train_step import TrainStep
+    from oracle import logmel_np as OL
+    B, N, steps = 4, 47975, 6
+    sd = _state("slowfast", (97, 300))
+    wav = [torch.from_numpy(OL.synthetic_waveforms(B, N, 150 + i)).cuda() for i in range(3)]
+    ocfg = M.epic_cfg(dropout=0.0)
+    labels = [{k: v.cuda() for k, v in M.synthetic_labels(ocfg, B, seed=160 + i).items()} for i in range(3)]
+    losses, finals = {}, {}
+    for mode in ("plain", "pipelined", "pipelined-eager", "segmented-only"):
+        cfg, model = _build("slowfast", (97, 300), "bfloat16", freeze)
+        model.load_state_dict(sd)
+        model.train()
+        if freeze:
+            model.freeze_fn("bn_parameters")
+            model.freeze_fn("bn_statistics")
+        bn = [p for n, p in model.named_parameters() if "bn" in n and p.requires_grad]
+        other = [p for n, p in model.named_parameters() if "bn" not in n and p.requires_grad]
+        opt = FusedSGD([{"params": bn, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}], lr=0.01,
+                       momentum=0.9, nesterov=True)
+        step = TrainStep(cfg, model, opt, B, N, graph=mode != "pipelined-eager", warmup=3,
+                         pipeline=mode.startswith("pipelined"), segmented_update=mode != "plain")
+        out, pend = [], 0
+        batch = lambda i: (wav[i % 3], labels[i % 3])
+        for it in range(steps):
+            if not mode.startswith("pipelined") or it == 5:   # it == 5: direct form with nothing pending
+                out.append(float(step(*batch(it))))
+                continue
+            if pend == 0:                # nobody announced this batch: the step extracts it up front (it = 0, 3)
+                step.prefetch(*batch(it))
+                pend += 1
+            if it in (0, 1, 3):          # the next batch announced in time: extracted inside this step
+                step.prefetch(*batch(it + 1))
+                pend += 1
+            out.append(float(step()))
+            pend -= 1
+        losses[mode] = out
+        torch.cuda.synchronize()
+        finals[mode] = ({k: v.detach().clone() for k, v in model.state_dict().items()},
+                        [opt.state[p]["momentum_buffer"].clone() for p in bn + other])
+    print("\n[pipelined step]", {k: ["%.5f" % l for l in v] for k, v in losses.items()})
+    for mode in ("pipelined", "pipelined-eager", "segmented-only"):
+        assert losses[mode] == losses["plain"], (mode, losses[mode], losses["plain"])
+        bad = [k for k in finals["plain"][0] if not torch.equal(finals["plain"][0][k], finals[mode][0][k])]
+        assert not bad, "%s: state differs from the plain step: %s" % (mode, bad[:5])
+        assert all(torch.equal(a, b) for a, b in zip(finals["plain"][1], finals[mode][1]))
+
+
 def test_fused_sgd_reaches_next_forward():
     """One optimiser step with a large learning rate must change the next forward's output by what the updated fp32
     master weights give: the engine's packed bf16 copies are refreshed after FusedSGD.step() (eager and captured)."""
