@@ -89,8 +89,9 @@ class GradBucketer:
 class PeerExchange:
     """Sum-over-ranks of small double vectors through NVLink peer memory (``asf_peer_allreduce_f64``, csrc/peer.cu):
     the SyncBatchNorm statistics of every train-mode BatchNorm layer, forward and backward.  One symmetric buffer per
-    rank (torch.distributed._symmetric_memory) holds, for every exchange key, two slots of n doubles and ``world``
-    flags; the kernel publishes, signals the peers, waits for their signals and adds the ranks in rank order.
+    rank (torch.distributed._symmetric_memory) holds, for every exchange key, 2 (epoch parity) x ``world`` slots of n
+    doubles and ``world`` flags; the kernel pushes its values into its slot of every rank's buffer, signals the peers,
+    waits for their signals and adds the slots of its own buffer in rank order.
     Construction is collective (every rank, same keys, same order)."""
 
     def __init__(self, group, device, layout):
@@ -106,9 +107,9 @@ class PeerExchange:
         off = 0
         for key, n in layout:
             slot = off
-            off += 2 * n * 8
+            off += 2 * self.world * n * 8
             flag = off
-            off += (self.world * 4 + 7) // 8 * 8
+            off += (self.world * 4 + 15) // 16 * 16
             self.where[key] = (len(self.where), n, slot, flag)
         self.buf = symm.empty(off, dtype=torch.uint8, device=device)
         self.buf.zero_()

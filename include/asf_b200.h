@@ -420,8 +420,9 @@ int asf_ensemble_reduce(const float* clips, int C, int num_views, int num_videos
  * torch.nn.SyncBatchNorm issues per layer and pass (the reference converts to it at models/build.py:45-46).
  *   data[0..n) (doubles, this rank's sums) <- sum over ranks, added in rank order (bit-identical on every rank).
  * peer_base_dev: DEVICE array of `world` addresses, the base of every rank's symmetric buffer as mapped into THIS
- * process; slot_off_bytes: offset of this exchange's 2 x n doubles, flag_off_bytes: offset of its `world` uint32 flags
- * (both inside the symmetric buffer, zero-initialised, the same on every rank); epoch: local device counter of this
+ * process; slot_off_bytes: offset (16-byte aligned) of this exchange's 2 x world x n doubles (every rank pushes its n
+ * values, n even, into slot [epoch parity][its rank] of every rank's buffer), flag_off_bytes: offset of its `world` uint32
+ * flags (both inside the symmetric buffer, zero-initialised, the same on every rank); epoch: local device counter of this
  * exchange, zero-initialised.  Every rank must call it the same number of times, stream-ordered per exchange.
  * ---------------------------------------------------------------------------------------------- */
 int asf_peer_allreduce_f64(double* data, int n, const unsigned long long* peer_base_dev, int rank, int world,
