@@ -158,6 +158,10 @@ SIGNATURES = {
     "asf_sgemm": [_P, _P, _P, _I, _I, _I, _I, _I, _L, _L, _L, _F, _F, _P, _P],
     "asf_softmax_rows": [_P, _I, _I, _L, _P],
     "asf_scale_mask": [_P, _P, _P, _L, _F, _P],
+    "asf_dropout_apply": [_P, _P, _P, _P, _L, _F, _P],
+    "asf_head_fwd": [_P, _L, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "asf_softmax_ce": [_I, _P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P],
+    "asf_head_bwd": [_I, _P, _P, _P, _P, _P, _L, _P, _F, _I, _I, _P, _P, _P, _P, _P, _L, _P],
     "asf_gather_rows": [_P, _P, _P, _I, _I, _I, _I, _P],
     "asf_stem_wgrad": [_P, _P, _I, _P, C.POINTER(ConvGeom), _P],
 }
@@ -215,6 +219,19 @@ def dtype_code(dt):
 
 def ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def ptr_array(tensors):
+    """HOST array of device pointers (NULL for None) for the per-head arguments of the asf_head_* entry points."""
+    return (C.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+
+
+def int_array(vals):
+    return (C.c_int * len(vals))(*[int(v) for v in vals])
+
+
+def i64_array(vals):
+    return (C.c_int64 * len(vals))(*[int(v) for v in vals])
 
 
 def stream_ptr():

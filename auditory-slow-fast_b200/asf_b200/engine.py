@@ -1032,18 +1032,24 @@ class Engine:
         plan.drop_mask = None
         if training and head.dropout_rate > 0.0:
             keep = 1.0 - head.dropout_rate
-            plan.drop_mask = (torch.rand_like(plan.feat) < keep).float()
-            L.call("asf_scale_mask", L.ptr(plan.feat), L.ptr(plan.drop_mask), L.ptr(plan.feat_drop), plan.feat.numel(),
-                   C.c_float(1.0 / keep), st)
+            if getattr(plan, "drop_mask_buf", None) is None:
+                plan.drop_mask_buf = torch.empty_like(plan.feat)
+            plan.drop_mask = plan.drop_mask_buf
+            draws = torch.rand_like(plan.feat)
+            L.call("asf_dropout_apply", L.ptr(plan.feat), L.ptr(draws), L.ptr(plan.feat_drop),
+                   L.ptr(plan.drop_mask), plan.feat.numel(), C.c_float(keep), st)
             feat = plan.feat_drop
         plan.feat_used = feat
-        outs = []
-        for pr, lg in zip(plan.projs, plan.logits):
-            L.call("asf_sgemm", L.ptr(feat), L.ptr(pr.weight), L.ptr(lg), plan.B, pr.out_features, pr.in_features, 0, 1,
-                   feat.shape[1], pr.in_features, pr.out_features, C.c_float(1.0), C.c_float(0.0), L.ptr(pr.bias), st)
-            if not training:
+        # every task head in ONE launch, straight into fresh output tensors (csrc/head.cu)
+        projs = plan.projs
+        outs = [torch.empty((plan.B, pr.out_features), dtype=torch.float32, device=self.device) for pr in projs]
+        L.call("asf_head_fwd", L.ptr(feat), feat.shape[1], plan.B, projs[0].in_features, len(projs),
+               L.ptr_array([pr.weight for pr in projs]), L.ptr_array([pr.bias for pr in projs]),
+               L.int_array([pr.out_features for pr in projs]), L.ptr_array(outs),
+               L.i64_array([pr.out_features for pr in projs]), st)
+        if not training:
+            for pr, lg in zip(projs, outs):
                 L.call("asf_softmax_rows", L.ptr(lg), plan.B, pr.out_features, pr.out_features, st)
-            outs.append(lg.clone())
         return outs
 
     # ------------------------------------------------------------------------------------------ backward
@@ -1107,31 +1113,26 @@ class Engine:
         st = L.stream_ptr()
         B = plan.B
         self._pending_unpack = []
-        # ---- head
-        plan.dfeat.zero_()
+        # ---- head: dW, db of every task head and d feat (dropout mask applied) in one launch (csrc/head.cu)
         feat = plan.feat_used
-        for pr, dl in zip(plan.projs, dlogits):
-            if dl is None:
-                continue
-            dl = dl.contiguous().float()
-            gw, acc = self._grad_target(pr.weight)
-            if gw is not None:  # dW[j][c] = sum_b dl[b][j] feat[b][c]
-                L.call("asf_sgemm", L.ptr(dl), L.ptr(feat), L.ptr(gw), pr.out_features, pr.in_features, B, 1, 0,
-                       pr.out_features, feat.shape[1], pr.in_features, C.c_float(1.0), C.c_float(1.0 if acc else 0.0),
-                       None, st)
-            gb, accb = self._grad_target(pr.bias)
-            if gb is not None:
-                if accb:
-                    gb.add_(dl.sum(0))
-                else:
-                    gb.copy_(dl.sum(0))
-            # dfeat[b][c] += sum_j dl[b][j] W[j][c]
-            L.call("asf_sgemm", L.ptr(dl), L.ptr(pr.weight), L.ptr(plan.dfeat), B, pr.in_features, pr.out_features, 0, 0,
-                   pr.out_features, pr.in_features, pr.in_features, C.c_float(1.0), C.c_float(1.0), None, st)
-        if plan.drop_mask is not None:
-            keep = 1.0 - m.head.dropout_rate
-            L.call("asf_scale_mask", L.ptr(plan.dfeat), L.ptr(plan.drop_mask), L.ptr(plan.dfeat), plan.dfeat.numel(),
-                   C.c_float(1.0 / keep), st)
+        projs = plan.projs
+        live = [(pr, dl) for pr, dl in zip(projs, dlogits) if dl is not None]
+        if not live:
+            raise RuntimeError("asf_b200: backward called without a gradient for any head output")
+        dls = []
+        for pr, dl in live:
+            if dl.dtype != torch.float32 or dl.stride(-1) != 1:
+                dl = dl.contiguous().float()
+            dls.append(dl)
+        gws = [self._grad_target(pr.weight) for pr, _ in live]
+        gbs = [self._grad_target(pr.bias) for pr, _ in live]
+        keep = 1.0 - m.head.dropout_rate
+        L.call("asf_head_bwd", len(live), L.ptr_array(dls), L.i64_array([dl.stride(0) for dl in dls]),
+               L.int_array([pr.out_features for pr, _ in live]), L.ptr_array([pr.weight for pr, _ in live]),
+               L.ptr(feat), feat.shape[1], L.ptr(plan.drop_mask), C.c_float(1.0 / keep if plan.drop_mask is not None else 1.0),
+               B, projs[0].in_features, L.ptr_array([g for g, _ in gws]), L.int_array([a for _, a in gws]),
+               L.ptr_array([g for g, _ in gbs]), L.int_array([a for _, a in gbs]), L.ptr(plan.dfeat),
+               plan.dfeat.shape[1], st)
         self._notify(["head"])
         c_off = 0
         for xa in plan.final:

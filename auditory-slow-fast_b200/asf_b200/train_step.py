@@ -23,8 +23,64 @@ import torch.nn.functional as F
 from .datasets.audio_loader_epic import logmel_batch
 
 
+_CE_TICKETS = {}
+
+
+def _ce_ticket(device):
+    """Zero-initialised, self-resetting arrival counter of asf_softmax_ce (one per device and stream: launches that
+    share a ticket must be stream-ordered)."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _CE_TICKETS.get(key)
+    if t is None:
+        t = _CE_TICKETS[key] = torch.zeros(1, dtype=torch.int32, device=device)
+    return t
+
+
+class _FusedCE(torch.autograd.Function):
+    """Both cross-entropies, their mean and d loss / d logits in ONE launch (asf_softmax_ce, csrc/head.cu) instead of
+    the ~25 small launches of two F.cross_entropy calls and their autograd backward."""
+
+    @staticmethod
+    def forward(ctx, labels, *logits):
+        from . import _lib as L
+        heads, B = len(logits), logits[0].shape[0]
+        logits = [lg if lg.stride(-1) == 1 else lg.contiguous() for lg in logits]
+        loss = torch.empty((), dtype=torch.float32, device=logits[0].device)
+        parts = torch.empty(2, dtype=torch.float32, device=logits[0].device)
+        need = [ctx.needs_input_grad[1 + h] for h in range(heads)]
+        dl = [torch.empty_like(lg, memory_format=torch.contiguous_format) if n else None for lg, n in zip(logits, need)]
+        # (held in variables until the call has been issued: a temporary would be freed, and its block handed to the next
+        # allocation, while its address is still on its way into the launch)
+        scratch = torch.empty(heads * B, dtype=torch.float32, device=loss.device)
+        ticket = _ce_ticket(loss.device)
+        L.call("asf_softmax_ce", heads, L.ptr_array(logits), L.i64_array([lg.stride(0) for lg in logits]),
+               L.int_array([lg.shape[1] for lg in logits]), L.ptr_array(list(labels)), B, L.ptr(loss), L.ptr(parts),
+               L.ptr_array(dl),
+               L.i64_array([d.stride(0) if d is not None else 0 for d in dl]),
+               L.ptr(scratch), L.ptr(ticket), L.stream_ptr())
+        ctx.dl = dl
+        ctx.mark_non_differentiable(parts)
+        return loss, parts
+
+    @staticmethod
+    def backward(ctx, go, _):
+        return (None,) + tuple(None if d is None else d * go for d in ctx.dl)
+
+
+def _fusable(preds, labels):
+    ts = list(preds) if isinstance(preds, (tuple, list)) else [preds]
+    ls = [labels["verb"], labels["noun"]] if isinstance(preds, (tuple, list)) else [labels]
+    ok = all(t.is_cuda and t.dtype == torch.float32 and t.dim() == 2 for t in ts) and all(
+        l.is_cuda and l.dtype == torch.int64 and l.is_contiguous() for l in ls) and len(ts) <= 2
+    return ok, ts, ls
+
+
 def compute_loss(preds, labels):
     """tools/train_utils.py:76-101: two heads -> mean of the verb and noun CE; one head -> CE."""
+    ok, ts, ls = _fusable(preds, labels)
+    if ok:
+        loss, parts = _FusedCE.apply(tuple(ls), *ts)
+        return loss, parts[0], parts[1 if len(ts) > 1 else 0]
     if isinstance(preds, (tuple, list)):
         lv = F.cross_entropy(preds[0], labels["verb"])
         ln = F.cross_entropy(preds[1], labels["noun"])

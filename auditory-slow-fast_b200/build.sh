@@ -8,7 +8,7 @@ mkdir -p "$HERE/build"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -I"$HERE/../include" -I"$HERE/csrc")
 objs=()
 pids=()
-for f in elementwise elementwise_bf16 conv_simt logmel logmel_tc specaug evalmetrics staging peer tapgemm_sm100; do
+for f in elementwise elementwise_bf16 conv_simt logmel logmel_tc specaug evalmetrics staging peer head tapgemm_sm100; do
   src="$HERE/csrc/$f.cu"; obj="$HERE/build/$f.o"
   stale=0
   for dep in "$src" "$HERE"/csrc/*.cuh "$HERE/../include/asf_b200.h"; do

@@ -373,6 +373,27 @@ int asf_avgpool_fwd(const void* x, int dtype, int B, int P, int C, float* feat, 
 /* dx[b][p][c] = dfeat[b][c_off + c] / P, masked by (mask > 0) when mask != NULL */
 int asf_avgpool_bwd(const float* dfeat, int64_t ld_feat, int c_off, const void* mask, void* dx, int dtype, int B,
                     int P, int C, void* stream);
+/* ---- the classifier head and the loss in four launches (csrc/head.cu)
+ * Replaces ResNetBasicHead.forward (dropout + one nn.Linear per task, audio_slowfast/models/head_helper.py:70-109),
+ * compute_loss (tools/train_utils.py:76-101: F.cross_entropy per task, mean over tasks) and their backward passes.
+ * Arrays indexed by head are HOST arrays of `heads` (1 or 2) entries holding device pointers / sizes. */
+/* y = x * (u < keep) / keep, mask = (u < keep) as floats (u: uniform [0,1) draws, torch.rand_like) */
+int asf_dropout_apply(const float* x, const float* u, float* y, float* mask, int64_t n, float keep, void* stream);
+/* out[h][b][j] = sum_k feat[b][k] W[h][j][k] + bias[h][j]   (bias or bias[h] may be NULL) */
+int asf_head_fwd(const float* feat, int64_t ld_feat, int B, int K, int heads, const float* const* W,
+                 const float* const* bias, const int* N, float* const* out, const int64_t* ld_out, void* stream);
+/* loss_heads[h] = mean_b CE(logits[h][b], labels[h][b]), *loss = mean_h loss_heads[h];
+ * dl[h][b][j] = d loss / d logits[h][b][j] = (softmax_j - [j == label]) / (B * heads)  (dl or dl[h] may be NULL).
+ * row_scratch: heads * B floats; ticket: one zero-initialised uint32 (self-resetting; launches sharing it must be
+ * stream-ordered). */
+int asf_softmax_ce(int heads, const float* const* logits, const int64_t* ld, const int* N, const int64_t* const* labels,
+                   int B, float* loss, float* loss_heads, float* const* dl, const int64_t* ld_dl, float* row_scratch,
+                   unsigned* ticket, void* stream);
+/* dW[h][j][k] (+)= sum_b dl[h][b][j] feat[b][k];  db[h][j] (+)= sum_b dl[h][b][j];
+ * dfeat[b][k] = (mask ? mask[b][k] * inv_keep : 1) * sum_{h,j} dl[h][b][j] W[h][j][k]   (dW/db/dfeat entries may be NULL) */
+int asf_head_bwd(int heads, const float* const* dl, const int64_t* ld_dl, const int* N, const float* const* W,
+                 const float* feat, int64_t ld_feat, const float* mask, float inv_keep, int B, int K, float* const* dW,
+                 const int* acc_w, float* const* db, const int* acc_b, float* dfeat, int64_t ld_dfeat, void* stream);
 /* small fp32 GEMM on CUDA cores: C[M][N] = alpha * op(A) op(B) + beta*C (+ bias[n]); row-major, ta/tb transpose */
 int asf_sgemm(const float* A, const float* Bm, float* C, int M, int N, int K, int ta, int tb, int64_t lda,
               int64_t ldb, int64_t ldc, float alpha, float beta, const float* bias, void* stream);

@@ -280,3 +280,103 @@ def test_train_step_with_specaugment_in_the_graph():
     assert len(set(seen)) == 3, "every replay must draw fresh augmentation parameters"
     counter = list(aug._counter.values())[0]
     assert int(counter) >= 3
+
+
+# ---- the classifier head and the loss (csrc/head.cu) against torch ops
+@pytest.mark.parametrize("B,K,Ns", [(64, 2304, (97, 300)), (5, 2304, (309,)), (130, 2048, (97, 300)), (2, 96, (3, 5))])
+def test_head_forward_loss_backward_match_torch(B, K, Ns):
+    """asf_dropout_apply / asf_head_fwd / asf_softmax_ce / asf_head_bwd = dropout + nn.Linear per task +
+    F.cross_entropy per task, mean over tasks (head_helper.py:70-109, train_utils.py:76-101) and their autograd
+    gradients, for the EPIC (two tasks), VGG-Sound (one task) and ragged shapes, with and without accumulation."""
+    import ctypes as C
+    g = torch.Generator(device="cuda").manual_seed(B * 7 + K)
+    dev = "cuda"
+    feat = torch.randn(B, K, device=dev, generator=g)
+    u = torch.rand(B, K, device=dev, generator=g)
+    keep = 0.5
+    Ws = [torch.randn(n, K, device=dev, generator=g) * 0.05 for n in Ns]
+    bs = [torch.randn(n, device=dev, generator=g) for n in Ns]
+    labels = [torch.randint(0, n, (B,), device=dev, generator=g) for n in Ns]
+    st = L.stream_ptr()
+    # forward
+    y, mask = torch.empty_like(feat), torch.empty_like(feat)
+    L.call("asf_dropout_apply", L.ptr(feat), L.ptr(u), L.ptr(y), L.ptr(mask), feat.numel(), C.c_float(keep), st)
+    ref_mask = (u < keep).float()
+    assert torch.equal(mask, ref_mask) and torch.equal(y, feat * ref_mask * (1.0 / keep))
+    outs = [torch.empty(B, n, device=dev) for n in Ns]
+    L.call("asf_head_fwd", L.ptr(y), K, B, K, len(Ns), L.ptr_array(Ws), L.ptr_array(bs), L.int_array(Ns),
+           L.ptr_array(outs), L.i64_array(Ns), st)
+    # torch reference with autograd
+    f_ref = feat.clone().requires_grad_(True)
+    Wr = [w.clone().requires_grad_(True) for w in Ws]
+    br = [b.clone().requires_grad_(True) for b in bs]
+    yr = f_ref * ref_mask * (1.0 / keep)
+    lr = [F.linear(yr, w, b) for w, b in zip(Wr, br)]
+    for o, r in zip(outs, lr):
+        assert torch.allclose(o, r, rtol=1e-5, atol=1e-5 * float(r.abs().max())), float((o - r).abs().max())
+    ces = [F.cross_entropy(r, l) for r, l in zip(lr, labels)]
+    loss_ref = sum(ces) / len(ces)
+    loss_ref.backward()
+    # fused loss + gradient w.r.t. the logits (computed from OUR logits)
+    loss = torch.empty((), device=dev)
+    parts = torch.empty(2, device=dev)
+    dls = [torch.empty(B, n + 3, device=dev)[:, :n] for n in Ns]  # pitched rows
+    scratch, ticket = torch.empty(len(Ns) * B, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+    L.call("asf_softmax_ce", len(Ns), L.ptr_array(outs), L.i64_array(Ns), L.int_array(Ns), L.ptr_array(labels), B,
+           L.ptr(loss), L.ptr(parts), L.ptr_array(dls), L.i64_array([d.stride(0) for d in dls]),
+           L.ptr(scratch), L.ptr(ticket), st)
+    assert int(ticket) == 0  # self-resetting
+    assert abs(float(loss) - float(loss_ref)) <= 1e-5 * abs(float(loss_ref))
+    for h, ce in enumerate(ces):
+        assert abs(float(parts[h]) - float(ce)) <= 1e-5 * abs(float(ce))
+    # backward of the head: plain and accumulating into existing gradients
+    for acc in (0, 1):
+        dW = [torch.full_like(w, 0.25) for w in Ws]
+        db = [torch.full_like(b, -0.5) for b in bs]
+        dfeat = torch.full_like(feat, 7.0)
+        L.call("asf_head_bwd", len(Ns), L.ptr_array(dls), L.i64_array([d.stride(0) for d in dls]), L.int_array(Ns),
+               L.ptr_array(Ws), L.ptr(y), K, L.ptr(mask), C.c_float(1.0 / keep), B, K, L.ptr_array(dW),
+               L.int_array([acc] * len(Ns)), L.ptr_array(db), L.int_array([acc] * len(Ns)), L.ptr(dfeat), K, st)
+        torch.cuda.synchronize()
+        for h in range(len(Ns)):
+            rw, rb = Wr[h].grad + (0.25 if acc else 0.0), br[h].grad + (-0.5 if acc else 0.0)
+            assert float((dW[h] - rw).abs().max()) <= 2e-5 * float(Wr[h].grad.abs().max()) + 1e-7, (acc, h)
+            assert float((db[h] - rb).abs().max()) <= 2e-5 * float(br[h].grad.abs().max()) + 1e-7, (acc, h)
+        assert float((dfeat - f_ref.grad).abs().max()) <= 2e-5 * float(f_ref.grad.abs().max()) + 1e-9
+    # one head without a weight gradient (frozen parameter) and no dfeat
+    dW = [None] + [torch.zeros_like(w) for w in Ws[1:]]
+    L.call("asf_head_bwd", len(Ns), L.ptr_array(dls), L.i64_array([d.stride(0) for d in dls]), L.int_array(Ns),
+           L.ptr_array(Ws), L.ptr(y), K, None, C.c_float(1.0), B, K, L.ptr_array(dW), L.int_array([0] * len(Ns)),
+           L.ptr_array([None] * len(Ns)), L.int_array([0] * len(Ns)), None, 0, st)
+    torch.cuda.synchronize()
+
+
+def test_fused_cross_entropy_autograd_matches_torch():
+    """train_step.compute_loss on CUDA logits = tools/train_utils.py:76-101 (value, per-task values, gradients through
+    autograd, a scaled backward, and a head whose logits need no gradient)."""
+    from asf_b200.train_step import compute_loss
+    g = torch.Generator(device="cuda").manual_seed(5)
+    B = 16
+    lv = torch.randn(B, 97, device="cuda", generator=g, requires_grad=True)
+    ln = torch.randn(B, 300, device="cuda", generator=g, requires_grad=True)
+    labels = {"verb": torch.randint(0, 97, (B,), device="cuda", generator=g),
+              "noun": torch.randint(0, 300, (B,), device="cuda", generator=g)}
+    loss, cv, cn = compute_loss((lv, ln), labels)
+    (3.0 * loss).backward()
+    rv, rn = lv.detach().clone().requires_grad_(True), ln.detach().clone().requires_grad_(True)
+    rcv, rcn = F.cross_entropy(rv, labels["verb"]), F.cross_entropy(rn, labels["noun"])
+    rl = 0.5 * (rcv + rcn)
+    (3.0 * rl).backward()
+    assert abs(float(loss) - float(rl)) < 1e-5 and abs(float(cv) - float(rcv)) < 1e-5 and abs(float(cn) - float(rcn)) < 1e-5
+    assert torch.allclose(lv.grad, rv.grad, rtol=1e-5, atol=1e-7) and torch.allclose(ln.grad, rn.grad, rtol=1e-5, atol=1e-7)
+    # single task, logits that are a non-leaf expression, and a detached second call
+    x = torch.randn(B, 309, device="cuda", generator=g, requires_grad=True)
+    y = torch.randint(0, 309, (B,), device="cuda", generator=g)
+    l1, _, _ = compute_loss(x * 2.0, y)
+    l1.backward()
+    xr = x.detach().clone().requires_grad_(True)
+    F.cross_entropy(xr * 2.0, y).backward()
+    assert torch.allclose(x.grad, xr.grad, rtol=1e-5, atol=1e-7)
+    with torch.no_grad():
+        l2, _, _ = compute_loss(x, y)
+    assert abs(float(l2) - float(F.cross_entropy(x, y))) < 1e-5

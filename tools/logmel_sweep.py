@@ -10,11 +10,9 @@ from concurrent.futures import ProcessPoolExecutor
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "auditory-slow-fast_b200")):
     sys.path.insert(0, p)
-import numpy as np
-import torch
+import numpy as np  # noqa: F401
 
-from asf_b200.datasets.audio_loader_epic import logmel_cuda
-from oracle import logmel_np as OL
+from oracle import logmel_np as OL  # numpy only: the spawned host workers re-import this file, so no torch up here
 
 
 def _cpu_clip(args):
@@ -30,27 +28,53 @@ def cpu_rate(n, seconds, workers):
             _cpu_clip((n, k))
             k += 1
         return k / (time.perf_counter() - t0)
-    with ProcessPoolExecutor(workers) as ex:
-        list(ex.map(_cpu_clip, [(n, i) for i in range(workers)]))  # spin the pool up
-        k = max(workers * 2, int(workers * seconds * 10))
-        t0 = time.perf_counter()
-        list(ex.map(_cpu_clip, [(n, i) for i in range(k)], chunksize=max(1, k // (workers * 4))))
-        return k / (time.perf_counter() - t0)
+    # spawn, not fork (this process may hold a CUDA context and BLAS threads), one BLAS thread per worker
+    import multiprocessing as mp
+    saved = {k: os.environ.get(k) for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS")}
+    for k in saved:
+        os.environ[k] = "1"
+    try:
+        with ProcessPoolExecutor(workers, mp_context=mp.get_context("spawn")) as ex:
+            list(ex.map(_cpu_clip, [(n, i) for i in range(workers)]))  # spin the pool up
+            k = workers * 4
+            t0 = time.perf_counter()
+            list(ex.map(_cpu_clip, [(n, i) for i in range(k)], chunksize=1))
+            return k / (time.perf_counter() - t0)
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
 
 
 def main():
-    cpu_s = float(sys.argv[sys.argv.index("--cpu-seconds") + 1]) if "--cpu-seconds" in sys.argv else 2.0
+    import torch
+
+    from asf_b200.datasets.audio_loader_epic import logmel_cuda
+    cpu_s = float(sys.argv[sys.argv.index("--cpu-seconds") + 1]) if "--cpu-seconds" in sys.argv else 1.0
     cores = os.cpu_count() or 1
-    print("# log-mel extraction sweep (BASELINE configs[4]); GPU: %s; host cores: %d" % (torch.cuda.get_device_name(0), cores))
+    print("# log-mel extraction sweep (BASELINE configs[4]); GPU: %s; host cores: %d" % (
+        torch.cuda.get_device_name(0) if torch.cuda.is_available() else "none", cores))
     print("# N = round(24000 (d - 0.001)) - 1 samples -> T = 200 d frames x 128 mels; algorithmic bytes = 4 N + 4 T 128 per clip")
     print("%5s %6s %8s %6s | %12s %10s %9s | %12s %12s | %9s" % ("d_s", "B", "N", "T", "gpu_clips/s", "us/launch", "GB/s_alg",
                                                             "cpu1_clips/s", "cpuN_clips/s", "gpu/cpuN"))
+    durations = (1, 2, 4, 10)
+    lens = {d: int(round(24000 * (d - 0.001))) - 1 for d in durations}
+    # host rates first, before this process touches CUDA
+    t0 = time.perf_counter()
+    cpu1 = {d: cpu_rate(lens[d], cpu_s, 1) for d in durations}
+    cpun = {d: cpu_rate(lens[d], cpu_s, cores) for d in durations}
+    print("# host rates measured in %.0f s: 1 core %s, %d cores %s" % (
+        time.perf_counter() - t0, {d: round(v, 1) for d, v in cpu1.items()}, cores, {d: round(v, 1) for d, v in cpun.items()}),
+        flush=True)
+    if "--cpu-only" in sys.argv:
+        return
     g = torch.Generator(device="cuda").manual_seed(1234)
-    for d in (1, 2, 4, 10):
-        n = int(round(24000 * (d - 0.001))) - 1
+    for d in durations:
+        n = lens[d]
         T = 1 + n // 120
-        c1 = cpu_rate(n, cpu_s, 1)
-        cn = cpu_rate(n, cpu_s, cores)
+        c1, cn = cpu1[d], cpun[d]
         for B in (1, 16, 256, 1024, 4096):
             w = (0.1 * torch.randn(B, n, device="cuda", generator=g)).clamp_(-1, 1)
             out = logmel_cuda(w)
