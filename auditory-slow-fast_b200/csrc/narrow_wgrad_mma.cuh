@@ -204,7 +204,14 @@ __global__ void __maxnreg__(96) narrow_wgrad_mma_kernel(const __grid_constant__ 
 // positions per CTA and number of CTAs (= the ksplit the caller sizes the workspace for) of a narrow-layer launch
 static void narrow_wgrad_rows(const asf_tapgemm_t* q, int* ksplit, int* rows_per_cta) {
   const long long m_total = (long long)q->m_ext[0] * q->m_ext[1] * q->m_ext[2];
-  int ctas = 2 * sm_budget(q);
+  // CTAs per SM: every CTA leaves one partial copy of the layer's gradient for the split-K reduction to read
+  static int per_sm = -1;
+  if (per_sm < 0) {
+    const char* e = getenv("ASF_NWM_CTAS_PER_SM");
+    per_sm = e ? atoi(e) : 2;
+    if (per_sm < 1 || per_sm > 4) per_sm = 2;
+  }
+  int ctas = per_sm * sm_budget(q);
   long long rpc = (cdiv(m_total, ctas) + NW_ROWS - 1) / NW_ROWS * NW_ROWS;
   if (rpc < 4 * NW_ROWS) rpc = 4 * NW_ROWS;
   *rows_per_cta = (int)rpc;
