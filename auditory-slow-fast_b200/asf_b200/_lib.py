@@ -144,6 +144,7 @@ SIGNATURES = {
     "asf_unpack_wgrad_multi": [_P, _I, C.c_longlong, _P],
     "asf_tapgemm_wgrad_ksplit": [C.POINTER(TapGemm)],
     "asf_channel_stats": [_P, _I, _L, _I, _L, _P, _P, _P, _P],
+    "asf_channel_stats_noalloc": [_P, _I, _L, _I, _L, _P, _P],
     "asf_bn_finalize": [_P, _I, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "asf_bn_fold": [_P, _P, _P, _P, _F, _I, _P, _P, _P],
     "asf_bn_train_fwd": [_P, _L, _P, _L, _P, _L, _I, _L, _I, _P, _D, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P],

@@ -4,6 +4,8 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "stats_reduce.cuh"
 
@@ -811,6 +813,54 @@ int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld,
   ASF_DISPATCH_DTYPE(dtype, T, return (launch_channel_reduce<T, false>((const T*)x, ld, (const T*)nullptr, 0, rows, C,
                                                                       nullptr, nullptr, stats, ws, ticket,
                                                                       (cudaStream_t)stream)));
+}
+
+// ---- allocation-free variant (no counterpart in the reference) --------
+// The partial-sum workspace and the arrival tickets of the reduction live in file-scope device arrays, so a caller that
+// may not allocate (CUDA graph capture, serving loops) passes inputs and outputs only.  Every GPU that loads the library
+// holds these ASF_NOALLOC_SCRATCH_BYTES until exit.  In HOST code the array names below are stand-ins, not device
+// addresses: the device addresses are fetched once per device with cudaGetSymbolAddress and passed to the kernel.
+static __device__ __align__(256) float g_noalloc_ws[ASF_STATS_WS_FLOATS(ASF_NOALLOC_MAX_CHANNELS)];
+static __device__ __align__(256) uint32_t g_noalloc_ticket[ASF_STATS_TICKETS];
+static_assert(sizeof(float) * ASF_STATS_WS_FLOATS(ASF_NOALLOC_MAX_CHANNELS) + sizeof(uint32_t) * ASF_STATS_TICKETS ==
+                  ASF_NOALLOC_SCRATCH_BYTES, "ASF_NOALLOC_SCRATCH_BYTES in asf_b200.h is out of date");
+
+static int noalloc_scratch(float** ws, uint32_t** ticket) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static float* ws_of[MAX_DEV] = {};
+  static uint32_t* tk_of[MAX_DEV] = {};
+  int dev = 0;
+  ASF_CUDA(cudaGetDevice(&dev));
+  ASF_CHECK_ARG(dev >= 0 && dev < MAX_DEV, "asf_channel_stats_noalloc: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ws_of[dev]) {  // once per device, with that device current
+    float* w = nullptr;
+    uint32_t* t = nullptr;
+    ASF_CUDA(cudaGetSymbolAddress((void**)&w, g_noalloc_ws));
+    ASF_CUDA(cudaGetSymbolAddress((void**)&t, g_noalloc_ticket));
+    ASF_CHECK_ARG(w && t, "asf_channel_stats_noalloc: no device address for the scratch arrays");
+    ws_of[dev] = w;
+    tk_of[dev] = t;
+  }
+  *ws = ws_of[dev];
+  *ticket = tk_of[dev];
+  return 0;
+}
+
+int asf_channel_stats_noalloc(const void* x, int dtype, int64_t rows, int C, int64_t ld, double* stats, void* stream) {
+  ASF_CHECK_ARG(x && stats && rows > 0 && C > 0 && ld >= C, "asf_channel_stats_noalloc: bad arguments");
+  ASF_CHECK_ARG(C <= ASF_NOALLOC_MAX_CHANNELS,
+                "asf_channel_stats_noalloc: %d channels exceed the built-in scratch (ASF_NOALLOC_MAX_CHANNELS = %d); use "
+                "asf_channel_stats with a caller-owned workspace", C, ASF_NOALLOC_MAX_CHANNELS);
+  float* ws = nullptr;
+  uint32_t* ticket = nullptr;
+  int rc = noalloc_scratch(&ws, &ticket);
+  if (rc) return rc;
+  // The array keeps the previous call's contents.  The partial sums are all written before they are read; the tickets
+  // must start at zero (they reset themselves, but a call that was aborted mid-way would leave them counting).
+  ASF_CUDA(cudaMemsetAsync(ticket, 0, sizeof(uint32_t) * ASF_STATS_TICKETS, (cudaStream_t)stream));
+  return asf_channel_stats(x, dtype, rows, C, ld, stats, ws, ticket, stream);
 }
 
 int asf_bn_finalize(const double* stats, int C, double count, const float* gamma, const float* beta, float eps,

@@ -321,6 +321,17 @@ int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long 
  * CTA (`ticket`: ASF_STATS_TICKETS zero-initialised uint32, self-resetting).  See asf_epilogue_t. */
 int asf_channel_stats(const void* x, int dtype, int64_t rows, int C, int64_t ld, double* stats, float* ws,
                       uint32_t* ticket, void* stream);
+/* Allocation-free variant of asf_channel_stats.  No counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same result, bit for bit; the caller passes inputs and outputs only.  The
+ * reduction's workspace and tickets are file-scope device arrays inside the library (ASF_NOALLOC_SCRATCH_BYTES per GPU
+ * that loads it, held until exit), so C <= ASF_NOALLOC_MAX_CHANNELS; more channels are rejected with ASF_E_BADARG.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  EVERY call on a device shares
+ * the one scratch array: calls that overlap on the GPU (different streams, concurrent graph branches) race -- order
+ * them on one stream or with events. */
+#define ASF_NOALLOC_MAX_CHANNELS 256
+#define ASF_NOALLOC_SCRATCH_BYTES (4ll * ASF_STATS_WS_FLOATS(ASF_NOALLOC_MAX_CHANNELS) + 4ll * ASF_STATS_TICKETS)
+int asf_channel_stats_noalloc(const void* x, int dtype, int64_t rows, int C, int64_t ld, double* stats, void* stream);
 /* train-mode finalize: mean/var from stats over `count` rows (in double: var = E[x^2] - mean^2 is formed from the
  * double sums); scale = gamma*invstd, shift = beta - mean*scale;
  * running_mean/var momentum update (unbiased var) and num_batches_tracked += 1 when running_mean != NULL. */
