@@ -400,6 +400,32 @@ extern "C" int asf_tapgemm(const asf_tapgemm_t* q, int mode, void* stream) {
         // doubles the number of busy SMs, or when the operand slabs leave fewer than 3 ring stages
         while (bn > 64 && bn % 32 == 0 && (int64_t)p.m_tiles_total * cdiv(q->N, bn) * 2 <= sm_budget(q)) bn /= 2;
         while (bn > 64 && bn % 32 == 0 && (smem_cap - tma_fixed) / (TG_A_BYTES + bn * 128) < 3) bn /= 2;
+        {
+          // Wave quantisation (ASF_TG_WAVE = fixed cost of a tile in units of output columns, 0 = off): tiles are dealt
+          // round robin to the persistent CTAs, so a launch takes ceil(tiles / CTAs) rounds of (fixed + block_n); e.g.
+          // 200 tiles of 256 columns on 148 SMs are 2 rounds with the second a third full, 400 tiles of 128 are 3
+          // rounds of half the length.
+          static int wave = -1;
+          if (wave < 0) {
+            const char* e = getenv("ASF_TG_WAVE");
+            wave = e ? atoi(e) : 0;
+          }
+          if (wave > 0 && !q->epi.stats) {
+            int best = bn;
+            double best_cost = 1e30;
+            for (int c = bn; c >= 64 && c % 16 == 0; c /= 2) {
+              if ((smem_cap - tma_fixed) / (TG_A_BYTES + c * 128) < 3) continue;
+              const int64_t tiles = (int64_t)p.m_tiles_total * cdiv(q->N, c);
+              const double cost = (double)cdiv(tiles, sm_budget(q)) * (wave + c);
+              if (cost < best_cost * 0.97) {  // prefer the wider tile unless the narrower one is clearly ahead
+                best_cost = cost;
+                best = c;
+              }
+              if (c % 32) break;
+            }
+            bn = best;
+          }
+        }
       }
     }
     ASF_CHECK_ARG(bn >= 16 && bn <= 256 && bn % 16 == 0, "asf_tapgemm: block_n %d must be a multiple of 16 in [16,256]", bn);
