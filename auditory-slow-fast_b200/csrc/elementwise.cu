@@ -1,6 +1,7 @@
 // BatchNorm statistics / apply / backward, pools, head helpers, weight (re)packing.
 // All kernels are HBM-bound streaming passes: channel index is the fastest-varying thread index so every
-// warp touches contiguous addresses; reductions go warp/block-level first and finish with a few fp32 atomics.
+// warp touches contiguous addresses; reductions go warp/block-level first, every block stores its partial sums and
+// the last block to arrive adds them in a fixed order (stats_reduce.cuh): no floating-point atomics.
 #include <stdarg.h>
 #include <stdlib.h>
 

@@ -8,9 +8,12 @@
 //        epilogue of tile i overlaps the MMAs of tile i+1, S-stage smem ring (full/empty mbarriers).
 //        Convolution padding = TMA out-of-bounds zero fill; taps = coordinate offsets on the tensor map;
 //        stride-2 / stride-4 convs = a parity / phase dimension in the tensor map.  No im2col, no halo copies.
-//   mode 1 (wgrad): dW[n][tap][c] += sum_rows Y[row][n] * X[row+off(tap)][c]; both operands are read straight from
+//   mode 1 (wgrad): dW[n][tap][c] = sum_rows Y[row][n] * X[row+off(tap)][c]; both operands are read straight from
 //        the channels-last activations as MN-major UMMA operands (rows are the GEMM K), split over row tiles
-//        across CTAs and finished with fp32 atomics.
+//        across CTAs; every CTA STORES its partial tile into the layer's split-K workspace and asf_unpack_wgrad(_multi)
+//        adds the partials in a fixed order (no floating-point atomics anywhere: results are bit-reproducible).
+//   Narrow layers (<= 64 output channels) take the warp-MMA kernels of narrow_conv.cuh / narrow_wgrad_mma.cuh behind
+//   the same entry point.
 //
 // Replaces cuDNN conv fwd/dgrad/wgrad + the separate BN / ReLU / add / cat kernels behind
 //   /root/reference/audio_slowfast/models/resnet_helper.py:170-225, :310-341 and audio_model_builder.py:90-111.
