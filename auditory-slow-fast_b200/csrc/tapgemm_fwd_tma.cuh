@@ -318,9 +318,15 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     }
     int pf_it = -1, pf_s = 0, pf_s1 = 0, pf_n0 = 0;
     int pf_ob = 0;  // operand ring slot of the next prefetch
-    long long pf_row = 0;
-    bool pf_valid = false;
-    auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs; this thread's row in it
+    // The loads of a warp are laid out for the LSU, not for the consumer: lane l fetches 16-byte chunk (l & 3) of rows
+    // (l >> 2) + 8 i, i = 0..3, of the warp's 32 rows, so one instruction touches 8 rows x 64 contiguous bytes = 8 cache
+    // lines.  (Every thread fetching its OWN row made each instruction touch 32 lines for 16 bytes each; at one tag
+    // lookup per line and clock the two epilogue groups kept the LSU busy ~1 kcycle per slab and operand -- the whole
+    // difference between an epilogue with a residual and one without.)  The consumer of a row is another lane of the
+    // same warp: __syncwarp() after the wait, and the one that ends every slab iteration, order the hand-over.
+    int pf_rows[4] = {0, 0, 0, 0};  // output-row index of row (lane >> 2) + 8 i of this warp in the prefetch tile, -1 = outside
+    const int pf_c = lane & 3, pf_rl = quarter * 32 + (lane >> 2);
+    auto pf_seek = [&]() {  // next tile of this CTA in which this group has slabs; the warp's rows in it
       for (++pf_it; pf_it < n_it; ++pf_it) {
         const int tile_ = blockIdx.x + pf_it * gridDim.x;
         const int n0_ = (tile_ % p.n_tiles) * p.block_n;
@@ -329,8 +335,11 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
           int st_[3];
           tile_coords(p, tile_ / p.n_tiles, st_);
           const int m1 = st_[0] + r1, m2 = st_[1] + r2, m3 = st_[2] + r3;
-          pf_valid = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
-          pf_row = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
+          const bool ok = (m1 < p.m_ext[0]) && (m2 < p.m_ext[1]) && (m3 < p.m_ext[2]);
+          const long long row = (long long)m1 * p.o_stride[0] + (long long)m2 * p.o_stride[1] + (long long)m3 * p.o_stride[2];
+          const int mine = ok ? (int)row : -1;  // (row indices fit 31 bits: the launcher bounds the output space)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) pf_rows[i] = __shfl_sync(0xffffffffu, mine, (lane >> 2) + 8 * i);
           pf_n0 = n0_;
           return;
         }
@@ -340,13 +349,14 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
     auto prefetch_next = [&]() {
       if (pf_it < n_it) {
         const int nb = pf_n0 + pf_s * 32;
-        if (pf_valid) {
+        if (nb + 8 * pf_c + 8 <= p.N) {
           for (int o = 0; o < n_ops; ++o) {
-            const uint8_t* src = opsrc[o] + (pf_row * opld[o] + nb) * 2;
+            const uint8_t* src = opsrc[o] + ((long long)nb + 8 * pf_c) * 2;
             uint8_t* dst = op_buf + (o * OD + pf_ob) * EPI_SLAB_BYTES;
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
-              if (nb + 8 * c + 8 <= p.N) cp_async16(dst + slab_off(r, c), src + 16 * c);
+            for (int i = 0; i < 4; ++i)
+              if (pf_rows[i] >= 0)
+                cp_async16(dst + slab_off(pf_rl + 8 * i, pf_c), src + (long long)pf_rows[i] * opld[o] * 2);
           }
         }
         if (++pf_ob == OD) pf_ob = 0;
@@ -403,6 +413,7 @@ __global__ void __launch_bounds__(TGT_THREADS, 1) tapgemm_fwd_tma_kernel(const _
         }
         if (n_ops > 0) {
           if (OD == 2) cp_async_wait<1>(); else if (OD == 3) cp_async_wait<2>(); else cp_async_wait<3>();
+          __syncwarp();  // this thread's operand row was fetched by other lanes of the warp
         }
         if (STATS) {
           // two barriers ago every warp had stored slab gs - 2's partials into scratch half gs & 1; nobody writes that
