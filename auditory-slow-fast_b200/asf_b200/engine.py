@@ -631,7 +631,9 @@ class Engine:
 
     def _side_stream(self):
         if self._side is None:
-            self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("ASF_PATH_PRIO", "0")))
+            # ASF_SIDE_PRIO: priority of the fast pathway's stream alone (its backward chain is what the step ends on)
+            self._side = torch.cuda.Stream(device=self.device, priority=int(os.environ.get(
+                "ASF_SIDE_PRIO", os.environ.get("ASF_PATH_PRIO", "0"))))
         return self._side
 
     def _slow_stream(self):

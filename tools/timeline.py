@@ -33,7 +33,7 @@ bn_params = [p for n, p in model.named_parameters() if "bn" in n and p.requires_
 other = [p for n, p in model.named_parameters() if "bn" not in n and p.requires_grad]
 opt = FusedSGD([{"params": bn_params, "weight_decay": 0.0}, {"params": other, "weight_decay": 1e-4}], lr=0.01,
                momentum=0.9, nesterov=True)
-ts = TrainStep(cfg, model, opt, B, 47975, graph=True)
+ts = TrainStep(cfg, model, opt, B, 47975, graph=True, segmented_update=os.environ.get("ASF_TL_SEGMENTED") == "1")
 w = torch.from_numpy(OL.synthetic_waveforms(B, 47975, 1234)).cuda()
 g = torch.Generator().manual_seed(1)
 lab = {"verb": torch.randint(0, 97, (B,), generator=g).cuda(), "noun": torch.randint(0, 300, (B,), generator=g).cuda()}
