@@ -165,6 +165,7 @@ SIGNATURES = {
     "asf_head_bwd": [_I, _P, _P, _P, _P, _P, _L, _P, _F, _I, _I, _P, _P, _P, _P, _P, _L, _P],
     "asf_gather_rows": [_P, _P, _P, _I, _I, _I, _I, _P],
     "asf_stem_wgrad": [_P, _P, _I, _P, C.POINTER(ConvGeom), _P],
+    "asf_stem_wgrad_fused": [_P, _P, _I, _P, _P, _I, _P, C.POINTER(ConvGeom), _P],
 }
 
 
@@ -180,6 +181,8 @@ def _declare(l):
     # queries returning a count (>= 1) or a negative error code
     l.asf_stem_wgrad_ksplit.argtypes = [C.POINTER(ConvGeom), _I]
     l.asf_stem_wgrad_ksplit.restype = C.c_int
+    l.asf_stem_wgrad_fused_rows.argtypes = [C.POINTER(ConvGeom), _I]
+    l.asf_stem_wgrad_fused_rows.restype = C.c_int
     l.asf_conv_wgrad_simt_ksplit.argtypes = [C.POINTER(ConvGeom)]
     l.asf_conv_wgrad_simt_ksplit.restype = C.c_int
 

@@ -748,13 +748,28 @@ class Engine:
             g.ld_out = dy.ld
             if rscale is not None:
                 raise RuntimeError("stem BN is never folded in training")
+            n = u.Cout * u.taps
+            rows = getattr(u, "wgf_rows", None)
+            if rows is None:
+                rows = 0
+                if os.environ.get("ASF_STEM_FUSED", "1") != "0" and gview.is_contiguous() and gview.dtype == torch.float32:
+                    rows = L.lib().asf_stem_wgrad_fused_rows(C.byref(g), dy.code)
+                u.wgf_rows = rows
+                if rows > 0:
+                    u.wgf_ws = torch.empty(rows * n, dtype=torch.float32, device=self.device)
+                    u.wgf_ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
+            if rows > 0:
+                # input lines staged in shared memory, cross-block sum folded into the kernel: the last kernel of the
+                # backward pass is not followed by a reduction launch
+                L.call("asf_stem_wgrad_fused", C.c_void_p(u.x.ptr), C.c_void_p(dy.ptr), dy.code, L.ptr(u.wgf_ws), L.ptr(gview),
+                       int(bool(accumulate)), L.ptr(u.wgf_ticket), C.byref(g), st)
+                return
             ks = getattr(u, "wg_ksplit", None)
             if ks is None:
                 ks = L.lib().asf_stem_wgrad_ksplit(C.byref(g), dy.code)
                 if ks < 1:
                     raise RuntimeError("asf_stem_wgrad_ksplit failed (code %d): %s" % (ks, L.lib().asf_last_error().decode()))
                 u.wg_ksplit = ks
-            n = u.Cout * u.taps
             ws = getattr(u, "wg_ws", None)
             if ws is None or ws.numel() < ks * n:
                 ws = u.wg_ws = torch.empty(ks * n, dtype=torch.float32, device=self.device)

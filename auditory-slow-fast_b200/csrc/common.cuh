@@ -108,6 +108,9 @@ int bn_relu_maxpool_bwd_v8(const bf16* x, const bf16* dy, int64_t ld_dy, bf16* d
 int stem_conv_fwd_bf16(const float* in, const float* w, bf16* out, const asf_conv_geom_t* g, cudaStream_t st);
 int stem_wgrad_v9_blocks(const asf_conv_geom_t* g);
 int stem_wgrad_v9(const float* in, const bf16* dout, float* dwp, const asf_conv_geom_t* g, cudaStream_t st);
+int stem_wgrad_v10_rows(const asf_conv_geom_t* g);
+int stem_wgrad_v10(const float* in, const bf16* dout, float* dwp, float* dw, int accumulate, unsigned* ticket,
+                   const asf_conv_geom_t* g, cudaStream_t st);
 
 // dispatch on a dtype code
 #define ASF_DISPATCH_DTYPE(code, T, ...)                       \

@@ -1133,6 +1133,19 @@ int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dwp
   });
 }
 
+int asf_stem_wgrad_fused_rows(const asf_conv_geom_t* g, int dout_dtype) {
+  if (!g || g->Cin != 1 || g->kt * g->kf > STEM_MAX_TAPS || !stem_vec_ok(g, dout_dtype)) return 0;
+  return stem_wgrad_v10_rows(g);
+}
+
+int asf_stem_wgrad_fused(const float* in, const void* dout, int dout_dtype, float* dwp, float* dw, int accumulate,
+                         uint32_t* ticket, const asf_conv_geom_t* g, void* stream) {
+  ASF_CHECK_ARG(in && dout && dwp && dw && ticket && g, "asf_stem_wgrad_fused: null pointer");
+  ASF_CHECK_ARG(asf_stem_wgrad_fused_rows(g, dout_dtype) > 0 && al16(dout) && al16(dwp),
+                "asf_stem_wgrad_fused: shape / dtype / alignment not supported (see asf_stem_wgrad_fused_rows)");
+  return stem_wgrad_v10(in, (const bf16*)dout, dwp, dw, accumulate, ticket, g, (cudaStream_t)stream);
+}
+
 int asf_unpack_wgrad_multi(const asf_unpack_desc_t* descs_dev, int n, long long total_chunks, void* stream) {
   ASF_CHECK_ARG(descs_dev && n > 0 && total_chunks > 0 && total_chunks < (1ll << 31), "asf_unpack_wgrad_multi: bad arguments");
   // (every layer: I % 4 == 0 and 16-byte aligned dwp -- the tap-GEMM wgrad already requires I % 8 == 0)

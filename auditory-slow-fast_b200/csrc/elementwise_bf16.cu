@@ -804,6 +804,132 @@ __global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restr
   }
 }
 
+// Stem weight gradient, third layout ("v10"): the last kernel of the backward pass, i.e. the serial tail of the step.
+// v9 read the input straight from global memory (7 scalar loads + one 16-byte load per row and kernel row, two rows in
+// flight per lane: 9 % of the FMA rate, 74 us for the fast stem).  Here a block walks chunks of SW10_LC output lines of one
+// clip: the (SW10_LC - 1) * st + kt input lines a chunk touches are staged once in shared memory WITH their zero padding
+// (no bounds tests in the inner loop), every warp owns one (8-channel group, kernel row) pair and a share of the
+// chunk's lines for the whole launch -- its 8 x kf accumulators live in registers across chunks -- and the only global
+// load in the inner loop, the row's 16 bytes of dout, is fetched four iterations ahead; the next chunk's lines arrive
+// by cp.async into the other buffer while this chunk is being consumed (one barrier per chunk).
+// With dw != nullptr the cross-block sum is folded in: blocks store their partial rows, the block that draws the last
+// ticket adds them in block order (stats_reduce.cuh) and writes (or accumulates into) the gradient -- no separate
+// split-K reduction launch behind the last kernel of the step.  Bit-reproducible either way.
+constexpr int SW10_LC = 8;
+__global__ void __launch_bounds__(512) stem_wgrad_v10_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
+                                                             float* __restrict__ dwp, float* __restrict__ dw,
+                                                             int accumulate, unsigned* __restrict__ ticket,
+                                                             asf_conv_geom_t g, int nsl, int NL, int W, int cpc,
+                                                             int n_chunks) {
+  pdl_trigger();
+  pdl_wait();
+  extern __shared__ __align__(16) float s10[];  // staged input lines [NL][W]; later task slots, then reduction scratch
+  const int taps = g.kt * g.kf, CG = g.Cout / 8, ngroups = CG * g.kt;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int grp = warp % ngroups, sl = warp / ngroups;
+  const int cg = grp % CG, it = grp / CG;
+  const int lines_per_sl = SW10_LC / nsl;
+  const int fiters = (g.Fout + 31) >> 5;
+  const int nq = lines_per_sl * fiters;
+  float acc[8][STEM_KF_MAX];
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+#pragma unroll
+    for (int k = 0; k < STEM_KF_MAX; ++k) acc[j][k] = 0.f;
+  // staging of one chunk's input lines (with their zero padding) into buffer `buf`: 4-byte cp.async, zero-filled outside
+  auto stage = [&](int chunk, int buf) {
+    if (chunk < n_chunks) {
+      const int b = chunk / cpc, to0 = (chunk - b * cpc) * SW10_LC;
+      const int t0 = to0 * g.st - g.pt;
+      float* dstb = s10 + (size_t)buf * NL * W;
+      for (int l = warp; l < NL; l += nwarps) {
+        const int t = t0 + l;
+        const bool tv = t >= 0 && t < g.Tin;
+        const float* src = in + ((int64_t)b * g.Tin + (tv ? t : 0)) * g.Fin;
+        for (int i = lane; i < W; i += 32) {
+          const int f = i - g.pf;
+          const bool v = tv && f >= 0 && f < g.Fin;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(dstb + l * W + i)), "l"(src + (v ? f : 0)),
+                       "r"(v ? 4 : 0)
+                       : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  stage(blockIdx.x, 0);
+  int cbuf = 0;
+  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, cbuf ^= 1) {
+    const int b = chunk / cpc, to0 = (chunk - b * cpc) * SW10_LC;
+    // this warp's rows of the chunk: row q -> output line sl * lines_per_sl + q / fiters, column 32 (q % fiters) + lane
+    auto row_meta = [&](int q, int& line, int& fo) -> bool {
+      line = sl * lines_per_sl + q / fiters;
+      fo = (q % fiters) * 32 + lane;
+      return q < nq && to0 + line < g.Tout && fo < g.Fout;
+    };
+    auto row_load = [&](int q) -> uint4 {
+      int line, fo;
+      if (!row_meta(q, line, fo)) return make_uint4(0u, 0u, 0u, 0u);
+      return *(const uint4*)(dout + (((int64_t)b * g.Tout + to0 + line) * g.Fout + fo) * g.ld_out + cg * 8);
+    };
+    uint4 dq[4];  // four rows of dout in flight per lane, the first ones across the staging barrier
+#pragma unroll
+    for (int u = 0; u < 4; ++u) dq[u] = row_load(u);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();  // this chunk's lines are visible; every warp is done with the other buffer
+    stage(chunk + gridDim.x, cbuf ^ 1);
+    const float* sbuf = s10 + (size_t)cbuf * NL * W;
+    for (int q0 = 0; q0 < nq; q0 += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint4 dcur = dq[u];
+        dq[u] = row_load(q0 + u + 4);
+        int line_c, fo_c;
+        if (!row_meta(q0 + u, line_c, fo_c)) continue;  // (zeros would add nothing)
+        const float* xs = sbuf + (line_c * g.st + it) * W + fo_c * g.sf;
+        float xv[STEM_KF_MAX];
+#pragma unroll
+        for (int k = 0; k < STEM_KF_MAX; ++k) xv[k] = k < g.kf ? xs[k] : 0.f;
+        const F8 d = unpack8(dcur);
+#pragma unroll
+        for (int k = 0; k < STEM_KF_MAX; ++k)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j][k] = fmaf(d.v[j], xv[k], acc[j][k]);
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();  // the staged lines are dead: their space becomes the per-warp task slots [nwarps][8][STEM_KF_MAX]
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+#pragma unroll
+    for (int k = 0; k < STEM_KF_MAX; ++k) {
+      if (k < g.kf) {  // uniform across the warp
+        float v = acc[j][k];
+#pragma unroll
+        for (int sft = 16; sft >= 1; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
+        if (lane == 0) s10[(warp * 8 + j) * STEM_KF_MAX + k] = v;
+      }
+    }
+  __syncthreads();
+  const int n_out = g.Cout * taps;
+  float* my = dwp + (size_t)blockIdx.x * n_out;
+  for (int i = threadIdx.x; i < n_out; i += blockDim.x) {
+    const int n = i / taps, tp = i - n * taps;
+    const int it_ = tp / g.kf, k = tp - it_ * g.kf;
+    const int gq = it_ * CG + (n >> 3), j = n & 7;
+    float t = 0.f;
+    for (int s_ = 0; s_ < nsl; ++s_) t += s10[((s_ * ngroups + gq) * 8 + j) * STEM_KF_MAX + k];  // slices in order
+    my[i] = t;
+  }
+  if (dw == nullptr) return;
+  __shared__ unsigned s_flag;
+  if (!stats_last_cta(ticket, gridDim.x, &s_flag)) return;
+  stats_ordered_reduce(dwp, (int)gridDim.x, n_out, n_out, (double*)s10, [&](int s_, double v) {
+    dw[s_] = accumulate ? dw[s_] + (float)v : (float)v;
+  });
+}
+
 static void stem_v9_geom(const asf_conv_geom_t* g, int* nslice, int64_t* blocks, int64_t* rpb) {
   const int64_t rows = (int64_t)g->B * g->Tout * g->Fout;
   const int ngroups = (g->Cout / 8) * g->kt;
@@ -837,6 +963,52 @@ int stem_wgrad_v9(const float* in, const bf16* dout, float* dwp, const asf_conv_
   ASF_CHECK_ARG(smem <= 48 * 1024, "asf_stem_wgrad: %zu bytes of task slots exceed 48 KB", smem);
   ASF_CUDA(launch_pdl(stem_wgrad_v9_kernel, dim3((unsigned)blocks), dim3(256), smem, st, in, dout, dwp, *g, (int)rpb,
                       nslice));
+  ASF_LAUNCH_CHECK();
+  return 0;
+}
+
+// v10 launch geometry; rows == 0: this shape stays on v9 (more than 16 (group, kernel row) pairs, or lines too long)
+struct StemV10 {
+  int nsl, NL, W, cpc, n_chunks, threads, grid;
+  size_t smem;
+};
+static bool stem_v10_geom(const asf_conv_geom_t* g, StemV10* v) {
+  const int ngroups = (g->Cout / 8) * g->kt;
+  if (g->Cout % 8 || g->kf > STEM_KF_MAX || ngroups < 1 || ngroups > 16 || (g->Cout * g->kt * g->kf) % 4) return false;
+  int nsl = 1;
+  while (nsl * 2 <= SW10_LC && ngroups * nsl * 2 <= 16) nsl *= 2;
+  v->nsl = nsl;
+  v->NL = (SW10_LC - 1) * g->st + g->kt;
+  v->W = (g->Fout - 1) * g->sf + g->kf;
+  v->cpc = (int)cdiv(g->Tout, SW10_LC);
+  const int64_t chunks = (int64_t)g->B * v->cpc;
+  if (chunks >= (1LL << 31)) return false;
+  v->n_chunks = (int)chunks;
+  v->threads = 32 * ngroups * nsl;
+  size_t bytes = 2 * sizeof(float) * (size_t)v->NL * v->W;  // double buffered
+  const size_t slots = sizeof(float) * (size_t)(v->threads / 32) * 8 * STEM_KF_MAX;
+  const size_t scratch = sizeof(double) * 4 * (size_t)v->threads;
+  if (slots > bytes) bytes = slots;
+  if (scratch > bytes) bytes = scratch;
+  if (bytes > 48 * 1024) return false;
+  v->smem = bytes;
+  v->grid = (int)(chunks < 148 ? chunks : 148);  // one block per SM (110 registers x 320..512 threads)
+  return true;
+}
+
+int stem_wgrad_v10_rows(const asf_conv_geom_t* g) {
+  StemV10 v;
+  return stem_v10_geom(g, &v) ? v.grid : 0;
+}
+
+int stem_wgrad_v10(const float* in, const bf16* dout, float* dwp, float* dw, int accumulate, unsigned* ticket,
+                   const asf_conv_geom_t* g, cudaStream_t st) {
+  StemV10 v;
+  ASF_CHECK_ARG(stem_v10_geom(g, &v), "asf_stem_wgrad_fused: geometry not supported (asf_stem_wgrad_fused_rows == 0)");
+  ASF_CHECK_ARG((int64_t)g->B * g->Tout * g->Fout < (1LL << 31) && (int64_t)g->B * g->Tin * g->Fin < (1LL << 31),
+                "asf_stem_wgrad_fused: tensor too large");
+  ASF_CUDA(launch_pdl(stem_wgrad_v10_kernel, dim3((unsigned)v.grid), dim3((unsigned)v.threads), v.smem, st, in, dout, dwp, dw,
+                      accumulate, ticket, *g, v.nsl, v.NL, v.W, v.cpc, v.n_chunks));
   ASF_LAUNCH_CHECK();
   return 0;
 }

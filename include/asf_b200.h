@@ -252,6 +252,14 @@ int asf_tapgemm_wgrad_ksplit(const asf_tapgemm_t* p);
 int asf_stem_wgrad_ksplit(const asf_conv_geom_t* g, int dout_dtype);
 int asf_stem_wgrad(const float* in, const void* dout, int dout_dtype, float* dwp, const asf_conv_geom_t* g,
                    void* stream);
+/* The same with the cross-block sum folded in (bf16 dout): blocks store partial rows into dwp (>= rows x Cout*kt*kf
+ * floats, rows = asf_stem_wgrad_fused_rows(), 0 when the shape is not supported), the block drawing the last `ticket`
+ * (one zero-initialised, self-resetting uint32) adds them in block order and writes dw[Cout][1][kt][kf]
+ * (accumulate: dw += ...).  Input lines are staged in shared memory; this is the last kernel of the backward pass
+ * (stem_helper.py:150-157 -> autograd's conv weight gradient), so no reduction launch follows it. */
+int asf_stem_wgrad_fused_rows(const asf_conv_geom_t* g, int dout_dtype);
+int asf_stem_wgrad_fused(const float* in, const void* dout, int dout_dtype, float* dwp, float* dw, int accumulate,
+                         uint32_t* ticket, const asf_conv_geom_t* g, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Weight (re)packing between the reference's state_dict layout (OIHW fp32) and kernel layouts.

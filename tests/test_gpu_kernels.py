@@ -479,6 +479,22 @@ def test_stem_wgrad(name, T, cout, k, s, p):
     torch.cuda.synchronize()
     assert torch.equal(dwp, dwp2), "the stem weight gradient must be bit-reproducible (no atomics)"
     assert rel_err(dw, 2 * w.grad) < 1e-4
+    # the fused form: input lines staged in shared memory, the cross-block sum folded into the kernel
+    rows = L.lib().asf_stem_wgrad_fused_rows(C.byref(g), L.BF16)
+    assert rows >= 1
+    ws = torch.full((rows, n), float("nan"), device="cuda")
+    tk = torch.zeros(1, dtype=torch.int32, device="cuda")
+    dwf = torch.full_like(dw, 5.0)
+    L.call("asf_stem_wgrad_fused", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(ws), L.ptr(dwf), 0, L.ptr(tk), C.byref(g), st)
+    dwf1 = dwf.clone()
+    L.call("asf_stem_wgrad_fused", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(ws), L.ptr(dwf), 1, L.ptr(tk), C.byref(g), st)
+    dwf2 = torch.full_like(dw, -1.0)
+    L.call("asf_stem_wgrad_fused", L.ptr(x), L.ptr(dy), L.BF16, L.ptr(ws), L.ptr(dwf2), 0, L.ptr(tk), C.byref(g), st)
+    torch.cuda.synchronize()
+    assert int(tk) == 0
+    assert rel_err(dwf1, w.grad) < 1e-4, rel_err(dwf1, w.grad)
+    assert rel_err(dwf, 2 * w.grad) < 1e-4
+    assert torch.equal(dwf1, dwf2), "the fused stem weight gradient must be bit-reproducible"
     # fp32 dout (parity mode): the scalar kernel, double accumulators
     dyf = dy.float()
     ksf = L.lib().asf_stem_wgrad_ksplit(C.byref(g), L.F32)
