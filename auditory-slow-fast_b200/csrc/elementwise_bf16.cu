@@ -830,6 +830,7 @@ __global__ void __launch_bounds__(512) stem_wgrad_v10_kernel(const float* __rest
   const int cg = grp % CG, it = grp / CG;
   const int lines_per_sl = SW10_LC / nsl;
   const int fiters = (g.Fout + 31) >> 5;
+  const int fl = (fiters & (fiters - 1)) == 0 ? 31 - __clz(fiters) : -1;  // log2(fiters) when it is a power of two
   const int nq = lines_per_sl * fiters;
   float acc[8][STEM_KF_MAX];
 #pragma unroll
@@ -862,15 +863,19 @@ __global__ void __launch_bounds__(512) stem_wgrad_v10_kernel(const float* __rest
   for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, cbuf ^= 1) {
     const int b = chunk / cpc, to0 = (chunk - b * cpc) * SW10_LC;
     // this warp's rows of the chunk: row q -> output line sl * lines_per_sl + q / fiters, column 32 (q % fiters) + lane
+    // (fiters is a power of two for every shipped stem: shifts instead of divisions in the inner loop)
+    const bf16* dbase = dout + ((int64_t)b * g.Tout + to0) * g.Fout * g.ld_out + cg * 8;
+    const int ld_o = (int)g.ld_out;
     auto row_meta = [&](int q, int& line, int& fo) -> bool {
-      line = sl * lines_per_sl + q / fiters;
-      fo = (q % fiters) * 32 + lane;
+      const int ql = fl >= 0 ? (q >> fl) : q / fiters;
+      line = sl * lines_per_sl + ql;
+      fo = (q - ql * fiters) * 32 + lane;
       return q < nq && to0 + line < g.Tout && fo < g.Fout;
     };
     auto row_load = [&](int q) -> uint4 {
       int line, fo;
       if (!row_meta(q, line, fo)) return make_uint4(0u, 0u, 0u, 0u);
-      return *(const uint4*)(dout + (((int64_t)b * g.Tout + to0 + line) * g.Fout + fo) * g.ld_out + cg * 8);
+      return *(const uint4*)(dbase + (int64_t)((line * g.Fout + fo) * ld_o));
     };
     uint4 dq[4];  // four rows of dout in flight per lane, the first ones across the staging barrier
 #pragma unroll

@@ -448,11 +448,12 @@ def test_stem_pool_forward_backward(dtype):
 
 @pytest.mark.parametrize("name,T,cout,k,s,p", [("slow", 100, 64, (1, 7), (2, 2), (0, 3)),
                                                ("fast", 400, 8, (5, 7), (2, 2), (2, 3)),
-                                               ("ragged", 37, 16, (3, 5), (2, 2), (1, 2))])
+                                               ("ragged", 37, 16, (3, 5), (2, 2), (1, 2)),
+                                               ("wide", 21, 8, (5, 7), (2, 2), (2, 3))])
 def test_stem_wgrad(name, T, cout, k, s, p):
     """asf_stem_wgrad (C_in = 1 stems, stem_helper.py:150-157) against torch's conv weight gradient, overwrite and
     accumulate; 'ragged' has row counts that do not divide the warp / slice tiling."""
-    B, Fq = 3, 128 if name != "ragged" else 50
+    B, Fq = 3, {"ragged": 50, "wide": 192}.get(name, 128)  # wide: 96 output columns = three 32-lane steps per line
     torch.manual_seed(3)
     x = torch.randn(B, 1, T, Fq, device="cuda")
     To, Fo = (T + 2 * p[0] - k[0]) // s[0] + 1, (Fq + 2 * p[1] - k[1]) // s[1] + 1
