@@ -816,7 +816,8 @@ __global__ void __launch_bounds__(256) stem_wgrad_v9_kernel(const float* __restr
 // ticket adds them in block order (stats_reduce.cuh) and writes (or accumulates into) the gradient -- no separate
 // split-K reduction launch behind the last kernel of the step.  Bit-reproducible either way.
 constexpr int SW10_LC = 8;
-__global__ void __launch_bounds__(512) stem_wgrad_v10_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
+template <int THREADS, int MINB, int DQ>
+__global__ void __launch_bounds__(THREADS, MINB) stem_wgrad_v10_kernel(const float* __restrict__ in, const bf16* __restrict__ dout,
                                                              float* __restrict__ dwp, float* __restrict__ dw,
                                                              int accumulate, unsigned* __restrict__ ticket,
                                                              asf_conv_geom_t g, int nsl, int NL, int W, int cpc,
@@ -877,18 +878,18 @@ __global__ void __launch_bounds__(512) stem_wgrad_v10_kernel(const float* __rest
       if (!row_meta(q, line, fo)) return make_uint4(0u, 0u, 0u, 0u);
       return *(const uint4*)(dbase + (int64_t)((line * g.Fout + fo) * ld_o));
     };
-    uint4 dq[4];  // four rows of dout in flight per lane, the first ones across the staging barrier
+    uint4 dq[DQ];  // DQ rows of dout in flight per lane, the first ones across the staging barrier
 #pragma unroll
-    for (int u = 0; u < 4; ++u) dq[u] = row_load(u);
+    for (int u = 0; u < DQ; ++u) dq[u] = row_load(u);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();  // this chunk's lines are visible; every warp is done with the other buffer
     stage(chunk + gridDim.x, cbuf ^ 1);
     const float* sbuf = s10 + (size_t)cbuf * NL * W;
-    for (int q0 = 0; q0 < nq; q0 += 4) {
+    for (int q0 = 0; q0 < nq; q0 += DQ) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < DQ; ++u) {
         const uint4 dcur = dq[u];
-        dq[u] = row_load(q0 + u + 4);
+        dq[u] = row_load(q0 + u + DQ);
         int line_c, fo_c;
         if (!row_meta(q0 + u, line_c, fo_c)) continue;  // (zeros would add nothing)
         const float* xs = sbuf + (line_c * g.st + it) * W + fo_c * g.sf;
@@ -974,7 +975,7 @@ int stem_wgrad_v9(const float* in, const bf16* dout, float* dwp, const asf_conv_
 
 // v10 launch geometry; rows == 0: this shape stays on v9 (more than 16 (group, kernel row) pairs, or lines too long)
 struct StemV10 {
-  int nsl, NL, W, cpc, n_chunks, threads, grid;
+  int nsl, NL, W, cpc, n_chunks, threads, grid, per_sm;
   size_t smem;
 };
 static bool stem_v10_geom(const asf_conv_geom_t* g, StemV10* v) {
@@ -997,7 +998,15 @@ static bool stem_v10_geom(const asf_conv_geom_t* g, StemV10* v) {
   if (scratch > bytes) bytes = scratch;
   if (bytes > 48 * 1024) return false;
   v->smem = bytes;
-  v->grid = (int)(chunks < 148 ? chunks : 148);  // one block per SM (110 registers x 320..512 threads)
+  // two blocks per SM when a block is <= 320 threads (the <320, 2, 2> instantiation: <= 102 registers); ASF_STEM_V10_PER_SM=1
+  // keeps one
+  static int per_sm_env = -1;
+  if (per_sm_env < 0) {
+    const char* e = getenv("ASF_STEM_V10_PER_SM");
+    per_sm_env = e ? atoi(e) : 2;
+  }
+  v->per_sm = (v->threads <= 320 && per_sm_env == 2) ? 2 : 1;
+  v->grid = (int)(chunks < 148 * v->per_sm ? chunks : 148 * v->per_sm);
   return true;
 }
 
@@ -1012,8 +1021,13 @@ int stem_wgrad_v10(const float* in, const bf16* dout, float* dwp, float* dw, int
   ASF_CHECK_ARG(stem_v10_geom(g, &v), "asf_stem_wgrad_fused: geometry not supported (asf_stem_wgrad_fused_rows == 0)");
   ASF_CHECK_ARG((int64_t)g->B * g->Tout * g->Fout < (1LL << 31) && (int64_t)g->B * g->Tin * g->Fin < (1LL << 31),
                 "asf_stem_wgrad_fused: tensor too large");
-  ASF_CUDA(launch_pdl(stem_wgrad_v10_kernel, dim3((unsigned)v.grid), dim3((unsigned)v.threads), v.smem, st, in, dout, dwp, dw,
-                      accumulate, ticket, *g, v.nsl, v.NL, v.W, v.cpc, v.n_chunks));
+  if (v.threads <= 320 && v.per_sm == 2) {
+    ASF_CUDA(launch_pdl(stem_wgrad_v10_kernel<320, 2, 2>, dim3((unsigned)v.grid), dim3((unsigned)v.threads), v.smem, st, in, dout,
+                        dwp, dw, accumulate, ticket, *g, v.nsl, v.NL, v.W, v.cpc, v.n_chunks));
+  } else {
+    ASF_CUDA(launch_pdl(stem_wgrad_v10_kernel<512, 1, 4>, dim3((unsigned)v.grid), dim3((unsigned)v.threads), v.smem, st, in, dout,
+                        dwp, dw, accumulate, ticket, *g, v.nsl, v.NL, v.W, v.cpc, v.n_chunks));
+  }
   ASF_LAUNCH_CHECK();
   return 0;
 }
