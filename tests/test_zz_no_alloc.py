@@ -52,7 +52,7 @@ def test_channel_stats_noalloc_allocates_nothing_and_rejects_oversize():
         L.call("asf_channel_stats_noalloc", L.ptr(x), L.BF16, rows, Cn, Cn, L.ptr(out), L.stream_ptr())
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
-    assert free1 == free0, (free0, free1)  # the driver handed out no device memory
+    assert free1 >= free0, (free0, free1)  # the driver handed out no device memory
     # beyond the built-in scratch: a clear error, nothing launched
     big = MAX_CHANNELS + 8
     xb = torch.randn(64, big, device="cuda").to(torch.bfloat16)
